@@ -1,0 +1,165 @@
+/* rails_cuda.h -- C ABI of the B200 (sm_100a) backend for the RAILS hot path.
+ *
+ * This is the drop-in boundary below the reference's plugin surface
+ * (SURVEY.md §8(b)).  The reference's solver loop
+ * (/root/reference/src/LyapunovSolver.hpp:100-346) talks only to three
+ * duck-typed C++ classes -- Operator, MultiVector, DenseMatrix
+ * (/root/reference/src/LyapunovSolverDecl.hpp:9-51).  The C++ wrapper classes
+ * in rails_b200/host/ implement those concepts for the GPU and call nothing
+ * but the functions declared here; each declaration cites the reference
+ * method whose arithmetic it replaces (StlWrapper = /root/reference/src/
+ * StlWrapper.cpp, EpetraMV = src/Epetra_MultiVectorWrapper.cpp, EpetraOp =
+ * src/Epetra_OperatorWrapper.cpp).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every function returns 0 on success and
+ *     a non-zero code on failure (the message is kept for
+ *     rails_cuda_last_error()).  No exceptions cross this boundary, matching
+ *     the reference's int-code error style (src/LyapunovSolver.hpp:89-95).
+ *   - a rails_mv_t is a column-major FP64 block resident in HBM: `rows` local
+ *     rows, leading dimension padded to a multiple of 16 doubles so that every
+ *     column starts on a 128-byte line, `cols` columns of capacity.
+ *     Operations address a column range [col0, col0+ncols).
+ *   - one process drives one GPU.  With a communicator
+ *     (rails_cuda_comm_init) a DISTRIBUTED multivector holds this rank's
+ *     contiguous row block of an Epetra-style linear map and inner products
+ *     are summed over ranks; a REPLICATED one (Epetra_LocalMap analogue,
+ *     src/Epetra_MultiVectorWrapper.cpp:226,451) is identical on all ranks.
+ *   - work is enqueued on the library's stream; a call synchronises only when
+ *     it returns a value to host memory.
+ *   - there is no CPU fallback: without a usable CUDA device every compute
+ *     entry point fails with RAILS_ERR_CUDA.
+ */
+#ifndef RAILS_CUDA_H
+#define RAILS_CUDA_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rails_mv_s *rails_mv_t;
+typedef struct rails_csr_s *rails_csr_t;
+
+enum {
+    RAILS_OK = 0,
+    RAILS_ERR_CUDA = 1,      /* CUDA runtime / NCCL failure or no device */
+    RAILS_ERR_ARG = 2,       /* bad handle, range or shape               */
+    RAILS_ERR_STATE = 3      /* library not initialised                  */
+};
+
+enum {
+    RAILS_MV_DISTRIBUTED = 0,
+    RAILS_MV_REPLICATED = 1
+};
+
+#define RAILS_NCCL_ID_BYTES 128
+
+/* ---- context --------------------------------------------------------- */
+int rails_cuda_init(int device);
+int rails_cuda_finalize(void);
+int rails_cuda_is_initialized(void);
+int rails_cuda_sync(void);
+const char *rails_cuda_last_error(void);
+/* number of this library's kernels launched since init (bench.py's
+ * gpu_launches) */
+long long rails_cuda_kernel_launches(void);
+/* device memory currently held by multivectors and operators, bytes */
+long long rails_cuda_bytes_in_use(void);
+/* CUDA-event timing on the library stream (bench.py, Timer sections):
+ * rails_cuda_event_record(slot) marks a point, rails_cuda_event_elapsed_ms
+ * synchronises on `stop` and returns the time between two marks. */
+int rails_cuda_event_record(int slot);
+int rails_cuda_event_elapsed_ms(int start_slot, int stop_slot, float *ms);
+
+/* ---- communicator (row partition over GPUs; Epetra_MpiComm analogue,
+ *      src/main.cpp:47) ------------------------------------------------- */
+int rails_cuda_comm_unique_id(char id[RAILS_NCCL_ID_BYTES]);
+int rails_cuda_comm_init(int rank, int nranks, const char id[RAILS_NCCL_ID_BYTES]);
+int rails_cuda_comm_rank(void);
+int rails_cuda_comm_size(void);
+/* Epetra_Map(m, 0, comm) linear map: rows [begin, end) of rank r of P */
+int rails_partition_rows(long long m, int nranks, int rank,
+                         long long *begin, long long *end);
+
+/* ---- multivector storage (StlWrapper ctors/resize/view/push_back,
+ *      src/StlWrapper.cpp:19-121,219-263,323-392) ----------------------- */
+int rails_mv_alloc(long long rows, int cols, int flags, rails_mv_t *out);
+int rails_mv_free(rails_mv_t mv);
+long long rails_mv_rows(rails_mv_t mv);
+long long rails_mv_ld(rails_mv_t mv);
+int rails_mv_cols(rails_mv_t mv);
+int rails_mv_flags(rails_mv_t mv);
+/* dst[:, dcol..] = src[:, scol..]   (memcpy in push_back :367-374, view
+ * assignment :65-121, copy ctor :31-44) */
+int rails_mv_copy_cols(rails_mv_t dst, int dcol, rails_mv_t src, int scol, int ncols);
+/* host <-> device, host block is column-major with leading dimension ldh */
+int rails_mv_upload(rails_mv_t mv, int col0, int ncols, const double *host, long long ldh);
+int rails_mv_download(rails_mv_t mv, int col0, int ncols, double *host, long long ldh);
+/* test-only element access (the (m,n) ctor + operator()(i,j) of
+ * test/GenericMultiVectorWrapper_test.cpp:23-29) */
+int rails_mv_get(rails_mv_t mv, long long row, int col, double *value);
+int rails_mv_set(rails_mv_t mv, long long row, int col, double value);
+
+/* ---- BLAS-1 family (StlWrapper :123-166) ------------------------------ */
+int rails_mv_fill(rails_mv_t mv, int col0, int ncols, double value);     /* = double :123-129 */
+int rails_mv_scal(rails_mv_t mv, int col0, int ncols, double alpha);     /* *=, /=   :131-145 */
+/* y[:, yc0..] += alpha * x[:, xc0..]                    (+=, -= :147-161) */
+int rails_mv_axpy(rails_mv_t y, int yc0, double alpha, rails_mv_t x, int xc0, int ncols);
+/* max_i sum_j |x_ij| over this rank's rows, then max over ranks (:291-303) */
+int rails_mv_norm_inf(rails_mv_t mv, int col0, int ncols, double *out);
+
+/* ---- inner products: out = X' Y  (a x b, host, column-major, ld = ldo)
+ *      StlWrapper::dot :394-412, EpetraMV::dot :418-438.  Includes the
+ *      cross-rank sum when both operands are distributed. ---------------- */
+int rails_mv_dot(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
+                 double *out, int ldo);
+/* same product left on the device in a REPLICATED multivector (a rows);
+ * used for Y = B' q (src/LyapunovSolver.hpp:150,389) without a host sync */
+int rails_mv_dot_dev(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
+                     rails_mv_t Out, int oc0);
+
+/* ---- tall-skinny times small: Out[:, oc0..oc0+c) = alpha * V[:, vc0..vc0+k) * C
+ *      + beta * Out      (StlWrapper::operator* :168-187, EpetraMV :194-241)
+ *      C is k x c column-major on the host (ldc) or a replicated multivector
+ *      on the device.  Out must not overlap the V columns read. ---------- */
+int rails_mv_gemm(rails_mv_t V, int vc0, int k, const double *C, int ldc, int c,
+                  double alpha, double beta, rails_mv_t Out, int oc0);
+int rails_mv_gemm_dev(rails_mv_t V, int vc0, int k, rails_mv_t C, int cc0, int c,
+                      double alpha, double beta, rails_mv_t Out, int oc0);
+
+/* ---- Gram-Schmidt: column-wise CGS2 of columns [first, last] against all
+ *      earlier columns (StlWrapper::orthogonalize :305-321), executed as one
+ *      device-side chain with no host round trip. ------------------------ */
+int rails_mv_orthogonalize(rails_mv_t V, int col0, int first, int last);
+
+/* ---- random(): bit-exact restatement of StlWrapper::random :414-423 with
+ *      libstdc++'s default_random_engine (= minstd_rand0) seeded by `seed`
+ *      (the caller passes std::rand()), filling the GLOBAL rows x ncols
+ *      block row-major; this rank writes rows [row_offset, row_offset+rows).
+ *      Values in (-1, 1). ------------------------------------------------ */
+int rails_mv_random(rails_mv_t mv, int col0, int ncols, long long row_offset,
+                    unsigned int seed);
+
+/* ---- operator: CSR x tall-skinny (EpetraOp::operator* :75-91 ->
+ *      Epetra_CrsMatrix::Apply).  rowptr has rows+1 entries; colidx holds
+ *      GLOBAL column indices; this rank owns global rows
+ *      [row_offset, row_offset+rows) of a global_rows x global_cols matrix. */
+int rails_csr_create(long long rows, long long global_rows, long long global_cols,
+                     long long row_offset, const int *rowptr, const int *colidx,
+                     const double *vals, rails_csr_t *out);
+int rails_csr_free(rails_csr_t A);
+long long rails_csr_rows(rails_csr_t A);
+long long rails_csr_nnz(rails_csr_t A);
+/* Y[:, yc0..yc0+ncols) = op(A) * X[:, xc0..xc0+ncols);  trans != 0 applies A'
+ * (transpose flag of EpetraOp :50-55,81; single-rank only) */
+int rails_csr_spmm(rails_csr_t A, int trans, rails_mv_t X, int xc0, int ncols,
+                   rails_mv_t Y, int yc0);
+/* sqrt(lambda_max(A'A)) by power iteration on the device (EpetraOp::norm
+ * :115-145; reached only when B is an Operator) */
+int rails_csr_norm2(rails_csr_t A, double *out);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

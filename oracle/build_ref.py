@@ -1,0 +1,79 @@
+"""TEST INFRASTRUCTURE: build recipe for oracle/_ref (the reference arm).
+
+Compiles the reference's own sources where they lie under /root/reference
+(nothing is copied into the repo) together with the small C entry points in
+oracle/ref_entry_*.cpp.  Outputs go only to oracle/_ref/ (git-ignored, but it
+travels to the GPU box with the gpurun snapshot).
+
+    oracle/_ref/librails_ref_stl.so   reference loop + reference StlWrapper
+                                      (dense A; config C1 and the unit pins)
+    oracle/_ref/librails_ref_csr.so   reference loop + oracle CSR/OpenMP
+                                      wrappers (sparse CPU arm, configs C2-C5)
+
+Flags follow the reference's no-build-type default `-O2` (CMakeLists.txt:16),
+NOT its Release `-O3 -ffast-math` (CMakeLists.txt:18), so that the numbers are
+reproducible.  SLICOT is absent on this image: sb03md_ is the
+stand-in in rails_b200/host/sb03md_shim.cpp; BLAS/LAPACK is the OpenBLAS
+bundled with opencv-python-headless.
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = "/root/reference"
+OUT = os.path.join(HERE, "_ref")
+
+
+def openblas_path():
+    import importlib.util
+    spec = importlib.util.find_spec("cv2")
+    cands = []
+    if spec and spec.submodule_search_locations:
+        site = os.path.dirname(list(spec.submodule_search_locations)[0])
+        cands.append(os.path.join(site, "opencv_python_headless.libs"))
+    cands.append("/opt/prime-rl/.venv/lib/python3.12/site-packages/"
+                 "opencv_python_headless.libs")
+    for d in cands:
+        if os.path.isdir(d):
+            for f in sorted(os.listdir(d)):
+                if f.startswith("libopenblas"):
+                    return d, os.path.join(d, f)
+    raise RuntimeError("no LP64 OpenBLAS with plain LAPACK symbols found")
+
+
+def run(cmd):
+    print("+", " ".join(cmd), flush=True)
+    subprocess.check_call(cmd)
+
+
+def build(verbose=True):
+    if not os.path.isdir(os.path.join(REF, "src")):
+        if verbose:
+            print("oracle/_ref: /root/reference absent, keeping prebuilt files")
+        return False
+    os.makedirs(OUT, exist_ok=True)
+    libdir, blas = openblas_path()
+    ref_srcs = [os.path.join(REF, "src", f) for f in
+                ("StlWrapper.cpp", "StlVector.cpp", "LapackWrapper.cpp",
+                 "SlicotWrapper.cpp", "Timer.cpp")]
+    shim = os.path.join(ROOT, "rails_b200", "host", "sb03md_shim.cpp")
+    common = ["g++", "-std=c++14", "-O2", "-fPIC", "-shared", "-fopenmp",
+              "-I" + REF, "-I" + HERE, "-I" + os.path.join(ROOT, "rails_b200", "host")]
+    link = [blas, "-Wl,--disable-new-dtags,-rpath," + libdir]
+
+    run(common + ["-o", os.path.join(OUT, "librails_ref_stl.so"),
+                  os.path.join(HERE, "ref_entry_stl.cpp")] + ref_srcs + [shim] + link)
+
+    csr_entry = os.path.join(HERE, "ref_entry_csr.cpp")
+    if os.path.exists(csr_entry):
+        # StlWrapper stays the DenseMatrix of this arm, as in the reference
+        run(common + ["-o", os.path.join(OUT, "librails_ref_csr.so"), csr_entry,
+                      os.path.join(HERE, "cpu_backend.cpp")] + ref_srcs + [shim] + link)
+    return True
+
+
+if __name__ == "__main__":
+    build()
+    sys.exit(0)

@@ -1,0 +1,128 @@
+// TEST INFRASTRUCTURE (oracle/_ref build): the UNMODIFIED reference solver
+// loop (/root/reference/src/LyapunovSolver.hpp) over the reference's own
+// StlWrapper backend (/root/reference/src/StlWrapper.cpp), behind a C entry
+// point so pytest / bench.py can drive it with ctypes.
+//
+// Compiled by oracle/build_ref.py from the sources where they lie under
+// /root/reference; only the resulting .so (oracle/_ref/) travels.  The Stl
+// backend is dense-only (A is an m x m column-major array and A*W is dgemm,
+// src/StlWrapper.cpp:168-187), so this arm is usable up to m ~ 1e4.
+#include <algorithm>
+#include <chrono>
+#include <iostream>
+#include <utility>
+
+#include "capture.hpp"
+
+#include "src/LyapunovSolver.hpp"
+#include "src/StlWrapper.hpp"
+
+using namespace RAILS;
+
+extern "C" int ref_stl_solve(
+    int m, const int *rowptr, const int *colidx, const double *vals,
+    int n_b, const double *B_in, unsigned seed,
+    int nparams, const char *const *keys, const double *pvals,
+    int hist_cap, double *hist_abs, double *hist_rel, int *hist_len,
+    int *k_out, int v_cap_cols, double *V_out, double *T_out,
+    double *seconds)
+{
+    std::srand(seed);
+
+    StlWrapper A(m, m);
+    A = 0.0;
+    for (int i = 0; i < m; ++i)
+        for (int p = rowptr[i]; p < rowptr[i + 1]; ++p)
+            A(i, colidx[p]) = vals[p];
+
+    StlWrapper B(m, n_b);
+    if (B_in)
+    {
+        for (int j = 0; j < n_b; ++j)
+            for (int i = 0; i < m; ++i)
+                B(i, j) = B_in[i + (size_t)j * m];
+    }
+    else
+        B.random();
+
+    // M is stored and never read by the C++ solver; the
+    // reference's own tests pass B for it (test/LyapunovSolver_test.cpp:138).
+    Solver<StlWrapper, StlWrapper, StlWrapper> solver(A, B, B);
+    rails_oracle::ParameterList params(nparams, keys, pvals);
+    int ret = solver.set_parameters(params);
+    if (ret)
+        return 100 + ret;
+
+    StlWrapper V(m, 1);
+    StlWrapper T;
+
+    std::string log;
+    {
+        rails_oracle::CoutCapture cap;
+        auto t0 = std::chrono::steady_clock::now();
+        ret = solver.solve(V, T);
+        auto t1 = std::chrono::steady_clock::now();
+        if (seconds)
+            *seconds = std::chrono::duration<double>(t1 - t0).count();
+        log = cap.str();
+    }
+
+    std::vector<double> ha, hr;
+    int len = rails_oracle::parse_history(log, ha, hr);
+    if (hist_len)
+        *hist_len = len;
+    for (int i = 0; i < std::min(len, hist_cap); ++i)
+    {
+        if (hist_abs) hist_abs[i] = ha[i];
+        if (hist_rel) hist_rel[i] = hr[i];
+    }
+
+    int k = V.N();
+    if (k_out)
+        *k_out = k;
+    if (V_out && T_out && k <= v_cap_cols)
+    {
+        for (int j = 0; j < k; ++j)
+            for (int i = 0; i < m; ++i)
+                V_out[i + (size_t)j * m] = V(i, j);
+        for (int j = 0; j < k; ++j)
+            for (int i = 0; i < k; ++i)
+                T_out[i + (size_t)j * v_cap_cols] = T(i, j);
+    }
+    return ret;
+}
+
+// Direct access to the reference's StlWrapper::random() stream
+// (src/StlWrapper.cpp:414-423) for pinning the device RNG.
+extern "C" void ref_stl_random(int m, int n, unsigned seed, double *out)
+{
+    std::srand(seed);
+    StlWrapper X(m, n);
+    X.random();
+    for (int j = 0; j < n; ++j)
+        for (int i = 0; i < m; ++i)
+            out[i + (size_t)j * m] = X(i, j);
+}
+
+// Reference SlicotWrapper entry (src/SlicotWrapper.cpp:8-49) over the
+// sb03md_ stand-in, for the known answers of test/SlicotWrapper_test.cpp.
+extern "C" int ref_sb03md(int n, double *A, int lda, double *X, int ldx,
+                          double *scale)
+{
+    int info = 0;
+    sb03md('C', 'X', 'N', 'T', n, A, lda, X, ldx, scale, &info);
+    return info;
+}
+
+// Reference CGS2 (src/StlWrapper.cpp:305-321) on a caller-supplied block.
+extern "C" void ref_stl_orthogonalize(int m, int n, double *X)
+{
+    StlWrapper V(m, n);
+    for (int j = 0; j < n; ++j)
+        for (int i = 0; i < m; ++i)
+            V(i, j) = X[i + (size_t)j * m];
+    V.orthogonalize();
+    for (int j = 0; j < n; ++j)
+        for (int i = 0; i < m; ++i)
+            X[i + (size_t)j * m] = V(i, j);
+}

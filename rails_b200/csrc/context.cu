@@ -1,0 +1,380 @@
+// Context, communicator and multivector storage of librails_cuda.so.
+#include "internal.h"
+
+#include <cstdarg>
+#include <cstring>
+
+namespace rails
+{
+
+Context &ctx()
+{
+    static Context c;
+    return c;
+}
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    ctx().last_error = buf;
+    fprintf(stderr, "rails_cuda error: %s\n", buf);
+    return code;
+}
+
+static int grow(double **p, size_t *cap, size_t need)
+{
+    if (need <= *cap)
+        return RAILS_OK;
+    Context &c = ctx();
+    size_t ncap = *cap ? *cap : 4096;
+    while (ncap < need)
+        ncap *= 2;
+    if (*p)
+    {
+        // stream-ordered: earlier kernels that still use the old block finish first
+        RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+        RAILS_CUDA_TRY(cudaFree(*p));
+    }
+    RAILS_CUDA_TRY(cudaMalloc(p, ncap * sizeof(double)));
+    *cap = ncap;
+    return RAILS_OK;
+}
+
+int ensure_partial(size_t doubles) { return grow(&ctx().d_partial, &ctx().partial_cap, doubles); }
+
+int upload_small(const double *host, int k, int c, int ldc, const double **d_out)
+{
+    Context &cx = ctx();
+    const size_t n = (size_t)k * c;
+    if (n > cx.ring_cap)
+    {
+        // oversized block: grow both rings (rare: warm-start / restart blocks)
+        RAILS_CUDA_TRY(cudaStreamSynchronize(cx.stream));
+        size_t ncap = cx.ring_cap ? cx.ring_cap : (1u << 20);
+        while (ncap < n) ncap *= 2;
+        if (cx.h_ring) RAILS_CUDA_TRY(cudaFreeHost(cx.h_ring));
+        if (cx.d_coef) RAILS_CUDA_TRY(cudaFree(cx.d_coef));
+        RAILS_CUDA_TRY(cudaMallocHost(&cx.h_ring, ncap * sizeof(double)));
+        RAILS_CUDA_TRY(cudaMalloc(&cx.d_coef, ncap * sizeof(double)));
+        cx.ring_cap = cx.coef_cap = ncap;
+        cx.ring_pos = 0;
+    }
+    if (cx.ring_pos + n > cx.ring_cap)
+    {
+        // wrap: everything staged so far must have been consumed
+        RAILS_CUDA_TRY(cudaStreamSynchronize(cx.stream));
+        cx.ring_pos = 0;
+    }
+    double *h = cx.h_ring + cx.ring_pos;
+    double *d = cx.d_coef + cx.ring_pos;
+    for (int j = 0; j < c; ++j)
+        memcpy(h + (size_t)j * k, host + (size_t)j * ldc, (size_t)k * sizeof(double));
+    RAILS_CUDA_TRY(cudaMemcpyAsync(d, h, n * sizeof(double), cudaMemcpyHostToDevice, cx.stream));
+    cx.ring_pos += (n + 15) / 16 * 16;
+    *d_out = d;
+    return RAILS_OK;
+}
+
+int ensure_small(size_t doubles)
+{
+    Context &c = ctx();
+    if (doubles <= c.small_cap)
+        return RAILS_OK;
+    size_t ncap = c.small_cap ? c.small_cap : 65536;
+    while (ncap < doubles)
+        ncap *= 2;
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    if (c.d_small) RAILS_CUDA_TRY(cudaFree(c.d_small));
+    if (c.h_small) RAILS_CUDA_TRY(cudaFreeHost(c.h_small));
+    RAILS_CUDA_TRY(cudaMalloc(&c.d_small, ncap * sizeof(double)));
+    RAILS_CUDA_TRY(cudaMallocHost(&c.h_small, ncap * sizeof(double)));
+    c.small_cap = ncap;
+    return RAILS_OK;
+}
+
+}
+
+using rails::ctx;
+
+extern "C" int rails_cuda_init(int device)
+{
+    rails::Context &c = ctx();
+    if (c.ready)
+        return RAILS_OK;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return rails::fail(RAILS_ERR_CUDA,
+                           "no CUDA device available (%s); this backend has no CPU fallback",
+                           cudaGetErrorString(e));
+    if (device < 0 || device >= ndev)
+        return rails::fail(RAILS_ERR_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    RAILS_CUDA_TRY(cudaSetDevice(device));
+    c.device = device;
+    cudaDeviceProp prop;
+    RAILS_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    c.sm_count = prop.multiProcessorCount;
+    RAILS_CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    RAILS_CUDA_TRY(cudaStreamCreateWithFlags(&c.comm_stream, cudaStreamNonBlocking));
+    // keep freed blocks in the stream-ordered pool: the wrappers create many
+    // m x 1 temporaries per iteration
+    cudaMemPool_t pool;
+    RAILS_CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, device));
+    unsigned long long thresh = ~0ull;
+    RAILS_CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+    c.events.assign(64, nullptr);
+    c.ready = true;
+    int rc = rails::ensure_small(65536);
+    if (rc) return rc;
+    rc = rails::ensure_partial(1 << 20);
+    if (rc) return rc;
+    {
+        const double dummy = 0.0;
+        const double *d = nullptr;
+        rc = rails::upload_small(&dummy, 1, 1, 1, &d);   // allocates the rings
+        c.ring_pos = 0;
+    }
+    return rc;
+}
+
+extern "C" int rails_cuda_finalize(void)
+{
+    rails::Context &c = ctx();
+    if (!c.ready)
+        return RAILS_OK;
+    cudaStreamSynchronize(c.stream);
+    if (c.comm) { ncclCommDestroy(c.comm); c.comm = nullptr; }
+    for (auto &ev : c.events)
+        if (ev) { cudaEventDestroy(ev); ev = nullptr; }
+    if (c.d_partial) cudaFree(c.d_partial);
+    if (c.d_small) cudaFree(c.d_small);
+    if (c.h_small) cudaFreeHost(c.h_small);
+    if (c.d_coef) cudaFree(c.d_coef);
+    if (c.h_ring) cudaFreeHost(c.h_ring);
+    c.h_ring = nullptr; c.ring_cap = c.ring_pos = 0;
+    c.d_partial = c.d_small = c.h_small = c.d_coef = nullptr;
+    c.partial_cap = c.small_cap = c.coef_cap = 0;
+    cudaStreamDestroy(c.stream);
+    cudaStreamDestroy(c.comm_stream);
+    c.stream = c.comm_stream = nullptr;
+    c.rank = 0; c.nranks = 1;
+    c.ready = false;
+    return RAILS_OK;
+}
+
+extern "C" int rails_cuda_is_initialized(void) { return ctx().ready ? 1 : 0; }
+
+extern "C" int rails_cuda_sync(void)
+{
+    RAILS_REQUIRE_READY();
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    return RAILS_OK;
+}
+
+extern "C" const char *rails_cuda_last_error(void) { return ctx().last_error.c_str(); }
+extern "C" long long rails_cuda_kernel_launches(void) { return ctx().launches.load(); }
+extern "C" long long rails_cuda_bytes_in_use(void) { return ctx().bytes_in_use.load(); }
+
+extern "C" int rails_cuda_event_record(int slot)
+{
+    RAILS_REQUIRE_READY();
+    rails::Context &c = ctx();
+    if (slot < 0 || slot >= (int)c.events.size())
+        return rails::fail(RAILS_ERR_ARG, "event slot %d out of range", slot);
+    if (!c.events[slot])
+        RAILS_CUDA_TRY(cudaEventCreate(&c.events[slot]));
+    RAILS_CUDA_TRY(cudaEventRecord(c.events[slot], c.stream));
+    return RAILS_OK;
+}
+
+extern "C" int rails_cuda_event_elapsed_ms(int a, int b, float *ms)
+{
+    RAILS_REQUIRE_READY();
+    rails::Context &c = ctx();
+    int n = (int)c.events.size();
+    if (a < 0 || a >= n || b < 0 || b >= n || !c.events[a] || !c.events[b] || !ms)
+        return rails::fail(RAILS_ERR_ARG, "bad event slots %d, %d", a, b);
+    RAILS_CUDA_TRY(cudaEventSynchronize(c.events[b]));
+    RAILS_CUDA_TRY(cudaEventElapsedTime(ms, c.events[a], c.events[b]));
+    return RAILS_OK;
+}
+
+// ---- communicator -------------------------------------------------------
+
+extern "C" int rails_cuda_comm_unique_id(char id[RAILS_NCCL_ID_BYTES])
+{
+    static_assert(sizeof(ncclUniqueId) <= RAILS_NCCL_ID_BYTES, "id size");
+    ncclUniqueId uid;
+    RAILS_NCCL_TRY(ncclGetUniqueId(&uid));
+    memset(id, 0, RAILS_NCCL_ID_BYTES);
+    memcpy(id, &uid, sizeof(uid));
+    return RAILS_OK;
+}
+
+extern "C" int rails_cuda_comm_init(int rank, int nranks, const char id[RAILS_NCCL_ID_BYTES])
+{
+    RAILS_REQUIRE_READY();
+    rails::Context &c = ctx();
+    if (nranks < 1 || rank < 0 || rank >= nranks)
+        return rails::fail(RAILS_ERR_ARG, "bad rank %d of %d", rank, nranks);
+    if (c.comm) { ncclCommDestroy(c.comm); c.comm = nullptr; }
+    c.rank = rank;
+    c.nranks = nranks;
+    if (nranks == 1)
+        return RAILS_OK;
+    ncclUniqueId uid;
+    memcpy(&uid, id, sizeof(uid));
+    RAILS_NCCL_TRY(ncclCommInitRank(&c.comm, nranks, uid, rank));
+    return RAILS_OK;
+}
+
+extern "C" int rails_cuda_comm_rank(void) { return ctx().rank; }
+extern "C" int rails_cuda_comm_size(void) { return ctx().nranks; }
+
+extern "C" int rails_partition_rows(long long m, int nranks, int rank,
+                                    long long *begin, long long *end)
+{
+    if (nranks < 1 || rank < 0 || rank >= nranks || m < 0 || !begin || !end)
+        return rails::fail(RAILS_ERR_ARG, "bad partition request");
+    long long base = m / nranks, rem = m % nranks;
+    *begin = rank * base + (rank < rem ? rank : rem);
+    *end = *begin + base + (rank < rem ? 1 : 0);
+    return RAILS_OK;
+}
+
+// ---- multivector storage ---------------------------------------------------
+
+static int check_range(rails_mv_t mv, int col0, int ncols, const char *what)
+{
+    if (!mv)
+        return rails::fail(RAILS_ERR_ARG, "%s: null multivector", what);
+    if (col0 < 0 || ncols < 0 || col0 + ncols > mv->cols)
+        return rails::fail(RAILS_ERR_ARG, "%s: columns [%d,%d) outside capacity %d",
+                           what, col0, col0 + ncols, mv->cols);
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_alloc(long long rows, int cols, int flags, rails_mv_t *out)
+{
+    RAILS_REQUIRE_READY();
+    if (rows < 0 || cols < 0 || !out)
+        return rails::fail(RAILS_ERR_ARG, "rails_mv_alloc(%lld, %d)", rows, cols);
+    rails_mv_s *mv = new rails_mv_s();
+    mv->rows = rows;
+    mv->ld = ((rows + 15) / 16) * 16;
+    if (mv->ld == 0) mv->ld = 16;
+    mv->cols = cols;
+    mv->flags = flags;
+    mv->bytes = (size_t)mv->ld * (size_t)(cols > 0 ? cols : 1) * sizeof(double);
+    cudaError_t e = cudaMallocAsync(&mv->data, mv->bytes, ctx().stream);
+    if (e != cudaSuccess)
+    {
+        delete mv;
+        return rails::fail(RAILS_ERR_CUDA, "cudaMallocAsync(%zu bytes): %s",
+                           (size_t)((rows + 15) / 16 * 16) * cols * 8, cudaGetErrorString(e));
+    }
+    ctx().bytes_in_use.fetch_add((long long)mv->bytes);
+    *out = mv;
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_free(rails_mv_t mv)
+{
+    if (!mv)
+        return RAILS_OK;
+    if (ctx().ready && mv->data)
+    {
+        RAILS_CUDA_TRY(cudaFreeAsync(mv->data, ctx().stream));
+        ctx().bytes_in_use.fetch_sub((long long)mv->bytes);
+    }
+    delete mv;
+    return RAILS_OK;
+}
+
+extern "C" long long rails_mv_rows(rails_mv_t mv) { return mv ? mv->rows : -1; }
+extern "C" long long rails_mv_ld(rails_mv_t mv) { return mv ? mv->ld : -1; }
+extern "C" int rails_mv_cols(rails_mv_t mv) { return mv ? mv->cols : -1; }
+extern "C" int rails_mv_flags(rails_mv_t mv) { return mv ? mv->flags : -1; }
+
+extern "C" int rails_mv_copy_cols(rails_mv_t dst, int dcol, rails_mv_t src, int scol, int ncols)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_range(dst, dcol, ncols, "copy_cols dst");
+    if (rc) return rc;
+    rc = check_range(src, scol, ncols, "copy_cols src");
+    if (rc) return rc;
+    if (dst->rows != src->rows)
+        return rails::fail(RAILS_ERR_ARG, "copy_cols: %lld vs %lld rows", dst->rows, src->rows);
+    if (ncols == 0 || dst->rows == 0)
+        return RAILS_OK;
+    RAILS_CUDA_TRY(cudaMemcpy2DAsync(dst->data + (size_t)dcol * dst->ld, dst->ld * sizeof(double),
+                                     src->data + (size_t)scol * src->ld, src->ld * sizeof(double),
+                                     (size_t)dst->rows * sizeof(double), ncols,
+                                     cudaMemcpyDeviceToDevice, ctx().stream));
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_upload(rails_mv_t mv, int col0, int ncols, const double *host, long long ldh)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_range(mv, col0, ncols, "upload");
+    if (rc) return rc;
+    if (ncols == 0 || mv->rows == 0)
+        return RAILS_OK;
+    if (!host || ldh < mv->rows)
+        return rails::fail(RAILS_ERR_ARG, "upload: bad host block");
+    RAILS_CUDA_TRY(cudaMemcpy2DAsync(mv->data + (size_t)col0 * mv->ld, mv->ld * sizeof(double),
+                                     host, ldh * sizeof(double),
+                                     (size_t)mv->rows * sizeof(double), ncols,
+                                     cudaMemcpyHostToDevice, ctx().stream));
+    // pageable host memory may be reused by the caller right after return
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_download(rails_mv_t mv, int col0, int ncols, double *host, long long ldh)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_range(mv, col0, ncols, "download");
+    if (rc) return rc;
+    if (ncols == 0 || mv->rows == 0)
+        return RAILS_OK;
+    if (!host || ldh < mv->rows)
+        return rails::fail(RAILS_ERR_ARG, "download: bad host block");
+    RAILS_CUDA_TRY(cudaMemcpy2DAsync(host, ldh * sizeof(double),
+                                     mv->data + (size_t)col0 * mv->ld, mv->ld * sizeof(double),
+                                     (size_t)mv->rows * sizeof(double), ncols,
+                                     cudaMemcpyDeviceToHost, ctx().stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_get(rails_mv_t mv, long long row, int col, double *value)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_range(mv, col, 1, "get");
+    if (rc) return rc;
+    if (row < 0 || row >= mv->rows || !value)
+        return rails::fail(RAILS_ERR_ARG, "get: row %lld outside %lld", row, mv->rows);
+    RAILS_CUDA_TRY(cudaMemcpyAsync(value, mv->data + (size_t)col * mv->ld + row, sizeof(double),
+                                   cudaMemcpyDeviceToHost, ctx().stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_set(rails_mv_t mv, long long row, int col, double value)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_range(mv, col, 1, "set");
+    if (rc) return rc;
+    if (row < 0 || row >= mv->rows)
+        return rails::fail(RAILS_ERR_ARG, "set: row %lld outside %lld", row, mv->rows);
+    RAILS_CUDA_TRY(cudaMemcpyAsync(mv->data + (size_t)col * mv->ld + row, &value, sizeof(double),
+                                   cudaMemcpyHostToDevice, ctx().stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    return RAILS_OK;
+}

@@ -1,0 +1,347 @@
+// Tall-skinny inner products  out = X' Y  (a x b)  and the Gram-Schmidt chain.
+//
+// Replaces StlWrapper::dot (src/StlWrapper.cpp:394-412, dgemm 'T','N') and
+// EpetraMV::dot (src/Epetra_MultiVectorWrapper.cpp:418-438).  In the solver
+// these are k x 1 products (V'q, AV'q in resid_lanczos, the CGS2 passes) and
+// k x e / e x k projection blocks: 0.25 flop/B, i.e. a pure HBM stream of
+// 8 m (a + b) bytes.
+//
+// Kernel shape: the operand with FEW columns (<= BT per launch) is held in
+// registers for a tile of 512*RP rows; the operand with MANY columns is
+// streamed once, U columns (U*RP 128-bit loads per thread) in flight.  Each
+// column's tile contribution is reduced inside the warp with shuffles and
+// accumulated in a per-warp shared-memory slice, so there are no atomics and
+// the summation order is fixed: row tiles are dealt round-robin to the
+// resident CTAs, a second kernel adds the per-CTA partials in CTA order.
+#include "internal.h"
+
+using rails::ctx;
+
+namespace rails
+{
+int scal_inv_norm_device(double *x, long long ld, long long rows, const double *d);
+}
+
+namespace
+{
+
+constexpr int DOT_THREADS = 256;
+constexpr int DOT_WARPS = DOT_THREADS / 32;
+// streamed columns handled per blockIdx.y: keeps the per-warp accumulators
+// at 64 KB of shared memory per CTA
+__host__ __device__ constexpr int dot_achunk(int bt) { return 1024 / bt; }
+
+template<bool FULL>
+__device__ __forceinline__ double2 load2(const double *__restrict__ p, long long r, long long rows)
+{
+    if (FULL)
+        return __ldg(reinterpret_cast<const double2 *>(p + r));
+    double2 v = make_double2(0.0, 0.0);
+    if (r < rows) v.x = __ldg(p + r);
+    if (r + 1 < rows) v.y = __ldg(p + r + 1);
+    return v;
+}
+
+template<int RP, int BT, int U, bool FULL>
+__device__ __forceinline__ void dot_tile(const double *__restrict__ X, long long ldx, int ac,
+                                         const double *__restrict__ Y, long long ldy,
+                                         long long rows, long long base, double *wacc, int lane)
+{
+    double2 yv[BT][RP];
+#pragma unroll
+    for (int t = 0; t < BT; ++t)
+#pragma unroll
+        for (int v = 0; v < RP; ++v)
+            yv[t][v] = load2<FULL>(Y + (size_t)t * ldy, base + v * 512, rows);
+
+    for (int j = 0; j < ac; j += U)
+    {
+        double2 xv[U][RP];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            // columns past the chunk re-read the last one; result discarded
+            const int jj = (j + u < ac) ? (j + u) : (ac - 1);
+#pragma unroll
+            for (int v = 0; v < RP; ++v)
+                xv[u][v] = load2<FULL>(X + (size_t)jj * ldx, base + v * 512, rows);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            double p[BT];
+#pragma unroll
+            for (int t = 0; t < BT; ++t)
+            {
+                double s = 0.0;
+#pragma unroll
+                for (int v = 0; v < RP; ++v)
+                {
+                    s = fma(xv[u][v].x, yv[t][v].x, s);
+                    s = fma(xv[u][v].y, yv[t][v].y, s);
+                }
+                p[t] = s;
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+                for (int t = 0; t < BT; ++t)
+                    p[t] += __shfl_xor_sync(0xffffffffu, p[t], off);
+            if (lane == 0 && j + u < ac)
+            {
+#pragma unroll
+                for (int t = 0; t < BT; ++t)
+                    wacc[(j + u) * BT + t] += p[t];
+            }
+        }
+    }
+}
+
+// partial[blockIdx.x][(j0 + j) * BT + t] = sum over this CTA's row tiles of
+// X[:, j0 + j] . Y[:, t]
+template<int RP, int BT, int U>
+__global__ void __launch_bounds__(DOT_THREADS)
+dot_kernel(const double *__restrict__ X, long long ldx, int a,
+           const double *__restrict__ Y, long long ldy, long long rows,
+           double *__restrict__ partial)
+{
+    extern __shared__ double sacc[];
+    constexpr int ACH = dot_achunk(BT);
+    const int j0 = blockIdx.y * ACH;
+    const int ac = min(ACH, a - j0);
+    const int nacc = ac * BT;
+    for (int i = threadIdx.x; i < nacc * DOT_WARPS; i += DOT_THREADS)
+        sacc[i] = 0.0;
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double *wacc = sacc + warp * nacc;
+    const double *Xc = X + (size_t)j0 * ldx;
+    constexpr long long TILE = 512LL * RP;
+    const long long ntiles = (rows + TILE - 1) / TILE;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+    {
+        const long long base = tile * TILE + 2 * threadIdx.x;
+        if ((tile + 1) * TILE <= rows)
+            dot_tile<RP, BT, U, true>(Xc, ldx, ac, Y, ldy, rows, base, wacc, lane);
+        else
+            dot_tile<RP, BT, U, false>(Xc, ldx, ac, Y, ldy, rows, base, wacc, lane);
+    }
+    __syncthreads();
+    double *out = partial + (size_t)blockIdx.x * ((size_t)a * BT) + (size_t)j0 * BT;
+    for (int i = threadIdx.x; i < nacc; i += DOT_THREADS)
+    {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < DOT_WARPS; ++w)
+            s += sacc[w * nacc + i];
+        out[i] = s;
+    }
+}
+
+// One warp per output entry: out = sum_b partial[b][idx], fixed order.
+// idx = j * bt + t maps to out[j * sj + (t0 + t) * st].
+__global__ void __launch_bounds__(256)
+dot_finish_kernel(const double *__restrict__ partial, int nblocks, int n, int bt, int t0,
+                  double *__restrict__ out, long long sj, long long st)
+{
+    const int idx = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (idx >= n) return;
+    const int lane = threadIdx.x & 31;
+    double s = 0.0;
+    for (int b = lane; b < nblocks; b += 32)
+        s += partial[(size_t)b * n + idx];
+    for (int off = 16; off > 0; off >>= 1)
+        s += __shfl_xor_sync(0xffffffffu, s, off);
+    if (lane == 0)
+    {
+        const int j = idx / bt, t = idx - j * bt;
+        out[(size_t)j * sj + (size_t)(t0 + t) * st] = s;
+    }
+}
+
+template<int RP, int BT, int U>
+int launch_dot(const double *X, long long ldx, int a, const double *Y, long long ldy,
+               long long rows, int t0, double *d_out, long long sj, long long st)
+{
+    rails::Context &c = ctx();
+    constexpr long long TILE = 512LL * RP;
+    long long ntiles = (rows + TILE - 1) / TILE;
+    if (ntiles < 1) ntiles = 1;
+    int nb = (int)std::min<long long>(ntiles, (long long)c.sm_count * 4);
+    int rc = rails::ensure_partial((size_t)nb * a * BT);
+    if (rc) return rc;
+    constexpr int ACH = dot_achunk(BT);
+    dim3 grid(nb, (a + ACH - 1) / ACH);
+    size_t smem = (size_t)std::min(a, ACH) * BT * DOT_WARPS * sizeof(double);
+    static bool attr_set = false;
+    if (!attr_set)
+    {
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(dot_kernel<RP, BT, U>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            ACH * BT * DOT_WARPS * (int)sizeof(double)));
+        attr_set = true;
+    }
+    auto kern = dot_kernel<RP, BT, U>;
+    RAILS_LAUNCH(kern, grid, DOT_THREADS, smem, X, ldx, a, Y, ldy, rows, c.d_partial);
+    RAILS_CHECK_LAUNCH();
+    int n = a * BT;
+    RAILS_LAUNCH(dot_finish_kernel, (n + 7) / 8, 256, 0, c.d_partial, nb, n, BT, t0, d_out, sj, st);
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
+}
+
+}
+
+namespace rails
+{
+
+// d_out (device, column-major a x b, leading dimension ldo) = X' Y over this
+// rank's rows, summed over ranks when asked.
+int dot_device(const double *X, long long ldx, int a, const double *Y, long long ldy, int b,
+               long long rows, double *d_out, int ldo, bool reduce_over_ranks)
+{
+    Context &c = ctx();
+    if (a == 0 || b == 0)
+        return RAILS_OK;
+    if (rows == 0)
+    {
+        RAILS_CUDA_TRY(cudaMemset2DAsync(d_out, (size_t)ldo * sizeof(double), 0,
+                                         (size_t)a * sizeof(double), b, c.stream));
+    }
+    else
+    {
+        // stream the operand with more columns (S), hold the other (H) in registers
+        const bool swap = b > a;
+        const double *S = swap ? Y : X, *H = swap ? X : Y;
+        const long long lds = swap ? ldy : ldx, ldh = swap ? ldx : ldy;
+        const int ns = swap ? b : a, nh = swap ? a : b;
+        // out(i, j): streamed column index moves with sj, held with st
+        const long long sj = swap ? ldo : 1, st = swap ? 1 : ldo;
+        int t = 0;
+        while (t < nh)
+        {
+            const int left = nh - t;
+            const double *Ht = H + (size_t)t * ldh;
+            int rc;
+            if (left >= 8)      { rc = launch_dot<1, 8, 4>(S, lds, ns, Ht, ldh, rows, t, d_out, sj, st); t += 8; }
+            else if (left >= 4) { rc = launch_dot<2, 4, 2>(S, lds, ns, Ht, ldh, rows, t, d_out, sj, st); t += 4; }
+            else if (left >= 2) { rc = launch_dot<4, 2, 2>(S, lds, ns, Ht, ldh, rows, t, d_out, sj, st); t += 2; }
+            else                { rc = launch_dot<4, 1, 4>(S, lds, ns, Ht, ldh, rows, t, d_out, sj, st); t += 1; }
+            if (rc) return rc;
+        }
+    }
+    if (reduce_over_ranks && c.comm)
+    {
+        if (ldo != a)
+            return fail(RAILS_ERR_ARG, "dot_device: rank reduction needs a compact result");
+        RAILS_NCCL_TRY(ncclAllReduce(d_out, d_out, (size_t)a * b, ncclDouble, ncclSum, c.comm, c.stream));
+    }
+    return RAILS_OK;
+}
+
+}
+
+namespace
+{
+
+int check_pair(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b, const char *what)
+{
+    if (!X || !Y)
+        return rails::fail(RAILS_ERR_ARG, "%s: null multivector", what);
+    if (xc0 < 0 || a < 0 || xc0 + a > X->cols || yc0 < 0 || b < 0 || yc0 + b > Y->cols)
+        return rails::fail(RAILS_ERR_ARG, "%s: column range outside capacity", what);
+    if (X->rows != Y->rows)
+        return rails::fail(RAILS_ERR_ARG, "%s: %lld vs %lld rows", what, X->rows, Y->rows);
+    return RAILS_OK;
+}
+
+}
+
+extern "C" int rails_mv_dot(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
+                            double *out, int ldo)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_pair(X, xc0, a, Y, yc0, b, "dot");
+    if (rc) return rc;
+    if (a == 0 || b == 0) return RAILS_OK;
+    if (!out || ldo < a)
+        return rails::fail(RAILS_ERR_ARG, "dot: bad result block");
+    rails::Context &c = ctx();
+    rc = rails::ensure_small((size_t)a * b);
+    if (rc) return rc;
+    const bool dist = X->flags == RAILS_MV_DISTRIBUTED && Y->flags == RAILS_MV_DISTRIBUTED;
+    rc = rails::dot_device(X->data + (size_t)xc0 * X->ld, X->ld, a, Y->data + (size_t)yc0 * Y->ld,
+                           Y->ld, b, X->rows, c.d_small, a, dist);
+    if (rc) return rc;
+    RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, (size_t)a * b * sizeof(double),
+                                   cudaMemcpyDeviceToHost, c.stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    for (int j = 0; j < b; ++j)
+        for (int i = 0; i < a; ++i)
+            out[i + (size_t)j * ldo] = c.h_small[i + (size_t)j * a];
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_dot_dev(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
+                                rails_mv_t Out, int oc0)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_pair(X, xc0, a, Y, yc0, b, "dot_dev");
+    if (rc) return rc;
+    if (!Out || oc0 < 0 || oc0 + b > Out->cols || Out->rows != a)
+        return rails::fail(RAILS_ERR_ARG, "dot_dev: result block must be %d x %d", a, b);
+    if (a == 0 || b == 0) return RAILS_OK;
+    rails::Context &c = ctx();
+    rc = rails::ensure_small((size_t)a * b);
+    if (rc) return rc;
+    const bool dist = X->flags == RAILS_MV_DISTRIBUTED && Y->flags == RAILS_MV_DISTRIBUTED;
+    rc = rails::dot_device(X->data + (size_t)xc0 * X->ld, X->ld, a, Y->data + (size_t)yc0 * Y->ld,
+                           Y->ld, b, X->rows, c.d_small, a, dist);
+    if (rc) return rc;
+    RAILS_CUDA_TRY(cudaMemcpy2DAsync(Out->data + (size_t)oc0 * Out->ld, Out->ld * sizeof(double),
+                                     c.d_small, (size_t)a * sizeof(double),
+                                     (size_t)a * sizeof(double), b, cudaMemcpyDeviceToDevice, c.stream));
+    return RAILS_OK;
+}
+
+// Column-wise CGS2 (StlWrapper::orthogonalize, src/StlWrapper.cpp:305-321):
+//   for i in [first, last]:  v = V(:, i);  v /= |v|;
+//       twice:  v -= V(:, 0:i-1) * (V(:, 0:i-1)' v);      v /= |v|
+// Every scalar (the squared norms, the k x 1 coefficient vectors) stays in
+// device memory between kernels; with a communicator the sums are all-reduced
+// on the same stream.  Nothing returns to the host.
+extern "C" int rails_mv_orthogonalize(rails_mv_t V, int col0, int first, int last)
+{
+    RAILS_REQUIRE_READY();
+    if (!V || col0 < 0 || first < 0 || last < first - 1 || col0 + last + 1 > V->cols)
+        return rails::fail(RAILS_ERR_ARG, "orthogonalize: bad column range");
+    rails::Context &c = ctx();
+    int rc = rails::ensure_small((size_t)last + 2);
+    if (rc) return rc;
+    const bool dist = V->flags == RAILS_MV_DISTRIBUTED;
+    double *base = V->data + (size_t)col0 * V->ld;
+    for (int i = first; i <= last; ++i)
+    {
+        double *v = base + (size_t)i * V->ld;
+        rc = rails::dot_device(v, V->ld, 1, v, V->ld, 1, V->rows, c.d_small, 1, dist);
+        if (rc) return rc;
+        rc = rails::scal_inv_norm_device(v, V->ld, V->rows, c.d_small);
+        if (rc) return rc;
+        if (i > 0)
+        {
+            for (int pass = 0; pass < 2; ++pass)
+            {
+                rc = rails::dot_device(base, V->ld, i, v, V->ld, 1, V->rows, c.d_small, i, dist);
+                if (rc) return rc;
+                rc = rails::gemm_device(base, V->ld, i, c.d_small, i, 1, -1.0, 1.0, v, V->ld, V->rows);
+                if (rc) return rc;
+            }
+        }
+        rc = rails::dot_device(v, V->ld, 1, v, V->ld, 1, V->rows, c.d_small, 1, dist);
+        if (rc) return rc;
+        rc = rails::scal_inv_norm_device(v, V->ld, V->rows, c.d_small);
+        if (rc) return rc;
+    }
+    return RAILS_OK;
+}

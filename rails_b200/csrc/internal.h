@@ -1,0 +1,141 @@
+// Internal declarations shared by the .cu files of librails_cuda.so.
+#ifndef RAILS_B200_INTERNAL_H
+#define RAILS_B200_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <atomic>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "rails_cuda.h"
+
+struct rails_mv_s
+{
+    double *data;
+    long long rows;   // local rows
+    long long ld;     // leading dimension, multiple of 16 doubles
+    int cols;         // capacity in columns
+    int flags;        // RAILS_MV_DISTRIBUTED / RAILS_MV_REPLICATED
+    size_t bytes;
+};
+
+struct rails_csr_s
+{
+    long long rows;          // local rows
+    long long global_rows;
+    long long global_cols;
+    long long row_offset;
+    long long nnz;
+    long long ncols_local;   // owned columns (= local rows of X)
+    // device arrays; column indices renumbered [owned | ghost]
+    int *rowptr;
+    int *colidx;
+    double *vals;
+    // row blocks for the staged kernel: block b covers rows
+    // [blk_row[b], blk_row[b+1])
+    int *blk_row;
+    int nblk;
+    int max_blk_nnz;
+    // halo plan (distributed only)
+    int nghost;                          // ghost rows of X needed here
+    std::vector<int> recv_count;         // per peer, ghost rows received
+    std::vector<int> send_count;         // per peer, owned rows sent
+    int *send_rows;                      // device: owned local row ids to pack
+    int nsend;
+    double *send_buf;                    // device staging, nsend x ncols
+    double *ghost_buf;                   // device, nghost x ncols
+    int halo_cols_cap;                   // columns the staging buffers hold
+    // host copy kept for the lazily built transpose
+    std::vector<int> h_rowptr, h_colidx;
+    std::vector<double> h_vals;
+    rails_csr_s *transposed;
+    size_t bytes;
+};
+
+namespace rails
+{
+
+struct Context
+{
+    bool ready = false;
+    int device = -1;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaStream_t comm_stream = nullptr;
+    // reduction workspace (device), small result staging (device + pinned host)
+    double *d_partial = nullptr;
+    size_t partial_cap = 0;       // doubles
+    double *d_small = nullptr;
+    size_t small_cap = 0;         // doubles
+    double *h_small = nullptr;    // pinned
+    double *d_coef = nullptr;     // uploaded coefficient blocks for gemm
+    size_t coef_cap = 0;
+    size_t coef_pos = 0;
+    double *h_ring = nullptr;     // pinned staging ring for small H2D operands
+    size_t ring_cap = 0;
+    size_t ring_pos = 0;
+    // communicator
+    ncclComm_t comm = nullptr;
+    int rank = 0;
+    int nranks = 1;
+    std::atomic<long long> launches{0};
+    std::atomic<long long> bytes_in_use{0};
+    std::vector<cudaEvent_t> events;
+    std::string last_error;
+};
+
+Context &ctx();
+int fail(int code, const char *fmt, ...);
+int ensure_partial(size_t doubles);
+int ensure_small(size_t doubles);
+// Copies a small host block (column-major k x c, ldc) into the pinned ring and
+// enqueues its upload; *d_out is a compact (ld = k) device copy that stays
+// valid until the ring wraps (thousands of calls later, guarded by a sync).
+int upload_small(const double *host, int k, int c, int ldc, const double **d_out);
+
+// device-side kernels callable across translation units
+int dot_device(const double *X, long long ldx, int a, const double *Y,
+               long long ldy, int b, long long rows, double *d_out, int ldo,
+               bool reduce_over_ranks);
+int gemm_device(const double *V, long long ldv, int k, const double *dC, int ldc,
+                int c, double alpha, double beta, double *Out, long long ldo,
+                long long rows);
+
+}
+
+#define RAILS_CUDA_TRY(expr)                                                   \
+    do {                                                                       \
+        cudaError_t e__ = (expr);                                              \
+        if (e__ != cudaSuccess)                                                \
+            return rails::fail(RAILS_ERR_CUDA, "%s:%d %s -> %s", __FILE__,     \
+                               __LINE__, #expr, cudaGetErrorString(e__));      \
+    } while (0)
+
+#define RAILS_NCCL_TRY(expr)                                                   \
+    do {                                                                       \
+        ncclResult_t r__ = (expr);                                             \
+        if (r__ != ncclSuccess)                                                \
+            return rails::fail(RAILS_ERR_CUDA, "%s:%d %s -> %s", __FILE__,     \
+                               __LINE__, #expr, ncclGetErrorString(r__));      \
+    } while (0)
+
+#define RAILS_REQUIRE_READY()                                                  \
+    do {                                                                       \
+        if (!rails::ctx().ready)                                               \
+            return rails::fail(RAILS_ERR_STATE,                                \
+                               "rails_cuda_init has not been called");         \
+    } while (0)
+
+// every kernel launch goes through this so gpu_launches is a real count
+#define RAILS_LAUNCH(kernel, grid, block, smem, ...)                           \
+    do {                                                                       \
+        kernel<<<(grid), (block), (smem), rails::ctx().stream>>>(__VA_ARGS__); \
+        rails::ctx().launches.fetch_add(1, std::memory_order_relaxed);         \
+    } while (0)
+
+#define RAILS_CHECK_LAUNCH() RAILS_CUDA_TRY(cudaGetLastError())
+
+#endif

@@ -1,0 +1,490 @@
+// CSR x tall-skinny multivector:  Y = op(A) X.
+//
+// Replaces EpetraOp::operator* (src/Epetra_OperatorWrapper.cpp:75-91 ->
+// Epetra_CrsMatrix::Apply, i.e. ghost import + row loop) and the dense
+// stand-in StlWrapper::operator* (src/StlWrapper.cpp:168-187) at
+// src/LyapunovSolver.hpp:146.  Algorithmic traffic:
+// 12 nnz + 4 (m+1) + 16 m e bytes; 1/6 flop per byte per column -> HBM bound.
+//
+// Kernel: rows are cut on the host into blocks of <= 256 rows and
+// <= SPMM_NNZ_CAP non-zeros.  A CTA first stages its block's values and column
+// indices into shared memory with fully coalesced loads (the CSR arrays are
+// read from HBM exactly once per call, whatever the number of columns e), then
+// each thread walks ONE row sequentially out of shared memory for EC columns
+// of X at a time.  Row sums are therefore accumulated in CSR order with a
+// separately rounded multiply and add, which makes the result bit-identical
+// to the scalar CPU loop y_i = sum_j a_ij x_j of the oracle.  Gathers from X
+// go through the read-only path; for stencil matrices neighbouring rows hit
+// the same lines and the rest is served by L2.
+//
+// Row partition (multi-GPU): columns are renumbered [owned | ghost] at
+// creation; ghost rows of X are packed by the owners and moved with grouped
+// ncclSend/ncclRecv over NVLink before the kernel reads them.
+#include "internal.h"
+
+#include <algorithm>
+#include <cstring>
+
+using rails::ctx;
+
+namespace
+{
+
+constexpr int SPMM_THREADS = 256;
+constexpr int SPMM_NNZ_CAP = 3072;      // 36 KB of shared memory per CTA
+
+template<int EC>
+__global__ void __launch_bounds__(SPMM_THREADS)
+spmm_kernel(const int *__restrict__ rowptr, const int *__restrict__ colidx,
+            const double *__restrict__ vals, const int *__restrict__ blk_row,
+            const double *__restrict__ X, long long ldx, long long nlocal,
+            const double *__restrict__ G, long long ldg,
+            double *__restrict__ Y, long long ldy, int ncols)
+{
+    __shared__ double sv[SPMM_NNZ_CAP];
+    __shared__ int sc[SPMM_NNZ_CAP];
+    __shared__ double red[SPMM_THREADS / 32];
+
+    const int r0 = blk_row[blockIdx.x], r1 = blk_row[blockIdx.x + 1];
+    const int p0 = rowptr[r0], p1 = rowptr[r1];
+    const int nnzb = p1 - p0;
+
+    if (nnzb <= SPMM_NNZ_CAP)
+    {
+        for (int i = threadIdx.x; i < nnzb; i += SPMM_THREADS)
+        {
+            sv[i] = __ldg(vals + p0 + i);
+            sc[i] = __ldg(colidx + p0 + i);
+        }
+        __syncthreads();
+        const int row = r0 + threadIdx.x;
+        if (row >= r1)
+            return;
+        const int a = rowptr[row] - p0, e = rowptr[row + 1] - p0;
+        for (int c0 = 0; c0 < ncols; c0 += EC)
+        {
+            double acc[EC];
+#pragma unroll
+            for (int t = 0; t < EC; ++t)
+                acc[t] = 0.0;
+            for (int p = a; p < e; ++p)
+            {
+                const int col = sc[p];
+                const double v = sv[p];
+                const double *xp;
+                long long ld;
+                if (col < nlocal) { xp = X + col; ld = ldx; }
+                else              { xp = G + (col - nlocal); ld = ldg; }
+#pragma unroll
+                for (int t = 0; t < EC; ++t)
+                    if (EC == 1 || c0 + t < ncols)
+                        acc[t] = __dadd_rn(acc[t], __dmul_rn(v, __ldg(xp + (size_t)(c0 + t) * ld)));
+            }
+#pragma unroll
+            for (int t = 0; t < EC; ++t)
+                if (EC == 1 || c0 + t < ncols)
+                    Y[row + (size_t)(c0 + t) * ldy] = acc[t];
+        }
+    }
+    else
+    {
+        // a single row longer than the staging buffer: whole CTA on one row
+        const int row = r0;
+        for (int c = 0; c < ncols; ++c)
+        {
+            double s = 0.0;
+            for (int p = p0 + threadIdx.x; p < p1; p += SPMM_THREADS)
+            {
+                const int col = __ldg(colidx + p);
+                const double x = col < nlocal ? __ldg(X + col + (size_t)c * ldx)
+                                              : __ldg(G + (col - nlocal) + (size_t)c * ldg);
+                s = fma(__ldg(vals + p), x, s);
+            }
+            for (int off = 16; off > 0; off >>= 1)
+                s += __shfl_xor_sync(0xffffffffu, s, off);
+            __syncthreads();
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+            __syncthreads();
+            if (threadIdx.x == 0)
+            {
+                double tot = 0.0;
+                for (int w = 0; w < SPMM_THREADS / 32; ++w) tot += red[w];
+                Y[row + (size_t)c * ldy] = tot;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+pack_rows_kernel(const int *__restrict__ rows, int n, const double *__restrict__ X, long long ldx,
+                 double *__restrict__ buf, long long ldb)
+{
+    const int c = blockIdx.y;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256)
+        buf[i + (size_t)c * ldb] = X[rows[i] + (size_t)c * ldx];
+}
+
+void free_csr(rails_csr_s *A)
+{
+    if (!A) return;
+    if (A->transposed) free_csr(A->transposed);
+    if (ctx().ready)
+    {
+        cudaFree(A->rowptr); cudaFree(A->colidx); cudaFree(A->vals); cudaFree(A->blk_row);
+        if (A->send_rows) cudaFree(A->send_rows);
+        if (A->send_buf) cudaFree(A->send_buf);
+        if (A->ghost_buf) cudaFree(A->ghost_buf);
+        ctx().bytes_in_use.fetch_sub((long long)A->bytes);
+    }
+    delete A;
+}
+
+// uploads CSR arrays whose column indices are already local ([owned|ghost])
+int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const double *vals)
+{
+    const long long rows = A->rows, nnz = A->nnz;
+    // row blocks
+    std::vector<int> blk;
+    blk.push_back(0);
+    int maxnnz = 0;
+    long long r = 0;
+    while (r < rows)
+    {
+        long long end = std::min(rows, r + SPMM_THREADS);
+        // shrink until the block fits the staging buffer (keep >= 1 row)
+        while (end > r + 1 && rowptr[end] - rowptr[r] > SPMM_NNZ_CAP)
+            --end;
+        maxnnz = std::max(maxnnz, rowptr[end] - rowptr[r]);
+        blk.push_back((int)end);
+        r = end;
+    }
+    A->nblk = (int)blk.size() - 1;
+    A->max_blk_nnz = maxnnz;
+    size_t b_rp = (size_t)(rows + 1) * sizeof(int), b_ci = (size_t)std::max<long long>(nnz, 1) * sizeof(int),
+           b_v = (size_t)std::max<long long>(nnz, 1) * sizeof(double), b_blk = blk.size() * sizeof(int);
+    RAILS_CUDA_TRY(cudaMalloc(&A->rowptr, b_rp));
+    RAILS_CUDA_TRY(cudaMalloc(&A->colidx, b_ci));
+    RAILS_CUDA_TRY(cudaMalloc(&A->vals, b_v));
+    RAILS_CUDA_TRY(cudaMalloc(&A->blk_row, b_blk));
+    A->bytes += b_rp + b_ci + b_v + b_blk;
+    ctx().bytes_in_use.fetch_add((long long)(b_rp + b_ci + b_v + b_blk));
+    cudaStream_t s = ctx().stream;
+    RAILS_CUDA_TRY(cudaMemcpyAsync(A->rowptr, rowptr, b_rp, cudaMemcpyHostToDevice, s));
+    if (nnz)
+    {
+        RAILS_CUDA_TRY(cudaMemcpyAsync(A->colidx, colidx, (size_t)nnz * sizeof(int), cudaMemcpyHostToDevice, s));
+        RAILS_CUDA_TRY(cudaMemcpyAsync(A->vals, vals, (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice, s));
+    }
+    RAILS_CUDA_TRY(cudaMemcpyAsync(A->blk_row, blk.data(), b_blk, cudaMemcpyHostToDevice, s));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(s));
+    return RAILS_OK;
+}
+
+int owner_of(long long gcol, long long m, int P)
+{
+    long long base = m / P, rem = m % P;
+    long long split = rem * (base + 1);
+    if (gcol < split) return (int)(gcol / (base + 1));
+    return (int)(rem + (gcol - split) / std::max<long long>(base, 1));
+}
+
+int ensure_halo_cols(rails_csr_s *A, int ncols)
+{
+    if (ncols <= A->halo_cols_cap) return RAILS_OK;
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    if (A->send_buf) { RAILS_CUDA_TRY(cudaFree(A->send_buf)); A->send_buf = nullptr; }
+    if (A->ghost_buf) { RAILS_CUDA_TRY(cudaFree(A->ghost_buf)); A->ghost_buf = nullptr; }
+    if (A->nsend) RAILS_CUDA_TRY(cudaMalloc(&A->send_buf, (size_t)A->nsend * ncols * sizeof(double)));
+    if (A->nghost) RAILS_CUDA_TRY(cudaMalloc(&A->ghost_buf, (size_t)A->nghost * ncols * sizeof(double)));
+    A->halo_cols_cap = ncols;
+    return RAILS_OK;
+}
+
+int halo_exchange(rails_csr_s *A, const double *X, long long ldx, int ncols)
+{
+    rails::Context &c = ctx();
+    int rc = ensure_halo_cols(A, ncols);
+    if (rc) return rc;
+    if (A->nsend)
+    {
+        dim3 grid(std::min((A->nsend + 255) / 256, c.sm_count * 4), ncols);
+        RAILS_LAUNCH(pack_rows_kernel, grid, 256, 0, A->send_rows, A->nsend, X, ldx, A->send_buf,
+                     (long long)A->nsend);
+        RAILS_CHECK_LAUNCH();
+    }
+    RAILS_NCCL_TRY(ncclGroupStart());
+    long long soff = 0, goff = 0;
+    for (int p = 0; p < c.nranks; ++p)
+    {
+        for (int col = 0; col < ncols; ++col)
+        {
+            if (A->send_count[p])
+                RAILS_NCCL_TRY(ncclSend(A->send_buf + soff + (size_t)col * A->nsend, A->send_count[p],
+                                        ncclDouble, p, c.comm, c.stream));
+            if (A->recv_count[p])
+                RAILS_NCCL_TRY(ncclRecv(A->ghost_buf + goff + (size_t)col * A->nghost, A->recv_count[p],
+                                        ncclDouble, p, c.comm, c.stream));
+        }
+        soff += A->send_count[p];
+        goff += A->recv_count[p];
+    }
+    RAILS_NCCL_TRY(ncclGroupEnd());
+    return RAILS_OK;
+}
+
+int launch_spmm(rails_csr_s *A, const double *X, long long ldx, int ncols, double *Y, long long ldy)
+{
+    if (A->rows == 0 || ncols == 0) return RAILS_OK;
+    const double *G = A->ghost_buf;
+    const long long ldg = A->nghost;
+    if (ncols >= 4)
+        RAILS_LAUNCH(spmm_kernel<4>, A->nblk, SPMM_THREADS, 0, A->rowptr, A->colidx, A->vals, A->blk_row,
+                     X, ldx, A->ncols_local, G, ldg, Y, ldy, ncols);
+    else if (ncols >= 2)
+        RAILS_LAUNCH(spmm_kernel<2>, A->nblk, SPMM_THREADS, 0, A->rowptr, A->colidx, A->vals, A->blk_row,
+                     X, ldx, A->ncols_local, G, ldg, Y, ldy, ncols);
+    else
+        RAILS_LAUNCH(spmm_kernel<1>, A->nblk, SPMM_THREADS, 0, A->rowptr, A->colidx, A->vals, A->blk_row,
+                     X, ldx, A->ncols_local, G, ldg, Y, ldy, ncols);
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
+}
+
+}
+
+extern "C" int rails_csr_create(long long rows, long long global_rows, long long global_cols,
+                                long long row_offset, const int *rowptr, const int *colidx,
+                                const double *vals, rails_csr_t *out)
+{
+    RAILS_REQUIRE_READY();
+    rails::Context &c = ctx();
+    if (rows < 0 || !rowptr || !out || rows >= (1LL << 31) || global_cols >= (1LL << 31))
+        return rails::fail(RAILS_ERR_ARG, "csr_create: bad sizes");
+    const long long nnz = rowptr[rows];
+    if (nnz < 0 || (nnz > 0 && (!colidx || !vals)))
+        return rails::fail(RAILS_ERR_ARG, "csr_create: bad arrays");
+    const bool dist = c.nranks > 1 && rows != global_rows;
+    if (dist && global_rows != global_cols)
+        return rails::fail(RAILS_ERR_ARG, "csr_create: a row-partitioned operator must be square");
+
+    rails_csr_s *A = new rails_csr_s();
+    A->rows = rows; A->global_rows = global_rows; A->global_cols = global_cols;
+    A->row_offset = row_offset; A->nnz = nnz;
+    A->rowptr = A->colidx = A->blk_row = nullptr; A->vals = nullptr;
+    A->send_rows = nullptr; A->send_buf = A->ghost_buf = nullptr;
+    A->nghost = A->nsend = 0; A->halo_cols_cap = 0; A->transposed = nullptr; A->bytes = 0;
+    A->recv_count.assign(c.nranks, 0);
+    A->send_count.assign(c.nranks, 0);
+
+    int rc;
+    if (!dist)
+    {
+        A->ncols_local = global_cols;
+        for (long long p = 0; p < nnz; ++p)
+            if (colidx[p] < 0 || colidx[p] >= global_cols)
+            {
+                delete A;
+                return rails::fail(RAILS_ERR_ARG, "csr_create: column %d out of range", colidx[p]);
+            }
+        // kept for a lazily built transpose (B as an Operator)
+        A->h_rowptr.assign(rowptr, rowptr + rows + 1);
+        A->h_colidx.assign(colidx, colidx + nnz);
+        A->h_vals.assign(vals, vals + nnz);
+        rc = upload_csr(A, rowptr, colidx, vals);
+        if (rc) { free_csr(A); return rc; }
+        *out = A;
+        return RAILS_OK;
+    }
+
+    // ---- row-partitioned: renumber columns [owned | ghost], build halo plan
+    A->ncols_local = rows;
+    std::vector<int> ghosts;
+    for (long long p = 0; p < nnz; ++p)
+    {
+        long long g = colidx[p];
+        if (g < 0 || g >= global_cols)
+        {
+            delete A;
+            return rails::fail(RAILS_ERR_ARG, "csr_create: column %lld out of range", g);
+        }
+        if (g < row_offset || g >= row_offset + rows)
+            ghosts.push_back((int)g);
+    }
+    std::sort(ghosts.begin(), ghosts.end());
+    ghosts.erase(std::unique(ghosts.begin(), ghosts.end()), ghosts.end());
+    A->nghost = (int)ghosts.size();
+    std::vector<int> lcol(nnz);
+    for (long long p = 0; p < nnz; ++p)
+    {
+        long long g = colidx[p];
+        if (g >= row_offset && g < row_offset + rows)
+            lcol[p] = (int)(g - row_offset);
+        else
+            lcol[p] = (int)(rows + (std::lower_bound(ghosts.begin(), ghosts.end(), (int)g) - ghosts.begin()));
+    }
+    rc = upload_csr(A, rowptr, lcol.data(), vals);
+    if (rc) { free_csr(A); return rc; }
+
+    const int P = c.nranks;
+    std::vector<int> need(P, 0);
+    std::vector<int> ghost_local(ghosts.size());
+    for (size_t i = 0; i < ghosts.size(); ++i)
+    {
+        int p = owner_of(ghosts[i], global_rows, P);
+        need[p]++;
+        long long b, e;
+        rails_partition_rows(global_rows, P, p, &b, &e);
+        ghost_local[i] = (int)(ghosts[i] - b);       // row id in the owner's numbering
+    }
+    A->recv_count = need;
+    // need matrix: all[r * P + p] = rows rank r needs from rank p
+    int *d_all = nullptr, *d_ids = nullptr;
+    RAILS_CUDA_TRY(cudaMalloc(&d_all, (size_t)P * P * sizeof(int)));
+    RAILS_CUDA_TRY(cudaMemcpyAsync(d_all + (size_t)c.rank * P, need.data(), P * sizeof(int),
+                                   cudaMemcpyHostToDevice, c.stream));
+    RAILS_NCCL_TRY(ncclAllGather(d_all + (size_t)c.rank * P, d_all, P, ncclInt, c.comm, c.stream));
+    std::vector<int> all((size_t)P * P);
+    RAILS_CUDA_TRY(cudaMemcpyAsync(all.data(), d_all, all.size() * sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    for (int p = 0; p < P; ++p)
+    {
+        A->send_count[p] = all[(size_t)p * P + c.rank];
+        A->nsend += A->send_count[p];
+    }
+    RAILS_CUDA_TRY(cudaMalloc(&d_ids, std::max<size_t>(ghost_local.size(), 1) * sizeof(int)));
+    RAILS_CUDA_TRY(cudaMalloc(&A->send_rows, std::max<size_t>(A->nsend, 1) * sizeof(int)));
+    if (!ghost_local.empty())
+        RAILS_CUDA_TRY(cudaMemcpyAsync(d_ids, ghost_local.data(), ghost_local.size() * sizeof(int),
+                                       cudaMemcpyHostToDevice, c.stream));
+    RAILS_NCCL_TRY(ncclGroupStart());
+    {
+        long long goff = 0, soff = 0;
+        for (int p = 0; p < P; ++p)
+        {
+            if (need[p])
+                RAILS_NCCL_TRY(ncclSend(d_ids + goff, need[p], ncclInt, p, c.comm, c.stream));
+            if (A->send_count[p])
+                RAILS_NCCL_TRY(ncclRecv(A->send_rows + soff, A->send_count[p], ncclInt, p, c.comm, c.stream));
+            goff += need[p];
+            soff += A->send_count[p];
+        }
+    }
+    RAILS_NCCL_TRY(ncclGroupEnd());
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    cudaFree(d_all);
+    cudaFree(d_ids);
+    *out = A;
+    return RAILS_OK;
+}
+
+extern "C" int rails_csr_free(rails_csr_t A)
+{
+    free_csr(A);
+    return RAILS_OK;
+}
+
+extern "C" long long rails_csr_rows(rails_csr_t A) { return A ? A->rows : -1; }
+extern "C" long long rails_csr_nnz(rails_csr_t A) { return A ? A->nnz : -1; }
+
+namespace
+{
+
+int build_transpose(rails_csr_s *A)
+{
+    if (A->transposed) return RAILS_OK;
+    if (A->h_rowptr.empty())
+        return rails::fail(RAILS_ERR_ARG, "transposed apply is not available on a row-partitioned operator");
+    const long long m = A->rows, n = A->global_cols, nnz = A->nnz;
+    std::vector<int> rp(n + 1, 0), ci(nnz);
+    std::vector<double> v(nnz);
+    for (long long p = 0; p < nnz; ++p) rp[A->h_colidx[p] + 1]++;
+    for (long long j = 0; j < n; ++j) rp[j + 1] += rp[j];
+    std::vector<int> next(rp.begin(), rp.end() - 1);
+    for (long long i = 0; i < m; ++i)
+        for (int p = A->h_rowptr[i]; p < A->h_rowptr[i + 1]; ++p)
+        {
+            int q = next[A->h_colidx[p]]++;
+            ci[q] = (int)i;
+            v[q] = A->h_vals[p];
+        }
+    rails_csr_s *T = new rails_csr_s();
+    T->rows = n; T->global_rows = n; T->global_cols = m; T->row_offset = 0; T->nnz = nnz;
+    T->ncols_local = m;
+    T->rowptr = T->colidx = T->blk_row = nullptr; T->vals = nullptr;
+    T->send_rows = nullptr; T->send_buf = T->ghost_buf = nullptr;
+    T->nghost = T->nsend = 0; T->halo_cols_cap = 0; T->transposed = nullptr; T->bytes = 0;
+    int rc = upload_csr(T, rp.data(), ci.data(), v.data());
+    if (rc) { free_csr(T); return rc; }
+    A->transposed = T;
+    return RAILS_OK;
+}
+
+}
+
+extern "C" int rails_csr_spmm(rails_csr_t A, int trans, rails_mv_t X, int xc0, int ncols,
+                              rails_mv_t Y, int yc0)
+{
+    RAILS_REQUIRE_READY();
+    if (!A || !X || !Y)
+        return rails::fail(RAILS_ERR_ARG, "spmm: null handle");
+    if (xc0 < 0 || ncols < 0 || xc0 + ncols > X->cols || yc0 < 0 || yc0 + ncols > Y->cols)
+        return rails::fail(RAILS_ERR_ARG, "spmm: column range outside capacity");
+    if (X->data == Y->data)
+        return rails::fail(RAILS_ERR_ARG, "spmm: X and Y must be different buffers");
+    rails_csr_s *Op = A;
+    if (trans)
+    {
+        int rc = build_transpose(A);
+        if (rc) return rc;
+        Op = A->transposed;
+    }
+    if (X->rows != Op->ncols_local || Y->rows != Op->rows)
+        return rails::fail(RAILS_ERR_ARG, "spmm: operator %lld x %lld applied to %lld rows -> %lld rows",
+                           Op->rows, Op->ncols_local, X->rows, Y->rows);
+    const double *Xd = X->data + (size_t)xc0 * X->ld;
+    if (Op->nghost || Op->nsend)
+    {
+        int rc = halo_exchange(Op, Xd, X->ld, ncols);
+        if (rc) return rc;
+    }
+    return launch_spmm(Op, Xd, X->ld, ncols, Y->data + (size_t)yc0 * Y->ld, Y->ld);
+}
+
+// sqrt(lambda_max(A'A)) by power iteration (EpetraOp::norm forms A'A and
+// asks an eigensolver for the largest eigenvalue, :115-145).
+extern "C" int rails_csr_norm2(rails_csr_t A, double *out)
+{
+    RAILS_REQUIRE_READY();
+    if (!A || !out)
+        return rails::fail(RAILS_ERR_ARG, "csr_norm2: null argument");
+    int rc = build_transpose(A);
+    if (rc) return rc;
+    rails_mv_t x = nullptr, y = nullptr;
+    rc = rails_mv_alloc(A->ncols_local, 1, RAILS_MV_REPLICATED, &x);
+    if (rc) return rc;
+    rc = rails_mv_alloc(A->rows, 1, RAILS_MV_REPLICATED, &y);
+    if (rc) { rails_mv_free(x); return rc; }
+    rails_mv_random(x, 0, 1, 0, 12345u);
+    double lambda = 0.0, prev = -1.0;
+    for (int it = 0; it < 1000; ++it)
+    {
+        double nx = 0.0;
+        rc = rails_mv_dot(x, 0, 1, x, 0, 1, &nx, 1);
+        if (rc) break;
+        if (nx == 0.0) { lambda = 0.0; break; }
+        rails_mv_scal(x, 0, 1, 1.0 / sqrt(nx));
+        rc = rails_csr_spmm(A, 0, x, 0, 1, y, 0);
+        if (rc) break;
+        rc = rails_mv_dot(y, 0, 1, y, 0, 1, &lambda, 1);   // |A x|^2 = x'A'A x
+        if (rc) break;
+        rc = rails_csr_spmm(A, 1, y, 0, 1, x, 0);
+        if (rc) break;
+        if (fabs(lambda - prev) <= 1e-14 * fabs(lambda)) break;
+        prev = lambda;
+    }
+    rails_mv_free(x);
+    rails_mv_free(y);
+    if (rc) return rc;
+    *out = sqrt(lambda);
+    return RAILS_OK;
+}

@@ -1,0 +1,109 @@
+"""Synthetic inputs for the RAILS hot path.
+
+The reference has no C++ generators; MATLAB's `laplacian2`
+(/root/reference/matlab/test/test_Laplace.m:14-21) fixes the sign/scale
+convention used here: diagonal -2*dim, neighbours +1, no 1/h^2 scaling.
+All matrices are CSR with int32 indices (the reference uses `int`
+everywhere) and columns sorted inside each row.
+
+Row numbering: x fastest, r = i + g*(j + g*l).  A contiguous block of rows is
+therefore a slab along the slowest index, which is what the Epetra-style
+linear row map hands each GPU.
+"""
+import numpy as np
+
+
+def _stencil_csr(g, dim, diag, lo, hi, row_begin=0, row_end=None):
+    """CSR rows [row_begin, row_end) of a constant-coefficient stencil.
+
+    lo[d] / hi[d] are the coefficients of the neighbour at -1 / +1 along
+    dimension d (Dirichlet boundaries: missing neighbours are dropped).
+    Column indices are GLOBAL.  Returns (rowptr, colidx, vals).
+    """
+    m = g ** dim
+    if row_end is None:
+        row_end = m
+    rows = np.arange(row_begin, row_end, dtype=np.int64)
+    nloc = rows.size
+    coords = []
+    r = rows.copy()
+    for _ in range(dim):
+        coords.append(r % g)
+        r //= g
+    # candidate entries in ascending column order:
+    # -g^(dim-1) ... -g, -1, 0, +1, +g ... +g^(dim-1)
+    offs, coefs, valid = [], [], []
+    for d in reversed(range(dim)):
+        offs.append(-(g ** d)); coefs.append(lo[d]); valid.append(coords[d] > 0)
+    offs.append(0); coefs.append(diag); valid.append(np.ones(nloc, dtype=bool))
+    for d in range(dim):
+        offs.append(g ** d); coefs.append(hi[d]); valid.append(coords[d] < g - 1)
+    valid = np.stack(valid, axis=1)                       # nloc x nst
+    counts = valid.sum(axis=1)
+    rowptr = np.zeros(nloc + 1, dtype=np.int64)
+    np.cumsum(counts, out=rowptr[1:])
+    cols = rows[:, None] + np.asarray(offs, dtype=np.int64)[None, :]
+    vals = np.broadcast_to(np.asarray(coefs, dtype=np.float64)[None, :], cols.shape)
+    colidx = cols[valid].astype(np.int32)
+    v = np.ascontiguousarray(vals[valid], dtype=np.float64)
+    if rowptr[-1] >= 2 ** 31:
+        raise ValueError("nnz exceeds int32 range for one partition")
+    return rowptr.astype(np.int32), colidx, v
+
+
+def laplacian(g, dim, row_begin=0, row_end=None):
+    """2-D 5-point / 3-D 7-point Laplacian, diag -2*dim, neighbours +1."""
+    return _stencil_csr(g, dim, -2.0 * dim, [1.0] * dim, [1.0] * dim,
+                        row_begin, row_end)
+
+
+def convection_diffusion(g, dim=3, peclet=0.5, row_begin=0, row_end=None):
+    """Laplacian + first-order upwind convection, velocity (1,..,1).
+
+    diag = -2*dim - dim*peclet, upwind (-1) neighbours +1+peclet, downwind +1
+    (SURVEY.md §8(d)): nonsymmetric, spectrum in the open left half-plane.
+    """
+    return _stencil_csr(g, dim, -2.0 * dim - dim * peclet,
+                        [1.0 + peclet] * dim, [1.0] * dim, row_begin, row_end)
+
+
+def shift_diagonal(rowptr, colidx, vals, delta, row_begin=0):
+    """A + delta*I on a row block (continuation step of config C5)."""
+    out = vals.copy()
+    nloc = rowptr.size - 1
+    rows = np.repeat(np.arange(row_begin, row_begin + nloc, dtype=np.int64),
+                     np.diff(rowptr))
+    out[colidx.astype(np.int64) == rows] += delta
+    return out
+
+
+def partition_rows(m, nranks, rank):
+    """Epetra_Map(m, 0, comm) linear map: first m % P ranks get one more row."""
+    base, rem = divmod(m, nranks)
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+CONFIGS = {
+    # name: (kind, g, dim, n_b, parameter dict)   -- SURVEY.md §8(d)
+    "C1": ("laplacian", 64, 2, 1, {"Tolerance": 1e-4, "Expand size": 1,
+                                   "Lanczos iterations": 10}),
+    "C2": ("laplacian", 1024, 2, 4, {"Tolerance": 1e-4, "Restart size": 200,
+                                     "Reduced size": 100, "Expand size": 4,
+                                     "Lanczos iterations": 20,
+                                     "Restart iterations": -1}),
+    "C3": ("laplacian", 256, 3, 1, {"Tolerance": 1e-4, "Expand size": 1,
+                                    "Lanczos iterations": 10}),
+    "C4": ("convdiff", 256, 3, 16, {"Tolerance": 1e-4, "Expand size": 16,
+                                    "Lanczos iterations": 40}),
+    "C5": ("laplacian", 512, 3, 1, {"Tolerance": 1e-4, "Expand size": 1,
+                                    "Lanczos iterations": 10}),
+}
+
+
+def build(kind, g, dim, row_begin=0, row_end=None):
+    if kind == "laplacian":
+        return laplacian(g, dim, row_begin, row_end)
+    if kind == "convdiff":
+        return convection_diffusion(g, dim, 0.5, row_begin, row_end)
+    raise ValueError(kind)

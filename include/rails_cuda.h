@@ -105,6 +105,13 @@ int rails_mv_fill(rails_mv_t mv, int col0, int ncols, double value);     /* = do
 int rails_mv_scal(rails_mv_t mv, int col0, int ncols, double alpha);     /* *=, /=   :131-145 */
 /* y[:, yc0..] += alpha * x[:, xc0..]                    (+=, -= :147-161) */
 int rails_mv_axpy(rails_mv_t y, int yc0, double alpha, rails_mv_t x, int xc0, int ncols);
+/* dst[:, dcol..] = alpha * src[:, scol..]: the scaled copy that
+ * `double * MultiVector` returns (:481-487) */
+int rails_mv_scaled_copy(rails_mv_t dst, int dcol, double alpha, rails_mv_t src, int scol, int ncols);
+/* y += sign * round(alpha * x), sign = +1 or -1: `y -= alpha * x` of
+ * resid_lanczos (src/LyapunovSolver.hpp:411-413) in one pass, with the
+ * product rounded before the add exactly as the scaled temporary would be */
+int rails_mv_add_scaled(rails_mv_t y, int yc0, double sign, double alpha, rails_mv_t x, int xc0, int ncols);
 /* max_i sum_j |x_ij| over this rank's rows, then max over ranks (:291-303) */
 int rails_mv_norm_inf(rails_mv_t mv, int col0, int ncols, double *out);
 

@@ -126,3 +126,73 @@ extern "C" void ref_stl_orthogonalize(int m, int n, double *X)
         for (int i = 0; i < m; ++i)
             X[i + (size_t)j * m] = V(i, j);
 }
+
+// ---------------------------------------------------------------------------
+// The PRODUCT's solver loop (rails_b200/host/RailsSolver.hpp) instantiated
+// with the reference's StlWrapper for all three concepts.  Same backend, same
+// operation order => must reproduce ref_stl_solve bit for bit; this is how the
+// shipped loop is pinned to the reference loop (tests/test_solver_loop.py).
+#include "RailsSolver.hpp"
+
+extern "C" int b200loop_stl_solve(
+    int m, const int *rowptr, const int *colidx, const double *vals,
+    int n_b, const double *B_in, unsigned seed,
+    int nparams, const char *const *keys, const double *pvals,
+    int hist_cap, double *hist_abs, double *hist_rel, int *hist_len,
+    int *k_out, int v_cap_cols, double *V_out, double *T_out,
+    double *seconds)
+{
+    std::srand(seed);
+
+    StlWrapper A(m, m);
+    A = 0.0;
+    for (int i = 0; i < m; ++i)
+        for (int p = rowptr[i]; p < rowptr[i + 1]; ++p)
+            A(i, colidx[p]) = vals[p];
+
+    StlWrapper B(m, n_b);
+    if (B_in)
+    {
+        for (int j = 0; j < n_b; ++j)
+            for (int i = 0; i < m; ++i)
+                B(i, j) = B_in[i + (size_t)j * m];
+    }
+    else
+        B.random();
+
+    RAILS::b200::Solver<StlWrapper, StlWrapper, StlWrapper> solver(A, B, B);
+    rails_oracle::ParameterList params(nparams, keys, pvals);
+    int ret = solver.set_parameters(params);
+    if (ret)
+        return 100 + ret;
+    solver.set_verbose(false);
+
+    StlWrapper V(m, 1);
+    StlWrapper T;
+    auto t0 = std::chrono::steady_clock::now();
+    ret = solver.solve(V, T);
+    if (seconds)
+        *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+
+    auto const &h = solver.history();
+    if (hist_len)
+        *hist_len = (int)h.size();
+    for (int i = 0; i < std::min((int)h.size(), hist_cap); ++i)
+    {
+        if (hist_abs) hist_abs[i] = h[i].residual;
+        if (hist_rel) hist_rel[i] = h[i].relative;
+    }
+    int k = V.N();
+    if (k_out)
+        *k_out = k;
+    if (V_out && T_out && k <= v_cap_cols)
+    {
+        for (int j = 0; j < k; ++j)
+            for (int i = 0; i < m; ++i)
+                V_out[i + (size_t)j * m] = V(i, j);
+        for (int j = 0; j < k; ++j)
+            for (int i = 0; i < k; ++i)
+                T_out[i + (size_t)j * v_cap_cols] = T(i, j);
+    }
+    return ret;
+}

@@ -1,0 +1,202 @@
+"""ctypes bindings of the product libraries (no torch, no oracle).
+
+    cuda  -> librails_cuda.so : the C ABI of include/rails_cuda.h
+    host  -> librails_host.so : rails_host_solve (solver loop over the CUDA
+                                wrapper classes)
+
+Loading fails loudly when the libraries have not been built
+(`python -m rails_b200.build`); there is no Python or CPU stand-in.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+c_double_p = ctypes.POINTER(ctypes.c_double)
+c_int_p = ctypes.POINTER(ctypes.c_int)
+
+
+def dptr(a):
+    return None if a is None else a.ctypes.data_as(c_double_p)
+
+
+def iptr(a):
+    return None if a is None else a.ctypes.data_as(c_int_p)
+
+
+_cuda = None
+_host = None
+
+
+def cuda():
+    global _cuda
+    if _cuda is None:
+        path = os.path.join(HERE, "librails_cuda.so")
+        if not os.path.exists(path):
+            raise RuntimeError("librails_cuda.so is not built: run `python -m rails_b200.build`")
+        lib = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        _declare_cuda(lib)
+        _cuda = lib
+    return _cuda
+
+
+def host():
+    global _host
+    if _host is None:
+        cuda()
+        path = os.path.join(HERE, "librails_host.so")
+        if not os.path.exists(path):
+            raise RuntimeError("librails_host.so is not built: run `python -m rails_b200.build`")
+        lib = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        lib.rails_host_last_sections.restype = ctypes.c_char_p
+        _host = lib
+    return _host
+
+
+# every symbol include/rails_cuda.h declares: (name, restype, argtypes)
+I, LL, D, P = ctypes.c_int, ctypes.c_longlong, ctypes.c_double, ctypes.c_void_p
+CUDA_SYMBOLS = [
+    ("rails_cuda_init", I, [I]),
+    ("rails_cuda_finalize", I, []),
+    ("rails_cuda_is_initialized", I, []),
+    ("rails_cuda_sync", I, []),
+    ("rails_cuda_last_error", ctypes.c_char_p, []),
+    ("rails_cuda_kernel_launches", LL, []),
+    ("rails_cuda_bytes_in_use", LL, []),
+    ("rails_cuda_event_record", I, [I]),
+    ("rails_cuda_event_elapsed_ms", I, [I, I, ctypes.POINTER(ctypes.c_float)]),
+    ("rails_cuda_comm_unique_id", I, [ctypes.c_char_p]),
+    ("rails_cuda_comm_init", I, [I, I, ctypes.c_char_p]),
+    ("rails_cuda_comm_rank", I, []),
+    ("rails_cuda_comm_size", I, []),
+    ("rails_partition_rows", I, [LL, I, I, ctypes.POINTER(LL), ctypes.POINTER(LL)]),
+    ("rails_mv_alloc", I, [LL, I, I, ctypes.POINTER(P)]),
+    ("rails_mv_free", I, [P]),
+    ("rails_mv_rows", LL, [P]),
+    ("rails_mv_ld", LL, [P]),
+    ("rails_mv_cols", I, [P]),
+    ("rails_mv_flags", I, [P]),
+    ("rails_mv_copy_cols", I, [P, I, P, I, I]),
+    ("rails_mv_upload", I, [P, I, I, c_double_p, LL]),
+    ("rails_mv_download", I, [P, I, I, c_double_p, LL]),
+    ("rails_mv_get", I, [P, LL, I, c_double_p]),
+    ("rails_mv_set", I, [P, LL, I, D]),
+    ("rails_mv_fill", I, [P, I, I, D]),
+    ("rails_mv_scal", I, [P, I, I, D]),
+    ("rails_mv_axpy", I, [P, I, D, P, I, I]),
+    ("rails_mv_scaled_copy", I, [P, I, D, P, I, I]),
+    ("rails_mv_add_scaled", I, [P, I, D, D, P, I, I]),
+    ("rails_mv_norm_inf", I, [P, I, I, c_double_p]),
+    ("rails_mv_dot", I, [P, I, I, P, I, I, c_double_p, I]),
+    ("rails_mv_dot_dev", I, [P, I, I, P, I, I, P, I]),
+    ("rails_mv_gemm", I, [P, I, I, c_double_p, I, I, D, D, P, I]),
+    ("rails_mv_gemm_dev", I, [P, I, I, P, I, I, D, D, P, I]),
+    ("rails_mv_orthogonalize", I, [P, I, I, I]),
+    ("rails_mv_random", I, [P, I, I, LL, ctypes.c_uint]),
+    ("rails_csr_create", I, [LL, LL, LL, LL, c_int_p, c_int_p, c_double_p, ctypes.POINTER(P)]),
+    ("rails_csr_free", I, [P]),
+    ("rails_csr_rows", LL, [P]),
+    ("rails_csr_nnz", LL, [P]),
+    ("rails_csr_spmm", I, [P, I, P, I, I, P, I]),
+    ("rails_csr_norm2", I, [P, c_double_p]),
+]
+
+
+def _declare_cuda(lib):
+    for name, res, args in CUDA_SYMBOLS:
+        f = getattr(lib, name)      # AttributeError if the symbol is missing
+        f.restype = res
+        f.argtypes = args
+
+
+class RailsError(RuntimeError):
+    pass
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise RailsError("%s failed (%d): %s" % (what, rc, cuda().rails_cuda_last_error().decode()))
+
+
+def init(device=0):
+    """Select the GPU.  Raises when no CUDA device is usable."""
+    check(cuda().rails_cuda_init(device), "rails_cuda_init")
+
+
+class MultiVector:
+    """Thin owner of a rails_mv_t for tests and the bench harness."""
+
+    def __init__(self, rows, cols, replicated=False):
+        self.h = P()
+        check(cuda().rails_mv_alloc(rows, cols, 1 if replicated else 0, ctypes.byref(self.h)), "mv_alloc")
+        self.rows, self.cols = rows, cols
+
+    @classmethod
+    def from_numpy(cls, a, replicated=False):
+        a = np.asfortranarray(a, dtype=np.float64)
+        if a.ndim == 1:
+            a = a.reshape(-1, 1, order="F")
+        mv = cls(a.shape[0], a.shape[1], replicated)
+        if a.size:
+            check(cuda().rails_mv_upload(mv.h, 0, a.shape[1], dptr(a), max(a.shape[0], 1)), "mv_upload")
+        return mv
+
+    def numpy(self, col0=0, ncols=None):
+        ncols = self.cols - col0 if ncols is None else ncols
+        out = np.zeros((self.rows, ncols), order="F")
+        if out.size:
+            check(cuda().rails_mv_download(self.h, col0, ncols, dptr(out), max(self.rows, 1)), "mv_download")
+        return out
+
+    def free(self):
+        if self.h:
+            cuda().rails_mv_free(self.h)
+            self.h = P()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, row_offset=0,
+          v_cap_cols=0, V0=None, time_from=0, time_to=0, hist_cap=4096):
+    """rails_host_solve through ctypes.  Returns a dict."""
+    lib = host()
+    rows = rowptr.size - 1
+    global_rows = rows if global_rows is None else global_rows
+    keys = [k.encode() for k in params]
+    karr = (ctypes.c_char_p * len(keys))(*keys)
+    pv = np.array([float(v) for v in params.values()], dtype=np.float64)
+    ha, hr = np.zeros(hist_cap), np.zeros(hist_cap)
+    hk, hs = np.zeros(hist_cap, dtype=np.int32), np.zeros(hist_cap)
+    hl, k = ctypes.c_int(0), ctypes.c_int(0)
+    V = T = None
+    if v_cap_cols > 0:
+        V = np.zeros((rows, v_cap_cols), order="F")
+        T = np.zeros((v_cap_cols, v_cap_cols), order="F")
+        if V0 is not None:
+            k.value = V0.shape[1]
+            V[:, :k.value] = V0
+    tm = ctypes.c_float(0)
+    ss, su, sd = ctypes.c_double(0), ctypes.c_double(0), ctypes.c_double(0)
+    Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
+    ret = lib.rails_host_solve(
+        ctypes.c_int(rows), ctypes.c_int(global_rows), ctypes.c_int(row_offset),
+        iptr(rowptr), iptr(colidx), dptr(vals), ctypes.c_int(n_b), dptr(Bc), ctypes.c_uint(seed),
+        ctypes.c_int(len(keys)), karr, dptr(pv), ctypes.c_int(hist_cap), dptr(ha), dptr(hr),
+        iptr(hk), dptr(hs), ctypes.byref(hl), ctypes.byref(k), ctypes.c_int(v_cap_cols),
+        dptr(V), dptr(T), ctypes.c_int(time_from), ctypes.c_int(time_to), ctypes.byref(tm),
+        ctypes.byref(ss), ctypes.byref(su), ctypes.byref(sd))
+    n = min(hl.value, hist_cap)
+    out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
+               space=hk[:n].copy(), seconds=hs[:n].copy(), timed_ms=tm.value,
+               solve_seconds=ss.value, setup_seconds=su.value, dense_solve_seconds=sd.value,
+               sections=lib.rails_host_last_sections().decode())
+    if V is not None and k.value <= v_cap_cols:
+        out["V"] = V[:, :k.value]
+        out["T"] = T[:k.value, :k.value]
+    return out

@@ -269,3 +269,81 @@ extern "C" int rails_mv_random(rails_mv_t mv, int col0, int ncols, long long row
     RAILS_CHECK_LAUNCH();
     return RAILS_OK;
 }
+
+namespace
+{
+
+__global__ void __launch_bounds__(EW_THREADS)
+scaled_copy_kernel(double *__restrict__ y, long long ldy, const double *__restrict__ x,
+                   long long ldx, long long rows2, double alpha)
+{
+    double2 *yc = reinterpret_cast<double2 *>(y + (size_t)blockIdx.y * ldy);
+    const double2 *xc = reinterpret_cast<const double2 *>(x + (size_t)blockIdx.y * ldx);
+    for (long long i = (long long)blockIdx.x * EW_THREADS + threadIdx.x; i < rows2;
+         i += (long long)gridDim.x * EW_THREADS)
+    {
+        double2 a = xc[i];
+        a.x *= alpha;
+        a.y *= alpha;
+        yc[i] = a;
+    }
+}
+
+__global__ void __launch_bounds__(EW_THREADS)
+add_scaled_kernel(double *__restrict__ y, long long ldy, const double *__restrict__ x,
+                  long long ldx, long long rows2, double sign, double alpha)
+{
+    double2 *yc = reinterpret_cast<double2 *>(y + (size_t)blockIdx.y * ldy);
+    const double2 *xc = reinterpret_cast<const double2 *>(x + (size_t)blockIdx.y * ldx);
+    for (long long i = (long long)blockIdx.x * EW_THREADS + threadIdx.x; i < rows2;
+         i += (long long)gridDim.x * EW_THREADS)
+    {
+        double2 a = xc[i];
+        double2 b = yc[i];
+        // round(alpha*x) first, then add: same bits as the two-step sequence
+        b.x = __dadd_rn(b.x, sign * __dmul_rn(alpha, a.x));
+        b.y = __dadd_rn(b.y, sign * __dmul_rn(alpha, a.y));
+        yc[i] = b;
+    }
+}
+
+}
+
+extern "C" int rails_mv_scaled_copy(rails_mv_t dst, int dcol, double alpha, rails_mv_t src, int scol, int ncols)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check(dst, dcol, ncols, "scaled_copy dst");
+    if (rc) return rc;
+    rc = check(src, scol, ncols, "scaled_copy src");
+    if (rc) return rc;
+    if (src->rows != dst->rows)
+        return rails::fail(RAILS_ERR_ARG, "scaled_copy: %lld vs %lld rows", src->rows, dst->rows);
+    long long rows2 = (dst->rows + 1) / 2;
+    if (ncols == 0 || rows2 == 0) return RAILS_OK;
+    dim3 grid(ew_grid(rows2), ncols);
+    RAILS_LAUNCH(scaled_copy_kernel, grid, EW_THREADS, 0, dst->data + (size_t)dcol * dst->ld, dst->ld,
+                 src->data + (size_t)scol * src->ld, src->ld, rows2, alpha);
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
+}
+
+extern "C" int rails_mv_add_scaled(rails_mv_t y, int yc0, double sign, double alpha, rails_mv_t x,
+                                   int xc0, int ncols)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check(y, yc0, ncols, "add_scaled y");
+    if (rc) return rc;
+    rc = check(x, xc0, ncols, "add_scaled x");
+    if (rc) return rc;
+    if (x->rows != y->rows)
+        return rails::fail(RAILS_ERR_ARG, "add_scaled: %lld vs %lld rows", x->rows, y->rows);
+    if (sign != 1.0 && sign != -1.0)
+        return rails::fail(RAILS_ERR_ARG, "add_scaled: sign must be +1 or -1");
+    long long rows2 = (y->rows + 1) / 2;
+    if (ncols == 0 || rows2 == 0) return RAILS_OK;
+    dim3 grid(ew_grid(rows2), ncols);
+    RAILS_LAUNCH(add_scaled_kernel, grid, EW_THREADS, 0, y->data + (size_t)yc0 * y->ld, y->ld,
+                 x->data + (size_t)xc0 * x->ld, x->ld, rows2, sign, alpha);
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
+}

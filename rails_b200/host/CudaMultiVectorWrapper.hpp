@@ -32,6 +32,7 @@
 #include "rails_cuda.h"
 
 #include <memory>
+#include <vector>
 
 namespace RAILS
 {
@@ -41,13 +42,18 @@ class CudaOperatorWrapper;
 class CudaMultiVectorWrapper
 {
 public:
+    struct Lazy;
     struct Buffer
     {
         rails_mv_t h;
+        // products that still READ this buffer; they are evaluated before the
+        // buffer is written to, so laziness is never observable
+        std::vector<std::weak_ptr<Lazy> > readers;
         explicit Buffer(rails_mv_t handle) : h(handle) {}
         ~Buffer() { rails_mv_free(h); }
         Buffer(Buffer const &) = delete;
         Buffer &operator=(Buffer const &) = delete;
+        void before_write(int col0, int ncols);
     };
 
     // test-only element access (the reference keeps operator()(i,j) protected
@@ -68,6 +74,23 @@ public:
         Element &operator-=(double v) { return *this = (double)*this - v; }
     };
 
+    // pending product  alpha * src[:, src_col0 : src_col0+src_k) * coef
+    struct Lazy
+    {
+        std::shared_ptr<Buffer> src;
+        int src_col0 = 0, src_k = 0;
+        bool has_coef = false;                 // false: plain alpha * src
+        HostDenseMatrix coef;                  // host coefficients (k x c), or
+        std::shared_ptr<Buffer> dev_coef;      // replicated device block
+        int dev_coef_col0 = 0;
+        double alpha = 1.0;
+        int m = 0, n = 0;                      // shape of the result
+        bool replicated = false;
+        std::shared_ptr<Buffer> result;        // set once evaluated
+        void evaluate();
+        bool reads(Buffer const *b, int col0, int ncols) const;
+    };
+
 private:
     mutable std::shared_ptr<Buffer> buf_;
     int col0_;            // first column of this object inside buf_
@@ -79,23 +102,14 @@ private:
     bool transpose_;
     bool replicated_;     // identical on all ranks (Epetra_LocalMap analogue)
 
-    // pending product  alpha * src[:, src_col0 : src_col0+src_k) * coef
-    struct Lazy
-    {
-        std::shared_ptr<Buffer> src;
-        int src_col0 = 0, src_k = 0;
-        bool has_coef = false;                 // false: plain alpha * src
-        HostDenseMatrix coef;                  // host coefficients (k x c), or
-        std::shared_ptr<Buffer> dev_coef;      // replicated device block
-        int dev_coef_col0 = 0;
-        double alpha = 1.0;
-    };
     mutable std::shared_ptr<Lazy> lazy_;
 
     void allocate(int m, int n, bool replicated);
     void materialize() const;
     void assign_columns(CudaMultiVectorWrapper const &other);
     void add_scaled(CudaMultiVectorWrapper const &other, double alpha);
+    void will_write();
+    static CudaMultiVectorWrapper make_lazy(std::shared_ptr<Lazy> const &l);
     rails_mv_t handle() const;
 
     friend class CudaOperatorWrapper;

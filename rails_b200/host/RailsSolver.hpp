@@ -1,0 +1,234 @@
+// RAILS::b200::Solver -- the restarted projection loop for
+//     A V T V' + V T V' A' + B B' = 0,      X ~ V T V'
+// over the same three duck-typed concepts as the reference's
+// RAILS::Solver<Matrix, MultiVector, DenseMatrix>
+// (/root/reference/src/LyapunovSolverDecl.hpp:9-51).
+//
+// Why it exists: the reference loop is header-only C++ that lives under
+// /root/reference and does not travel; this is the loop the product ships so
+// that the CUDA wrappers can run where the reference tree is absent.  It is a
+// from-scratch restatement of the ALGORITHM of src/LyapunovSolver.hpp:100-482
+// -- same public members, same parameter names and defaults (:27-36,76-87),
+// same return codes (0 converged / -1 stopped / 1 fell through, :239-240,345),
+// same progress lines on std::cout (:219-221,232-268) -- and it issues the
+// backend operations in the same order, so on any given backend it yields the
+// same bits as the reference loop (tests/test_solver_loop.py checks exactly
+// that against oracle/_ref with the reference's own StlWrapper).
+//
+// Additions that do not change the arithmetic: a per-iteration record
+// (history()), an optional observer called once per outer iteration (bench.py
+// uses it to bracket timed iterations with CUDA events) and wall-clock section
+// totals (sections()) with the reference's timer names.
+#ifndef RAILS_B200_RAILSSOLVER_HPP
+#define RAILS_B200_RAILSSOLVER_HPP
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <functional>
+#include <iostream>
+#include <locale>
+#include <map>
+#include <string>
+#include <utility>
+#include <vector>
+
+extern "C" {
+void sb03md_(char *dico, char *job, char *fact, char *trans, int *n, double *A, int *lda,
+             double *U, int *ldu, double *X, int *ldx, double *scale, double *sep,
+             double *ferr, double *alphar, double *alphai, int *iwork, double *dwork,
+             int *ldwork, int *info);
+void dsyev_(char *jobz, char *uplo, int *n, double *a, int *lda, double *w, double *work,
+            int *ldwork, int *info);
+}
+
+namespace RAILS
+{
+namespace b200
+{
+
+// B may be an Operator or a MultiVector (src/MatrixOrMultiVectorWrapper.hpp:7-61)
+template<class Matrix, class MultiVector>
+class InputB
+{
+    bool is_matrix_;
+    Matrix matrix_;
+    MultiVector vector_;
+
+public:
+    InputB(Matrix const &b) : is_matrix_(true), matrix_(b) {}
+    InputB(MultiVector const &b) : is_matrix_(false), vector_(b) {}
+
+    double norm() const { return is_matrix_ ? matrix_.norm() : vector_.norm(); }
+    MultiVector apply(MultiVector const &x) const
+    { return is_matrix_ ? matrix_ * x : vector_ * x; }
+    MultiVector apply_transposed(MultiVector const &x) const
+    { return is_matrix_ ? matrix_.transpose() * x : vector_.transpose() * x; }
+};
+
+// Matrix and MultiVector are one type (StlWrapper, ScalarWrapper)
+template<class Type>
+class InputB<Type, Type>
+{
+    Type b_;
+
+public:
+    template<class Any>
+    InputB(Any const &b) : b_(b) {}
+
+    double norm() const { return b_.norm(); }
+    Type apply(Type const &x) const { return b_ * x; }
+    Type apply_transposed(Type const &x) const { return b_.transpose() * x; }
+};
+
+struct IterationRecord
+{
+    int iteration;        // 1-based
+    int space_size;       // columns of V when the residual was estimated
+    double residual;      // largest Ritz value of the residual (absolute)
+    double relative;      // residual / |B|_2^2
+    bool restarted;       // this iteration ended in a restart
+    double seconds;       // wall clock since solve() began
+};
+
+template<class Matrix, class MultiVector, class DenseMatrix>
+class Solver
+{
+public:
+    typedef std::function<void(IterationRecord const &)> Observer;
+
+    template<class MatrixOrMultiVector>
+    Solver(Matrix const &A, MatrixOrMultiVector const &B, Matrix const &M)
+        : A_(A), B_(B), M_(M),
+          max_iter_(1000), tol_(1e-3), expand_size_(3), lanczos_iterations_(10),
+          restart_size_(-1), reduced_size_(-1), restart_iterations_(20),
+          restart_tolerance_(tol_ * 1e-3), minimize_solution_space_(true),
+          restart_from_solution_(false), verbose_(true)
+    {}
+
+    virtual ~Solver() {}
+
+    template<class ParameterList>
+    int set_parameters(ParameterList &params);
+
+    // Solve A*V*T*V' + V*T*V'*A' + B*B' = 0
+    int solve(MultiVector &V, DenseMatrix &T);
+
+    // Solve A*X + X*A' + B = 0 on the projected (k x k) problem
+    int dense_solve(DenseMatrix const &A, DenseMatrix const &B, DenseMatrix &X);
+
+    // Ritz pairs of the residual R = AV*T*V' + V*T*AV' + B*B'
+    int resid_lanczos(MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
+                      DenseMatrix &H, MultiVector &eigenvectors, DenseMatrix &eigenvalues,
+                      int max_iter);
+
+    // Restart basis from the dominant eigenvectors of T
+    int compute_restart_vectors(DenseMatrix &X, DenseMatrix const &T, int num, double tol);
+
+    // ---- additions ------------------------------------------------------
+    void set_observer(Observer obs) { observer_ = obs; }
+    void set_verbose(bool v) { verbose_ = v; }
+    std::vector<IterationRecord> const &history() const { return history_; }
+    // accumulated host wall-clock seconds per section (reference timer names)
+    std::map<std::string, double> const &sections() const { return sections_; }
+
+protected:
+    Matrix A_;
+    InputB<Matrix, MultiVector> B_;
+    Matrix M_;     // kept for interface parity; like the reference loop, unused
+
+    int max_iter_;
+    double tol_;
+    int expand_size_;
+    int lanczos_iterations_;
+    int restart_size_;
+    int reduced_size_;
+    int restart_iterations_;
+    double restart_tolerance_;
+    bool minimize_solution_space_;
+    bool restart_from_solution_;
+    bool verbose_;
+
+    Observer observer_;
+    std::vector<IterationRecord> history_;
+    std::map<std::string, double> sections_;
+
+    struct Section
+    {
+        std::map<std::string, double> &acc;
+        std::string name;
+        std::chrono::steady_clock::time_point t0;
+        Section(std::map<std::string, double> &a, const char *n)
+            : acc(a), name(n), t0(std::chrono::steady_clock::now()) {}
+        ~Section()
+        {
+            acc[name] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        }
+    };
+
+    void project(MultiVector const &V, MultiVector const &W, MultiVector &AV, MultiVector &BV,
+                 DenseMatrix &VAV, DenseMatrix &VBV, bool first, int max_size);
+    void compress(MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV,
+                  DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix const &T);
+};
+
+// A key is looked up as given, then UPPER, lower and Title Case; the last
+// spelling that is present wins (src/LyapunovSolver.hpp:40-70).
+template<class ParameterList, class Type>
+Type lookup_parameter(ParameterList &params, std::string const &name, Type def)
+{
+    std::locale loc;
+    Type value = params.get(name, def);
+
+    std::string upper(name), lower(name), title(name);
+    for (size_t i = 0; i < name.size(); ++i)
+    {
+        upper[i] = std::toupper(name[i], loc);
+        lower[i] = std::tolower(name[i], loc);
+    }
+    if (!title.empty())
+        title[0] = std::toupper(title[0]);
+    for (size_t i = 1; i < title.size(); ++i)
+        if (!isalpha(title[i - 1]) && islower(title[i]))
+            title[i] = std::toupper(title[i], loc);
+
+    value = params.get(upper, value);
+    value = params.get(lower, value);
+    value = params.get(title, value);
+    return value;
+}
+
+template<class Matrix, class MultiVector, class DenseMatrix>
+template<class ParameterList>
+int Solver<Matrix, MultiVector, DenseMatrix>::set_parameters(ParameterList &params)
+{
+    max_iter_ = lookup_parameter(params, "Maximum iterations", max_iter_);
+    tol_ = lookup_parameter(params, "Tolerance", tol_);
+    expand_size_ = lookup_parameter(params, "Expand size", expand_size_);
+    lanczos_iterations_ = lookup_parameter(params, "Lanczos iterations", lanczos_iterations_);
+    restart_size_ = lookup_parameter(params, "Restart size", restart_size_);
+    reduced_size_ = lookup_parameter(params, "Reduced size", reduced_size_);
+    restart_iterations_ = lookup_parameter(params, "Restart iterations", restart_iterations_);
+    // recomputed from the NEW tolerance unless given (:83)
+    restart_tolerance_ = lookup_parameter(params, "Restart tolerance", tol_ * 1e-3);
+    minimize_solution_space_ = lookup_parameter(params, "Minimize solution space",
+                                                minimize_solution_space_);
+    restart_from_solution_ = lookup_parameter(params, "Restart from solution",
+                                              restart_from_solution_);
+
+    if (lanczos_iterations_ <= expand_size_)
+    {
+        std::cerr << "Amount of Lanczos iterations is smaller than "
+                  << "the amount of vectors that are used to expand "
+                  << "the space in every iteration" << std::endl;
+        return 1;
+    }
+    return 0;
+}
+
+}
+}
+
+#include "RailsSolverImpl.hpp"
+
+#endif

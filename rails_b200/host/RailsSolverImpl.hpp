@@ -1,0 +1,444 @@
+// Implementation of RAILS::b200::Solver (see RailsSolver.hpp).  Line numbers
+// in comments refer to /root/reference/src/LyapunovSolver.hpp.
+#ifndef RAILS_B200_RAILSSOLVERIMPL_HPP
+#define RAILS_B200_RAILSSOLVERIMPL_HPP
+
+namespace RAILS
+{
+namespace b200
+{
+
+namespace detail
+{
+
+// indices of the `count` entries largest in magnitude, in the order the
+// reference's find_largest_eigenvalues produces (src/StlTools.hpp:12-30)
+template<class DenseMatrix>
+std::vector<int> largest_by_magnitude(DenseMatrix const &values, int count)
+{
+    std::vector<std::pair<int, double> > tagged;
+    for (int i = 0; i < values.M(); i++)
+        tagged.push_back(std::pair<int, double>(i, values(i)));
+    std::sort(tagged.begin(), tagged.end(),
+              [](std::pair<int, double> const &a, std::pair<int, double> const &b)
+              { return std::abs(a.second) > std::abs(b.second); });
+    std::vector<int> picked;
+    for (int i = 0; i < count; i++)
+        picked.push_back(tagged[i].first);
+    return picked;
+}
+
+}
+
+// VAV <- [[VAV; W'AV], V'AW],  VBV likewise, AV <- [AV, A W], BV <- [BV, B'W]
+// (:141-207).  W holds the columns of V that are new since the last call.
+template<class Matrix, class MultiVector, class DenseMatrix>
+void Solver<Matrix, MultiVector, DenseMatrix>::project(
+    MultiVector const &V, MultiVector const &W, MultiVector &AV, MultiVector &BV,
+    DenseMatrix &VAV, DenseMatrix &VBV, bool first, int max_size)
+{
+    MultiVector AW, BW;
+    {
+        Section s(sections_, "Apply A");
+        AW = A_ * W;
+    }
+    {
+        Section s(sections_, "Apply B");
+        BW = B_.apply_transposed(W);
+    }
+    if (first)
+    {
+        // BV has the shape of B', not of V
+        BV = MultiVector(BW, max_size);
+        BV.resize(0);
+    }
+
+    Section s(sections_, "Compute VAV");
+    const int old_cols = AV.N();
+    const int size = old_cols + W.N();
+    VAV.resize(size, size);          // keeps the old entries
+    VBV.resize(size, size);
+
+    if (old_cols > 0)
+    {
+        DenseMatrix WAV = W.dot(AV);
+        DenseMatrix WBV = BW.dot(BV);
+        for (int i = 0; i < WAV.M(); i++)
+            for (int j = 0; j < WAV.N(); j++)
+            {
+                VAV(i + old_cols, j) = WAV(i, j);
+                VBV(i + old_cols, j) = WBV(i, j);
+                VBV(j, i + old_cols) = WBV(i, j);
+            }
+    }
+
+    DenseMatrix VAW = V.dot(AW);
+    for (int i = 0; i < VAW.M(); i++)
+        for (int j = 0; j < VAW.N(); j++)
+            VAV(i, j + old_cols) = VAW(i, j);
+
+    DenseMatrix WBW = BW.dot(BW);
+    for (int i = 0; i < WBW.M(); i++)
+        for (int j = 0; j < WBW.N(); j++)
+            VBV(i + old_cols, j + old_cols) = WBW(i, j);
+
+    AV.push_back(AW);
+    BV.push_back(BW);
+}
+
+// Restart: V <- V X, AV <- AV X, BV <- BV X, VAV <- X'VAV X, VBV <- X'VBV X
+// with X the dominant eigenvectors of T (:258-303)
+template<class Matrix, class MultiVector, class DenseMatrix>
+void Solver<Matrix, MultiVector, DenseMatrix>::compress(
+    MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV,
+    DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix const &T)
+{
+    DenseMatrix X;
+    compute_restart_vectors(X, T, std::min(reduced_size_, V.N()), restart_tolerance_);
+    const int kept = X.N();
+
+    V.view(0, kept - 1) = V * X;
+    V.resize(kept);
+
+    if (verbose_)
+        std::cout << "Restarted with " << V.N() << " vectors" << std::endl;
+
+    W.resize(0);
+
+    DenseMatrix small = X.transpose() * (VAV * X);
+    VAV.resize(kept, kept);
+    VAV.view() = small;
+
+    AV.view(0, kept - 1) = AV * X;
+    AV.resize(kept);
+
+    small = X.transpose() * (VBV * X);
+    VBV.resize(kept, kept);
+    VBV.view() = small;
+
+    BV.view(0, kept - 1) = BV * X;
+    BV.resize(kept);
+}
+
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix &T)
+{
+    const auto t_begin = std::chrono::steady_clock::now();
+    history_.clear();
+    sections_.clear();
+
+    const int n = V.M();
+    int max_size = std::max(V.N(), std::min(restart_size_ > 0 ? restart_size_ : 100, n));
+
+    if (!restart_from_solution_)
+    {
+        // random normalised start vector in a buffer with room to grow (:108-115)
+        V.resize(max_size);
+        V.resize(1);
+        V.random();
+        V.orthogonalize();
+    }
+    else if (max_size != V.N())
+    {
+        const int have = V.N();
+        V.resize(max_size);
+        V.resize(have);
+    }
+
+    MultiVector W(V);                 // deep copy, as `MultiVector W = V` (:123)
+
+    MultiVector AV(V, max_size);
+    DenseMatrix VAV(max_size, max_size);
+    AV.resize(0);
+
+    MultiVector BV;
+    DenseMatrix VBV(max_size, max_size);
+
+    bool converged_before = false;
+    int last_restart = 0;
+    const double r0 = B_.norm();
+
+    for (int iter = 0; iter < max_iter_; iter++)
+    {
+        const int cols_before = V.N();
+        if (W.N())
+            project(V, W, AV, BV, VAV, VBV, iter == 0, max_size);
+
+        dense_solve(VAV, VBV, T);
+
+        const int L = lanczos_iterations_;
+        DenseMatrix H(L + 1, L + 1);
+        DenseMatrix ritz_values(L, 1);
+        MultiVector ritz_vectors;
+        resid_lanczos(AV, V, T, H, ritz_vectors, ritz_values, L);
+
+        const double res = ritz_values.norm_inf();
+
+        if (verbose_)
+            std::cout << "Iteration " << iter + 1
+                      << ". Estimate Lanczos, absolute: " << res
+                      << ", relative: " << std::abs(res) / r0 / r0 << std::endl;
+
+        IterationRecord rec;
+        rec.iteration = iter + 1;
+        rec.space_size = V.N();
+        rec.residual = res;
+        rec.relative = std::abs(res) / r0 / r0;
+        rec.restarted = false;
+
+        const bool converged = std::abs(res) < tol_ * r0 * r0;
+        const bool out_of_room = iter + 1 >= max_iter_ || V.N() >= n;
+        bool stop = false;
+        if (converged || out_of_room)
+        {
+            // first convergence only triggers a compression restart (:226-229)
+            if (converged && minimize_solution_space_ && !converged_before)
+                converged_before = true;
+            else
+                stop = true;
+        }
+
+        if (stop)
+        {
+            if (verbose_)
+                std::cout << "The Lyapunov solver "
+                          << (converged ? "converged" : "did not converge")
+                          << " in " << iter + 1
+                          << " iterations with a final relative residual of "
+                          << res / r0 / r0 << ". The size of the space used "
+                          << "for the solution is " << V.N() << std::endl;
+            rec.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+            history_.push_back(rec);
+            if (observer_)
+                observer_(rec);
+            return converged ? 0 : -1;
+        }
+
+        const bool space_full = restart_size_ > 0 && V.N() >= restart_size_;
+        const bool period_over = restart_iterations_ > 0 && iter - last_restart >= restart_iterations_;
+        if (space_full || period_over || converged)
+        {
+            if (verbose_)
+            {
+                if (converged)
+                    std::cout << "Method converged. Minimizing the solution "
+                              << "space size";
+                else if (restart_size_ > 0)
+                    std::cout << "Reached the maximum space size of " << restart_size_;
+                else if (restart_iterations_ > 0)
+                    std::cout << restart_iterations_ << " iterations have passed";
+                else
+                    std::cout << "No clue what happened";
+                std::cout << ". Trying to restart with "
+                          << (reduced_size_ > 0 ? reduced_size_ : V.N())
+                          << " vectors" << std::endl;
+            }
+
+            compress(V, W, AV, BV, VAV, VBV, T);
+            last_restart = iter;
+
+            rec.restarted = true;
+            rec.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+            history_.push_back(rec);
+            if (observer_)
+                observer_(rec);
+            continue;
+        }
+
+        const int room = (restart_size_ > 0 ? restart_size_ : n) - V.N();
+        const int grow_by = std::min(std::min(expand_size_, ritz_values.M()), room);
+
+        // capacity grows 100 columns at a time (:311-332)
+        if (V.N() + grow_by > max_size)
+        {
+            Section s(sections_, "Resize spaces");
+            max_size += 100;
+            const int have = V.N();
+
+            V.resize(max_size);
+            V.resize(have);
+
+            AV.resize(max_size);
+            AV.resize(have);
+
+            VAV.resize(max_size, max_size);
+            VAV.resize(have, have);
+
+            BV.resize(max_size);
+            BV.resize(have);
+
+            VBV.resize(max_size, max_size);
+            VBV.resize(have, have);
+        }
+
+        // expand with the Ritz vectors of the largest residual Ritz values
+        std::vector<int> picked = detail::largest_by_magnitude(ritz_values, grow_by);
+        for (int i = 0; i < grow_by; i++)
+            V.push_back(ritz_vectors.view(picked[i]));
+        {
+            Section s(sections_, "orthogonalize");
+            V.orthogonalize();
+        }
+
+        W = V.view(cols_before, cols_before + grow_by - 1);
+
+        rec.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+        history_.push_back(rec);
+        if (observer_)
+            observer_(rec);
+    }
+
+    return 1;
+}
+
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::dense_solve(DenseMatrix const &A,
+                                                          DenseMatrix const &B, DenseMatrix &X)
+{
+    Section s(sections_, "dense_solve");
+    // sb03md('C','X','N','T'): A Y + Y A' = scale * C, solution returned in
+    // the C array; then X = -Y (:348-365, src/SlicotWrapper.cpp:8-49)
+    X = B.copy();
+    DenseMatrix S = A.copy();
+    int n = A.M();
+    int info = 0;
+    double scale = 1.0;
+    if (n < 1)
+    {
+        std::cerr << "Slicot error: n < 1 is not supported" << std::endl;
+        return info;
+    }
+
+    char dico = 'C', job = 'X', fact = 'N', trans = 'T';
+    const int pad = n + 2;                     // workspace sizes of the reference wrapper
+    std::vector<double> U((size_t)pad * pad), wr(pad), wi(pad);
+    int ldwork = 2 * std::max(pad * pad, 3 * pad);
+    std::vector<double> work(ldwork);
+    double sep = 0.0, ferr = 0.0;
+    int lda = S.LDA(), ldx = X.LDA();
+    sb03md_(&dico, &job, &fact, &trans, &n, S, &lda, U.data(), &n, X, &ldx, &scale, &sep,
+            &ferr, wr.data(), wi.data(), NULL, work.data(), &ldwork, &info);
+
+    X *= -1.0;
+
+    if (info != 0 && info != n + 1)
+        std::cerr << "Error: sb03md returned info = " << info << std::endl;
+    return info;
+}
+
+// L steps of symmetric Lanczos (no re-orthogonalisation) on the residual
+// operator applied through its low-rank factors (:367-447):
+//     R q = B (B' q) + AV (T (V' q)) + V (T (AV' q))
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
+    MultiVector const &AV, MultiVector const &V, DenseMatrix const &T, DenseMatrix &H,
+    MultiVector &eigenvectors, DenseMatrix &eigenvalues, int max_iter)
+{
+    Section s(sections_, "resid_lanczos");
+
+    MultiVector Q(V, max_iter + 1);
+    Q.resize(1);
+    Q.random();
+    Q.view(0) /= Q.norm();
+
+    H = 0.0;
+
+    double alpha = 0.0, beta = 0.0;
+    int steps = 0;
+    for (int i = 0; i < max_iter; i++)
+    {
+        Q.resize(steps + 2);
+        // bound to the view temporaries themselves: copy-constructing a view
+        // would deep-copy it (the concept's copy constructor is deep)
+        MultiVector const &q = Q.view(steps);
+        MultiVector &&next = Q.view(steps + 1);
+
+        MultiVector Y = B_.apply_transposed(q);
+        next = B_.apply(Y);
+
+        DenseMatrix Z = V.dot(q);
+        Z = T * Z;
+        next += AV * Z;
+
+        Z = AV.dot(q);
+        Z = T * Z;
+        next += V * Z;
+
+        alpha = next.dot(q)(0, 0);
+        H(steps, steps) = alpha;
+
+        next -= alpha * q;
+        if (steps > 0)
+            next -= beta * Q.view(steps - 1);
+
+        beta = next.norm();
+        if (beta < 1e-14)
+        {
+            // invariant subspace: keep H as it is, cannot normalise
+            steps++;
+            break;
+        }
+
+        H(steps + 1, steps) = beta;
+        H(steps, steps + 1) = beta;
+
+        next /= beta;
+        steps++;
+    }
+
+    H.resize(steps, steps);
+    Q.resize(steps);
+
+    DenseMatrix v(steps, steps);
+    H.eigs(v, eigenvalues);
+
+    eigenvectors = Q * v;
+    return 0;
+}
+
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::compute_restart_vectors(
+    DenseMatrix &X, DenseMatrix const &T, int num, double tol)
+{
+    Section s(sections_, "compute_restart_vectors");
+
+    // all eigenpairs of T (DSYEV 'V','U' with a workspace query, as
+    // src/LapackWrapper.cpp:18-39)
+    DenseMatrix vecs = T.copy();
+    DenseMatrix vals(T.N(), 1);
+    {
+        char jobz = 'V', uplo = 'U';
+        int n = vecs.N(), lda = vecs.LDA(), info = 0, lwork = -1;
+        double query = 0.0;
+        dsyev_(&jobz, &uplo, &n, vecs, &lda, vals, &query, &lwork, &info);
+        lwork = (int)query;
+        std::vector<double> work(std::max(lwork, 1));
+        dsyev_(&jobz, &uplo, &n, vecs, &lda, vals, work.data(), &lwork, &info);
+        if (info)
+            std::cerr << "DSYEV info = " << info << std::endl;
+    }
+
+    num = (num > 0 ? num : T.N());
+    X = DenseMatrix(T.N(), num);
+
+    std::vector<int> picked = detail::largest_by_magnitude(vals, num);
+
+    // candidates are sorted by magnitude, so the rejected ones are a suffix
+    // and column i can be written in place (:468-479)
+    int kept = 0;
+    for (int i = 0; i < num; ++i)
+        if (std::abs(vals(picked[i], 0)) > tol)
+        {
+            for (int j = 0; j < T.N(); ++j)
+                X(j, i) = vecs(j, picked[i]);
+            kept++;
+        }
+
+    X.resize(T.N(), kept);
+    return 0;
+}
+
+}
+}
+
+#endif

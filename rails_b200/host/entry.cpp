@@ -1,0 +1,174 @@
+// C entry points of librails_host.so: the solver loop over the CUDA wrappers,
+// callable from Python (bench.py, tests) or any FFI with plain pointers.
+//
+// rails_host_solve is the user-facing call of this framework: host CSR arrays
+// and (optionally) a host B go in, the low-rank factors V (m x k) and T (k x k)
+// of X = V T V' come back to host memory, together with the iteration history.
+#include "CudaMultiVectorWrapper.hpp"
+#include "CudaOperatorWrapper.hpp"
+#include "HostDenseMatrix.hpp"
+#include "RailsSolver.hpp"
+
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <sstream>
+#include <string>
+
+using namespace RAILS;
+
+namespace
+{
+
+// duck-typed ParameterList: template<class T> T get(name, default)
+// (contract of src/LyapunovSolver.hpp:40-70)
+class KeyValueParameters
+{
+    std::map<std::string, double> values_;
+
+public:
+    KeyValueParameters(int n, const char *const *keys, const double *vals)
+    {
+        for (int i = 0; i < n; ++i)
+            values_[keys[i]] = vals[i];
+    }
+    template<typename T>
+    T get(std::string const &name, T def)
+    {
+        auto it = values_.find(name);
+        return it == values_.end() ? def : (T)it->second;
+    }
+};
+
+typedef b200::Solver<CudaOperatorWrapper, CudaMultiVectorWrapper, HostDenseMatrix> CudaSolver;
+
+std::string g_sections;
+
+}
+
+extern "C" {
+
+// Returns the solver's code (0 converged, -1 stopped unconverged, 1 fell out of
+// the loop), 100 + code for a rejected parameter list, 200 for a CUDA failure.
+//
+//   rows/global_rows/row_offset : this rank's row block of the square operator
+//       (single rank: rows = global_rows, row_offset = 0); colidx is GLOBAL
+//   B_in   : this rank's rows of B (rows x n_b, column-major, ld = rows), or
+//            NULL for B = random() after std::srand(seed)  (the reference
+//            tests' way of making B, test/LyapunovSolver_test.cpp:66-71)
+//   V_io   : warm start (params "Restart from solution" = 1): on entry k_io
+//            columns of V (this rank's rows, ld = rows); on exit the solution
+//            basis if it fits v_cap_cols columns.  T_out is v_cap_cols^2.
+//   timed region: CUDA events are recorded on the library stream when
+//            iteration `time_from` and iteration `time_to` finish; their
+//            distance is returned in *timed_ms (0 if not reached).
+int rails_host_solve(int rows, int global_rows, int row_offset,
+                     const int *rowptr, const int *colidx, const double *vals,
+                     int n_b, const double *B_in, unsigned seed,
+                     int nparams, const char *const *keys, const double *pvals,
+                     int hist_cap, double *hist_abs, double *hist_rel, int *hist_k,
+                     double *hist_sec, int *hist_len,
+                     int *k_io, int v_cap_cols, double *V_io, double *T_out,
+                     int time_from, int time_to, float *timed_ms,
+                     double *solve_seconds, double *setup_seconds, double *dense_solve_seconds)
+{
+    if (!rails_cuda_is_initialized())
+    {
+        std::cerr << "rails_host_solve: rails_cuda_init has not been called" << std::endl;
+        return 200;
+    }
+    auto t_setup = std::chrono::steady_clock::now();
+    std::srand(seed);
+
+    CudaOperatorWrapper A(rows, global_rows, global_rows, row_offset, rowptr, colidx, vals);
+    if (!A.device_handle())
+        return 200;
+
+    CudaMultiVectorWrapper B(global_rows, n_b);
+    if (B_in)
+    {
+        if (rails_mv_upload(B.device_handle(), 0, n_b, B_in, rows))
+            return 200;
+    }
+    else
+        B.random();
+
+    CudaSolver solver(A, B, A);
+    KeyValueParameters params(nparams, keys, pvals);
+    int ret = solver.set_parameters(params);
+    if (ret)
+        return 100 + ret;
+    solver.set_verbose(std::getenv("RAILS_VERBOSE") != nullptr);
+
+    bool warm = params.get("Restart from solution", false);
+    CudaMultiVectorWrapper V(global_rows, warm && k_io ? std::max(*k_io, 1) : 1);
+    if (warm && k_io && V_io && *k_io > 0)
+    {
+        if (rails_mv_upload(V.device_handle(), 0, *k_io, V_io, rows))
+            return 200;
+    }
+    HostDenseMatrix T;
+
+    bool have_start = false, have_stop = false;
+    solver.set_observer([&](b200::IterationRecord const &rec) {
+        if (rec.iteration == time_from)
+            have_start = rails_cuda_event_record(0) == 0;
+        if (rec.iteration == time_to)
+            have_stop = rails_cuda_event_record(1) == 0;
+    });
+    rails_cuda_sync();
+    auto t0 = std::chrono::steady_clock::now();
+    if (setup_seconds)
+        *setup_seconds = std::chrono::duration<double>(t0 - t_setup).count();
+
+    ret = solver.solve(V, T);
+    rails_cuda_sync();
+    auto t1 = std::chrono::steady_clock::now();
+    if (solve_seconds)
+        *solve_seconds = std::chrono::duration<double>(t1 - t0).count();
+    if (timed_ms)
+    {
+        *timed_ms = 0.0f;
+        if (have_start && have_stop)
+            rails_cuda_event_elapsed_ms(0, 1, timed_ms);
+    }
+
+    auto const &hist = solver.history();
+    if (hist_len)
+        *hist_len = (int)hist.size();
+    for (int i = 0; i < std::min((int)hist.size(), hist_cap); ++i)
+    {
+        if (hist_abs) hist_abs[i] = hist[i].residual;
+        if (hist_rel) hist_rel[i] = hist[i].relative;
+        if (hist_k) hist_k[i] = hist[i].space_size;
+        if (hist_sec) hist_sec[i] = hist[i].seconds;
+    }
+    std::ostringstream os;
+    for (auto const &kv : solver.sections())
+        os << kv.first << "=" << kv.second << ";";
+    g_sections = os.str();
+    if (dense_solve_seconds)
+    {
+        auto it = solver.sections().find("dense_solve");
+        *dense_solve_seconds = it == solver.sections().end() ? 0.0 : it->second;
+    }
+
+    int k = V.N();
+    if (k_io)
+        *k_io = k;
+    if (V_io && T_out && k <= v_cap_cols)
+    {
+        if (V.to_host(V_io, rows))
+            return 200;
+        for (int j = 0; j < k; ++j)
+            for (int i = 0; i < k; ++i)
+                T_out[i + (size_t)j * v_cap_cols] = T(i, j);
+    }
+    return ret;
+}
+
+// "name=seconds;" list of the last solve's host-side section totals
+const char *rails_host_last_sections(void) { return g_sections.c_str(); }
+
+}

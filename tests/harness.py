@@ -1,0 +1,134 @@
+"""Test-side ctypes bindings for the checkers: oracle/liboracle.so (CPU
+restatement) and oracle/_ref/librails_ref_stl.so (the reference itself).
+Nothing here is imported by the product."""
+import ctypes
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+c_double_p = ctypes.POINTER(ctypes.c_double)
+c_int_p = ctypes.POINTER(ctypes.c_int)
+LL = ctypes.c_longlong
+
+
+def dptr(a):
+    return None if a is None else a.ctypes.data_as(c_double_p)
+
+
+def iptr(a):
+    return None if a is None else a.ctypes.data_as(c_int_p)
+
+
+_oracle = None
+_ref = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import build_oracle
+        lib = ctypes.CDLL(build_oracle.build())
+        lib.oracle_norm_inf.restype = ctypes.c_double
+        _oracle = lib
+    return _oracle
+
+
+def ref_path():
+    return os.path.join(ROOT, "oracle", "_ref", "librails_ref_stl.so")
+
+
+def ref():
+    """The reference arm; None when oracle/_ref was never built here."""
+    global _ref
+    if _ref is None and os.path.exists(ref_path()):
+        _ref = ctypes.CDLL(ref_path())
+    return _ref
+
+
+def _params(params):
+    keys = [k.encode() for k in params]
+    karr = (ctypes.c_char_p * len(keys))(*keys)
+    pv = np.array([float(v) for v in params.values()], dtype=np.float64)
+    return len(keys), karr, pv
+
+
+def oracle_solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, v_cap_cols=0, V0=None,
+                 hist_cap=4096):
+    lib = oracle()
+    m = rowptr.size - 1
+    nk, karr, pv = _params(params)
+    ha, hr = np.zeros(hist_cap), np.zeros(hist_cap)
+    hk, hs = np.zeros(hist_cap, dtype=np.int32), np.zeros(hist_cap)
+    hl, k = ctypes.c_int(0), ctypes.c_int(0)
+    V = T = None
+    if v_cap_cols > 0:
+        V = np.zeros((m, v_cap_cols), order="F")
+        T = np.zeros((v_cap_cols, v_cap_cols), order="F")
+        if V0 is not None:
+            k.value = V0.shape[1]
+            V[:, :k.value] = V0
+    ss, sd = ctypes.c_double(0), ctypes.c_double(0)
+    Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
+    ret = lib.oracle_solve(
+        ctypes.c_int(m), iptr(rowptr), iptr(colidx), dptr(vals), ctypes.c_int(n_b), dptr(Bc),
+        ctypes.c_uint(seed), ctypes.c_int(nk), karr, dptr(pv), ctypes.c_int(hist_cap), dptr(ha),
+        dptr(hr), iptr(hk), dptr(hs), ctypes.byref(hl), ctypes.byref(k), ctypes.c_int(v_cap_cols),
+        dptr(V), dptr(T), ctypes.byref(ss), ctypes.byref(sd))
+    n = min(hl.value, hist_cap)
+    out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
+               space=hk[:n].copy(), seconds=hs[:n].copy(), solve_seconds=ss.value,
+               dense_solve_seconds=sd.value)
+    if V is not None and k.value <= v_cap_cols:
+        out["V"] = V[:, :k.value]
+        out["T"] = T[:k.value, :k.value]
+    return out
+
+
+def ref_stl_solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, v_cap_cols=0, hist_cap=4096,
+                  entry="ref_stl_solve"):
+    lib = ref()
+    m = rowptr.size - 1
+    nk, karr, pv = _params(params)
+    ha, hr = np.zeros(hist_cap), np.zeros(hist_cap)
+    hl, k = ctypes.c_int(0), ctypes.c_int(0)
+    V = T = None
+    if v_cap_cols > 0:
+        V = np.zeros((m, v_cap_cols), order="F")
+        T = np.zeros((v_cap_cols, v_cap_cols), order="F")
+    ss = ctypes.c_double(0)
+    Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
+    ret = getattr(lib, entry)(
+        ctypes.c_int(m), iptr(rowptr), iptr(colidx), dptr(vals), ctypes.c_int(n_b), dptr(Bc),
+        ctypes.c_uint(seed), ctypes.c_int(nk), karr, dptr(pv), ctypes.c_int(hist_cap), dptr(ha),
+        dptr(hr), ctypes.byref(hl), ctypes.byref(k), ctypes.c_int(v_cap_cols), dptr(V), dptr(T),
+        ctypes.byref(ss))
+    n = min(hl.value, hist_cap)
+    out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
+               solve_seconds=ss.value)
+    if V is not None and k.value <= v_cap_cols:
+        out["V"] = V[:, :k.value]
+        out["T"] = T[:k.value, :k.value]
+    return out
+
+
+def lowrank_rel_diff(V1, T1, V2, T2):
+    """||V1 T1 V1' - V2 T2 V2'||_F / ||V2 T2 V2'||_F through the factors."""
+    G11, G22, G12 = V1.T @ V1, V2.T @ V2, V1.T @ V2
+    n1 = np.trace(T1 @ G11 @ T1.T @ G11)
+    n2 = np.trace(T2 @ G22 @ T2.T @ G22)
+    cross = np.trace(T1 @ G12 @ T2.T @ G12.T)
+    return np.sqrt(max(n1 - 2 * cross + n2, 0.0) / n2)
+
+
+def csr_to_dense(rowptr, colidx, vals, n):
+    m = rowptr.size - 1
+    A = np.zeros((m, n))
+    for i in range(m):
+        A[i, colidx[rowptr[i]:rowptr[i + 1]]] = vals[rowptr[i]:rowptr[i + 1]]
+    return A

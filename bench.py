@@ -1,0 +1,395 @@
+#!/usr/bin/env python
+"""bench.py -- RAILS outer iterations/s on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--workload C1|C2|C3|C4|C5] [--grid G]
+
+A "step" is one outer RAILS iteration (src/LyapunovSolver.hpp:136-343:
+projection update, projected solve, L-step residual Lanczos, convergence test,
+expansion + CGS2, or a restart compression).  The workload at N = 1 is config
+C3 of BASELINE.json -- the 3-D 7-point Laplacian 256^3 (m = 16 777 216), B
+random m x 1, tolerance 1e-4 -- the configuration the north_star quotes its
+targets on; it fits one GPU.  (M = I: the C++ reference never reads M,
+SURVEY F1.)  With N > 1 the SAME matrix is row-partitioned over the ranks
+(Epetra linear map): "scaling": "strong".
+
+Timed region (`value`): iterations W+1 .. W+K of a solve started from scratch,
+bracketed by CUDA events on the library stream with everything resident in HBM
+(each rank reports its own event time; the max over ranks is used).  Inputs are
+far larger than the 126 MB L2 (V alone is 134 MB per column), so there is no
+L2 flush between iterations.
+`e2e`: the same solve through the user-facing C entry point rails_host_solve
+with HOST buffers -- the CSR arrays and B are uploaded, V and T downloaded,
+inside the timed wall-clock region; value = (W+K) iterations / that time.
+`roofline`: the dominant kernel (tall-skinny V'q of the residual Lanczos)
+timed alone with CUDA events at the workload's row count.
+`cpu_baseline` / `--impl reference`: the CPU oracle (CSR + OpenMP restatement
+of the reference loop; the reference's own sparse path needs Trilinos, which
+is not installable here) on the same inputs with all host threads.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from rails_b200 import problems  # noqa: E402
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("RAILS_BENCH_WORKLOAD", "C3"))
+    ap.add_argument("--grid", type=int, default=int(os.environ.get("RAILS_BENCH_GRID", "0")),
+                    help="override the grid size g of the workload (testing)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernels", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=25.0,
+                    help="time budget of the bounded CPU sample")
+    return ap.parse_args()
+
+
+def workload(args):
+    kind, g, dim, n_b, params = problems.CONFIGS[args.workload]
+    if args.grid:
+        g = args.grid
+    params = dict(params)
+    return kind, g, dim, n_b, params
+
+
+def workload_name(args, kind, g, dim, n_b):
+    return "%s %s %dD g=%d (m=%d), M=I, B random m x %d, tol 1e-4" % (
+        args.workload, kind, dim, g, g ** dim, n_b)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ts, line in self.lines:
+            if t0 is not None and (ts < t0 or ts > t1 + 0.3):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                  "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)),
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
+    """Per-kernel device time at the workload's row count (CUDA events on the
+    library stream, after warm-up; operands are GBs, far beyond L2).
+    Algorithmic bytes follow SURVEY.md §8(d) / DESIGN.md."""
+    lib = api.cuda()
+    P = ctypes.c_void_p
+    out = {}
+
+    def timed(fn, reps=reps, warm=3):
+        for _ in range(warm):
+            fn()
+        api.check(lib.rails_cuda_event_record(2), "event")
+        for _ in range(reps):
+            fn()
+        api.check(lib.rails_cuda_event_record(3), "event")
+        ms = ctypes.c_float(0)
+        api.check(lib.rails_cuda_event_elapsed_ms(2, 3, ctypes.byref(ms)), "elapsed")
+        return ms.value / reps
+
+    V = api.MultiVector(rows, k + 2)
+    q = api.MultiVector(rows, 2)
+    api.check(lib.rails_mv_random(V.h, 0, k + 2, row_offset, ctypes.c_uint(7)), "random")
+    api.check(lib.rails_mv_random(q.h, 0, 2, row_offset, ctypes.c_uint(8)), "random")
+    small = api.MultiVector(k, 1, replicated=True)
+    coef = np.asfortranarray(np.full((k, 1), 1e-3))
+    m = rows
+    nnz = int(rp[-1])
+
+    def rec(name, ms, nbytes, launches):
+        out[name] = {"ms": ms, "bytes": nbytes, "gbs": nbytes / ms / 1e6, "launches_per_call": launches}
+
+    ms = timed(lambda: api.check(lib.rails_mv_dot_dev(V.h, 0, k, q.h, 0, 1, small.h, 0), "dot"))
+    rec("dot_kx1", ms, 8.0 * m * (k + 1), 2)
+    ms = timed(lambda: api.check(lib.rails_mv_gemm(V.h, 0, k, api.dptr(coef), k, 1, 1.0, 1.0,
+                                                   q.h, 1), "gemm"))
+    rec("gemm_kx1_acc", ms, 8.0 * m * (k + 1) + 8.0 * m, 1)
+    A = P()
+    api.check(lib.rails_csr_create(rows, global_rows, global_rows, row_offset, api.iptr(rp),
+                                   api.iptr(ci), api.dptr(v), ctypes.byref(A)), "csr_create")
+    ms = timed(lambda: api.check(lib.rails_csr_spmm(A, 0, q.h, 0, 1, V.h, k), "spmm"))
+    rec("spmm_e1", ms, 12.0 * nnz + 4.0 * (m + 1) + 16.0 * m, 1)
+    lib.rails_csr_free(A)
+    ms = timed(lambda: api.check(lib.rails_mv_axpy(q.h, 1, 0.5, q.h, 0, 1), "axpy"))
+    rec("axpy", ms, 24.0 * m, 1)
+    # CGS2 of column k against the k columns before it (they need not be
+    # orthonormal for the traffic to be the same)
+    ms = timed(lambda: api.check(lib.rails_mv_orthogonalize(V.h, 0, k, k), "cgs2"), reps=4, warm=1)
+    rec("cgs2_1_vs_k", ms, 32.0 * m * k + 128.0 * m, 12)
+    for o in out.values():
+        o["k"] = k
+    V.free(); q.free(); small.free()
+    return out
+
+
+def dist_setup(n_gpus):
+    """torch.distributed (gloo) is the control plane only: rendezvous, barrier,
+    max-over-ranks of the device times, broadcast of the NCCL id.  The data
+    path (halo exchange, all-reduce of the k x e blocks) is NCCL inside
+    librails_cuda.so."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist_mod.init_process_group(backend="gloo", rank=rank, world_size=world)
+        dist = dist_mod
+    return dist, rank, world, local
+
+
+def allreduce_max(dist, x):
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t[0])
+
+
+def cpu_sample(rp, ci, v, n_b, params, B, warmup, steps, budget_s):
+    """The CPU oracle on the same inputs, all host threads; iterations
+    warmup+1 .. warmup+steps, cut short after `budget_s` seconds."""
+    import harness
+    P = dict(params)
+    P["Maximum iterations"] = warmup + steps
+    P["Oracle time limit"] = budget_s
+    o = harness.oracle_solve(rp, ci, v, n_b, P, B=B)
+    sec = o["seconds"]
+    done = len(sec)
+    cores = harness.oracle().oracle_num_threads()
+    if done > warmup + 1:
+        n = done - warmup
+        rate = n / (sec[-1] - sec[warmup - 1]) if warmup > 0 else n / sec[-1]
+        sample = "iterations %d..%d of the same solve, full size" % (warmup + 1, done)
+    else:
+        rate = done / sec[-1]
+        sample = "iterations 1..%d of the same solve, full size (budget hit inside warm-up)" % done
+    return {"value": rate, "unit": "iterations/s", "cores": cores, "kind": "port",
+            "sample": sample, "iterations_run": done, "seconds": float(sec[-1]),
+            "rel_residual_history": [float(x) for x in o["rel"][:done]]}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  The
+    reference's sparse CPU backend (Epetra) cannot be built here, so this is
+    the oracle port (CSR + OpenMP wrappers' arithmetic under the reference's
+    loop), with all host threads; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    kind, g, dim, n_b, params = workload(args)
+    rp, ci, v = problems.build(kind, g, dim)
+    B = np.asfortranarray(np.random.RandomState(1).uniform(-1.0, 1.0, (g ** dim, n_b)))
+    budget = float(os.environ.get("RAILS_BENCH_REF_SECONDS", "150"))
+    t0 = time.time()
+    cb = cpu_sample(rp, ci, v, n_b, params, B, args.warmup, args.steps, budget)
+    line = {
+        "impl": "reference", "metric": "RAILS outer iterations/s", "value": cb["value"],
+        "unit": "iterations/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 / cb["value"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args, kind, g, dim, n_b), "params": params},
+        "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": cb["value"], "unit": "iterations/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.time() - t0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args):
+    from rails_b200 import api
+    dist, rank, world, local = dist_setup(args.gpus)
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch N>1 with torch.distributed.run)"
+                         % (args.gpus, world))
+    api.init(local)
+    lib = api.cuda()
+    api.host()
+    if world > 1:
+        ident = [None]
+        if rank == 0:
+            buf = ctypes.create_string_buffer(128)
+            api.check(lib.rails_cuda_comm_unique_id(buf), "comm_unique_id")
+            ident[0] = buf.raw
+        dist.broadcast_object_list(ident, src=0)
+        api.check(lib.rails_cuda_comm_init(rank, world, ident[0]), "comm_init")
+
+    kind, g, dim, n_b, params = workload(args)
+    m = g ** dim
+    r0, r1 = problems.partition_rows(m, world, rank)
+    rows = r1 - r0
+    rp, ci, v = problems.build(kind, g, dim, r0, r1)
+    # B on the host (so that it is an uploaded input), same for every arm
+    B_full = np.random.RandomState(1).uniform(-1.0, 1.0, (m, n_b))
+    B = np.asfortranarray(B_full[r0:r1])
+    W, K = args.warmup, args.steps
+    P = dict(params)
+    P["Maximum iterations"] = W + K
+    cap = W + K + 2 * int(P.get("Expand size", 3)) + 2
+
+    sampler = ClockSampler(local)
+    if dist is not None:
+        dist.barrier()
+    lib.rails_cuda_sync()
+    if rank == 0:
+        sampler.start()
+    t0 = time.time()
+    res = api.solve(rp, ci, v, n_b, P, B=B, global_rows=m, row_offset=r0, v_cap_cols=cap,
+                    time_from=W, time_to=W + K)
+    lib.rails_cuda_sync()
+    if dist is not None:
+        dist.barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    if res["ret"] >= 100:
+        raise SystemExit("rails_host_solve failed with code %d" % res["ret"])
+    if res["timed_ms"] <= 0.0:
+        raise SystemExit("the solve ended after %d iterations, before the timed window "
+                         "[%d, %d] closed: use a larger workload or fewer steps"
+                         % (res["iterations"], W + 1, W + K))
+    timed_ms = allreduce_max(dist, res["timed_ms"])
+    wall = allreduce_max(dist, t1 - t0)
+    h2d = rp.nbytes + ci.nbytes + v.nbytes + B.nbytes
+    d2h = rows * res["k"] * 8 + res["k"] * res["k"] * 8
+    h2d_total = allreduce_max(dist, float(h2d)) * world
+    d2h_total = allreduce_max(dist, float(d2h)) * world
+
+    kernels = None
+    if not args.no_kernels:
+        kernels = time_kernels(api, rows, rp, ci, v, m, r0)
+    if rank != 0:
+        return
+
+    import json as _json
+    peaks = {}
+    try:
+        peaks = _json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650"
+    roofline = None
+    if kernels:
+        dk = kernels["dot_kx1"]
+        traffic = None
+        try:
+            traffic = _json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("dot_kx1")
+        except Exception:
+            pass
+        roofline = {"bound": "hbm", "kernel": "dot_kernel (V'q, k=%d, m=%d rows)" % (dk["k"], rows),
+                    "achieved": dk["gbs"], "peak": peak, "unit": "GB/s", "frac": dk["gbs"] / peak,
+                    "traffic": traffic, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": dk["bytes"], "ms_per_launch": dk["ms"]}
+
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        cb = cpu_sample(rp, ci, v, n_b, params, B, W, K, args.cpu_seconds)
+        cpu_baseline = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        n = min(cb["iterations_run"], res["iterations"])
+        ref_rel = np.array(cb["rel_residual_history"][:n])
+        cpu_baseline["history_rel_diff_vs_gpu"] = float(
+            np.max(np.abs(ref_rel - res["rel"][:n]) / ref_rel))
+
+    value = K / (timed_ms / 1e3)
+    line = {
+        "metric": "RAILS outer iterations/s", "value": value, "unit": "iterations/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": timed_ms / K,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": workload_name(args, kind, g, dim, n_b), "params": params,
+                   "l2": "inputs >> L2 (no flush): V is %.0f MB per column" % (rows * 8 / 1e6),
+                   "parallelism": "row partition over %d GPU(s)" % world,
+                   "space_size_in_window": [int(res["space"][W]) if W < len(res["space"]) else None,
+                                            int(res["space"][min(W + K, len(res["space"])) - 1])]},
+        "e2e": {"value": (W + K) / wall, "unit": "iterations/s",
+                "h2d_bytes_per_step": h2d_total / (W + K), "d2h_bytes_per_step": d2h_total / (W + K),
+                "what": "rails_host_solve with host CSR/B in, V/T out; %d iterations in %.3f s"
+                        % (W + K, wall)},
+        "gpu_launches": int(res["timed_launches"]),
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu_baseline,
+        "kernels": kernels,
+        "dense_solve_seconds": res["dense_solve_seconds"],
+        "solve_seconds": res["solve_seconds"], "setup_seconds": res["setup_seconds"],
+        "relative_residual": [float(res["rel"][0]), float(res["rel"][-1])],
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

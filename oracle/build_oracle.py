@@ -24,8 +24,8 @@ def build(force=False):
     libdir, blas = openblas_path()
     cmd = ["g++", "-std=c++14", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-fopenmp",
            "-o", out] + srcs + [blas, "-Wl,--disable-new-dtags,-rpath," + libdir]
-    print("+", " ".join(cmd), flush=True)
-    subprocess.check_call(cmd)
+    print("+", " ".join(cmd), file=sys.stderr, flush=True)
+    subprocess.check_call(cmd, stdout=sys.stderr)
     return out
 
 

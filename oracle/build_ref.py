@@ -44,8 +44,8 @@ def openblas_path():
 
 
 def run(cmd):
-    print("+", " ".join(cmd), flush=True)
-    subprocess.check_call(cmd)
+    print("+", " ".join(cmd), file=sys.stderr, flush=True)
+    subprocess.check_call(cmd, stdout=sys.stderr)
 
 
 def build(verbose=True):

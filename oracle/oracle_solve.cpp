@@ -142,6 +142,9 @@ extern "C" int oracle_solve(
     const double restart_tol = P.get("Restart tolerance", tol * 1e-3);
     const bool minimize = P.get("Minimize solution space", 1.0) != 0.0;
     const bool warm = P.get("Restart from solution", 0.0) != 0.0;
+    // checker-only key (bench.py's bounded CPU samples): stop with code -2
+    // after the first iteration that ends later than this many seconds
+    const double time_limit = P.get("Oracle time limit", 0.0);
     if (L <= expand_size)
         return 101;
 
@@ -279,6 +282,9 @@ extern "C" int oracle_solve(
         }
         nhist++;
         if (hist_len) *hist_len = nhist;
+
+        if (time_limit > 0.0 && sec > time_limit)
+            return finish(-2);
 
         const bool converged = std::abs(res) < tol * r0 * r0;
         if (converged || iter + 1 >= max_iter || kV >= m)

@@ -51,6 +51,7 @@ def host():
             raise RuntimeError("librails_host.so is not built: run `python -m rails_b200.build`")
         lib = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
         lib.rails_host_last_sections.restype = ctypes.c_char_p
+        lib.rails_host_last_timed_launches.restype = ctypes.c_longlong
         _host = lib
     return _host
 
@@ -195,7 +196,8 @@ def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, r
     out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
                space=hk[:n].copy(), seconds=hs[:n].copy(), timed_ms=tm.value,
                solve_seconds=ss.value, setup_seconds=su.value, dense_solve_seconds=sd.value,
-               sections=lib.rails_host_last_sections().decode())
+               sections=lib.rails_host_last_sections().decode(),
+               timed_launches=lib.rails_host_last_timed_launches())
     if V is not None and k.value <= v_cap_cols:
         out["V"] = V[:, :k.value]
         out["T"] = T[:k.value, :k.value]

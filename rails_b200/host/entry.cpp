@@ -44,6 +44,7 @@ public:
 typedef b200::Solver<CudaOperatorWrapper, CudaMultiVectorWrapper, HostDenseMatrix> CudaSolver;
 
 std::string g_sections;
+long long g_timed_launches = 0;
 
 }
 
@@ -111,13 +112,25 @@ int rails_host_solve(int rows, int global_rows, int row_offset,
     HostDenseMatrix T;
 
     bool have_start = false, have_stop = false;
+    long long launches_start = 0, launches_stop = 0;
     solver.set_observer([&](b200::IterationRecord const &rec) {
         if (rec.iteration == time_from)
+        {
             have_start = rails_cuda_event_record(0) == 0;
+            launches_start = rails_cuda_kernel_launches();
+        }
         if (rec.iteration == time_to)
+        {
             have_stop = rails_cuda_event_record(1) == 0;
+            launches_stop = rails_cuda_kernel_launches();
+        }
     });
     rails_cuda_sync();
+    if (time_from == 0 && time_to > 0)
+    {
+        have_start = rails_cuda_event_record(0) == 0;
+        launches_start = rails_cuda_kernel_launches();
+    }
     auto t0 = std::chrono::steady_clock::now();
     if (setup_seconds)
         *setup_seconds = std::chrono::duration<double>(t0 - t_setup).count();
@@ -133,6 +146,7 @@ int rails_host_solve(int rows, int global_rows, int row_offset,
         if (have_start && have_stop)
             rails_cuda_event_elapsed_ms(0, 1, timed_ms);
     }
+    g_timed_launches = have_start && have_stop ? launches_stop - launches_start : 0;
 
     auto const &hist = solver.history();
     if (hist_len)
@@ -170,5 +184,8 @@ int rails_host_solve(int rows, int global_rows, int row_offset,
 
 // "name=seconds;" list of the last solve's host-side section totals
 const char *rails_host_last_sections(void) { return g_sections.c_str(); }
+
+// kernels launched between the two timing marks of the last solve
+long long rails_host_last_timed_launches(void) { return g_timed_launches; }
 
 }

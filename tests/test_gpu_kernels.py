@@ -1,0 +1,287 @@
+"""GPU parity tests, kernel by kernel, through the C ABI (include/rails_cuda.h)
+against the CPU oracle on the same seeded inputs.
+
+Bars: bit-exact for random() and the SpMM (both are order-defined in the
+reference: the minstd stream of src/StlWrapper.cpp:414-423 and the CSR row sum
+y_i = sum_j a_ij x_j); 1e-13 * (sum of |terms|) for the reductions (the GPU
+sums in a different, fixed order) and the fma-accumulated V*C products.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+import harness
+from rails_b200 import problems
+
+pytestmark = pytest.mark.gpu
+
+LL = ctypes.c_longlong
+
+
+def _csr(api, rp, ci, v, m, ncols_global=None):
+    A = ctypes.c_void_p()
+    n = m if ncols_global is None else ncols_global
+    api.check(api.cuda().rails_csr_create(m, m, n, 0, api.iptr(rp), api.iptr(ci), api.dptr(v),
+                                          ctypes.byref(A)), "csr_create")
+    return A
+
+
+@pytest.mark.parametrize("m,n,seed", [(7, 3, 1), (1000, 1, 12345), (33, 4, 2147483647), (5, 2, 0)])
+def test_random_bit_exact_vs_reference_golden(gpu, golden, m, n, seed):
+    libc = ctypes.CDLL(None)
+    libc.srand(ctypes.c_uint(seed))
+    s = libc.rand()
+    mv = gpu.MultiVector(m, n)
+    gpu.check(gpu.cuda().rails_mv_random(mv.h, 0, n, 0, ctypes.c_uint(s)), "random")
+    assert np.array_equal(mv.numpy(), golden["rng_%d_%d_%d" % (m, n, seed)])
+    # a row block with an offset (row partition) reproduces the same rows
+    half = gpu.MultiVector(m - m // 2, n)
+    # the block is filled as rows [m//2, m) of the GLOBAL m x n fill
+    gpu.check(gpu.cuda().rails_mv_random(half.h, 0, n, m // 2, ctypes.c_uint(s)), "random")
+    assert np.array_equal(half.numpy(), golden["rng_%d_%d_%d" % (m, n, seed)][m // 2:])
+
+
+def test_random_large_vs_oracle(gpu):
+    m, n, s = 300001, 3, 1804289383
+    mv = gpu.MultiVector(m, n)
+    gpu.check(gpu.cuda().rails_mv_random(mv.h, 0, n, 0, ctypes.c_uint(s)), "random")
+    a = np.zeros((m, n), order="F")
+    harness.oracle().oracle_random(LL(m), n, ctypes.c_uint(s), LL(0), LL(m), harness.dptr(a), LL(m))
+    assert np.array_equal(mv.numpy(), a)
+
+
+@pytest.mark.parametrize("kind,g,dim", [("laplacian", 33, 2), ("convdiff", 17, 3), ("laplacian", 1, 2)])
+@pytest.mark.parametrize("e", [1, 2, 3, 4, 7, 16])
+def test_spmm_bit_exact(gpu, kind, g, dim, e):
+    rp, ci, v = problems.build(kind, g, dim)
+    m = rp.size - 1
+    rs = np.random.RandomState(e)
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, e)))
+    Yo = np.zeros((m, e), order="F")
+    harness.oracle().oracle_spmm(m, harness.iptr(rp), harness.iptr(ci), harness.dptr(v), e,
+                                 harness.dptr(X), LL(m), harness.dptr(Yo), LL(m))
+    A = _csr(gpu, rp, ci, v, m)
+    Xd, Yd = gpu.MultiVector.from_numpy(X), gpu.MultiVector(m, e + 1)
+    gpu.check(gpu.cuda().rails_csr_spmm(A, 0, Xd.h, 0, e, Yd.h, 1), "spmm")
+    assert np.array_equal(Yd.numpy(1, e), Yo)
+    gpu.cuda().rails_csr_free(A)
+
+
+def test_spmm_transpose_and_irregular_rows(gpu):
+    # random sparse rectangular matrix with empty rows and one very long row
+    rs = np.random.RandomState(3)
+    m, n = 700, 900
+    dense = np.where(rs.uniform(size=(m, n)) < 0.01, rs.uniform(-1, 1, (m, n)), 0.0)
+    dense[5, :] = rs.uniform(-1, 1, n)          # long row
+    dense[10:20, :] = 0.0                       # empty rows
+    rp = np.zeros(m + 1, dtype=np.int32)
+    ci, v = [], []
+    for i in range(m):
+        nz = np.nonzero(dense[i])[0]
+        ci.extend(nz); v.extend(dense[i, nz]); rp[i + 1] = len(ci)
+    ci, v = np.array(ci, dtype=np.int32), np.array(v, dtype=np.float64)
+    A = ctypes.c_void_p()
+    gpu.check(gpu.cuda().rails_csr_create(m, m, n, 0, gpu.iptr(rp), gpu.iptr(ci), gpu.dptr(v),
+                                          ctypes.byref(A)), "csr_create")
+    X = np.asfortranarray(rs.uniform(-1, 1, (n, 3)))
+    Xd, Yd = gpu.MultiVector.from_numpy(X), gpu.MultiVector(m, 3)
+    gpu.check(gpu.cuda().rails_csr_spmm(A, 0, Xd.h, 0, 3, Yd.h, 0), "spmm")
+    assert np.max(np.abs(Yd.numpy() - dense @ X)) < 1e-12
+    Z = np.asfortranarray(rs.uniform(-1, 1, (m, 2)))
+    Zd, Wd = gpu.MultiVector.from_numpy(Z), gpu.MultiVector(n, 2)
+    gpu.check(gpu.cuda().rails_csr_spmm(A, 1, Zd.h, 0, 2, Wd.h, 0), "spmm^T")
+    assert np.max(np.abs(Wd.numpy() - dense.T @ Z)) < 1e-12
+    nrm = ctypes.c_double(0)
+    gpu.check(gpu.cuda().rails_csr_norm2(A, ctypes.byref(nrm)), "norm2")
+    assert abs(nrm.value - np.linalg.norm(dense, 2)) < 1e-6 * nrm.value
+    gpu.cuda().rails_csr_free(A)
+
+
+@pytest.mark.parametrize("m", [1, 2, 15, 511, 512, 513, 4099, 100003])
+@pytest.mark.parametrize("a,b", [(1, 1), (5, 1), (1, 5), (3, 2), (37, 1), (1, 200), (200, 1),
+                                 (16, 16), (9, 4), (130, 3)])
+def test_dot_vs_oracle(gpu, m, a, b):
+    rs = np.random.RandomState(m % 1000 + a * 7 + b)
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, a)))
+    Y = np.asfortranarray(rs.uniform(-1, 1, (m, b)))
+    Go = np.zeros((a, b), order="F")
+    harness.oracle().oracle_dot(LL(m), a, harness.dptr(X), LL(m), b, harness.dptr(Y), LL(m),
+                                harness.dptr(Go))
+    Xd, Yd = gpu.MultiVector.from_numpy(X), gpu.MultiVector.from_numpy(Y)
+    G = np.full((a + 2, b), 7.0, order="F")      # leading dimension larger than a
+    gpu.check(gpu.cuda().rails_mv_dot(Xd.h, 0, a, Yd.h, 0, b, gpu.dptr(G), a + 2), "dot")
+    bound = 1e-13 * (np.abs(X).T @ np.abs(Y) + 1.0)
+    assert np.all(np.abs(G[:a] - Go) <= bound)
+    assert np.all(G[a:] == 7.0)
+
+
+def test_dot_is_deterministic(gpu):
+    rs = np.random.RandomState(11)
+    m = 1 << 20
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, 6)))
+    Xd = gpu.MultiVector.from_numpy(X)
+    G1, G2 = np.zeros((6, 6), order="F"), np.zeros((6, 6), order="F")
+    gpu.check(gpu.cuda().rails_mv_dot(Xd.h, 0, 6, Xd.h, 0, 6, gpu.dptr(G1), 6), "dot")
+    gpu.check(gpu.cuda().rails_mv_dot(Xd.h, 0, 6, Xd.h, 0, 6, gpu.dptr(G2), 6), "dot")
+    assert np.array_equal(G1, G2)
+    assert np.max(np.abs(G1 - X.T @ X)) < 1e-13 * m
+
+
+def test_dot_dev_stays_on_device(gpu):
+    rs = np.random.RandomState(2)
+    m = 5000
+    B = np.asfortranarray(rs.uniform(-1, 1, (m, 4)))
+    q = np.asfortranarray(rs.uniform(-1, 1, (m, 1)))
+    Bd, qd = gpu.MultiVector.from_numpy(B), gpu.MultiVector.from_numpy(q)
+    Y = gpu.MultiVector(4, 1, replicated=True)
+    gpu.check(gpu.cuda().rails_mv_dot_dev(Bd.h, 0, 4, qd.h, 0, 1, Y.h, 0), "dot_dev")
+    assert np.max(np.abs(Y.numpy() - B.T @ q)) < 1e-12
+    # B * Y with the coefficients taken from the device block
+    out = gpu.MultiVector(m, 1)
+    gpu.check(gpu.cuda().rails_mv_gemm_dev(Bd.h, 0, 4, Y.h, 0, 1, 1.0, 0.0, out.h, 0), "gemm_dev")
+    assert np.max(np.abs(out.numpy() - B @ (B.T @ q))) < 1e-11
+
+
+@pytest.mark.parametrize("m", [1, 3, 512, 1025, 70001])
+@pytest.mark.parametrize("k,c", [(1, 1), (7, 1), (64, 1), (200, 1), (257, 1), (10, 2), (11, 3),
+                                 (20, 4), (12, 8), (21, 11), (40, 30)])
+def test_gemm_vs_oracle(gpu, m, k, c):
+    rs = np.random.RandomState(k * 31 + c)
+    V = np.asfortranarray(rs.uniform(-1, 1, (m, k)))
+    C = np.asfortranarray(rs.uniform(-1, 1, (k + 1, c)))      # ldc > k
+    O0 = np.asfortranarray(rs.uniform(-1, 1, (m, c)))
+    for alpha, beta in [(1.0, 0.0), (-1.0, 1.0), (0.5, 1.0)]:
+        Oo = O0.copy(order="F")
+        harness.oracle().oracle_gemm(LL(m), k, harness.dptr(V), LL(m), harness.dptr(C), k + 1, c,
+                                     ctypes.c_double(alpha), ctypes.c_double(beta),
+                                     harness.dptr(Oo), LL(m))
+        Vd, Od = gpu.MultiVector.from_numpy(V), gpu.MultiVector.from_numpy(O0)
+        gpu.check(gpu.cuda().rails_mv_gemm(Vd.h, 0, k, gpu.dptr(C), k + 1, c, alpha, beta,
+                                           Od.h, 0), "gemm")
+        bound = 1e-13 * (np.abs(V) @ np.abs(C[:k]) + np.abs(O0) + 1.0)
+        assert np.all(np.abs(Od.numpy() - Oo) <= bound)
+
+
+def test_gemm_rejects_overlap(gpu):
+    V = gpu.MultiVector(100, 8)
+    C = np.zeros((4, 2), order="F")
+    rc = gpu.cuda().rails_mv_gemm(V.h, 0, 4, gpu.dptr(C), 4, 2, 1.0, 0.0, V.h, 3)
+    assert rc == 2
+    rc = gpu.cuda().rails_mv_gemm(V.h, 0, 4, gpu.dptr(C), 4, 2, 1.0, 0.0, V.h, 4)
+    assert rc == 0
+
+
+def test_blas1_family(gpu):
+    lib = gpu.cuda()
+    rs = np.random.RandomState(4)
+    for m in (1, 2, 9, 1000, 65537):
+        X = np.asfortranarray(rs.uniform(-1, 1, (m, 5)))
+        Y = np.asfortranarray(rs.uniform(-1, 1, (m, 5)))
+        Xd, Yd = gpu.MultiVector.from_numpy(X), gpu.MultiVector.from_numpy(Y)
+        gpu.check(lib.rails_mv_scal(Xd.h, 1, 3, 0.3), "scal")
+        Xe = X.copy(); Xe[:, 1:4] *= 0.3
+        assert np.array_equal(Xd.numpy(), Xe)
+        gpu.check(lib.rails_mv_axpy(Yd.h, 0, -1.0, Xd.h, 2, 2), "axpy")
+        Ye = Y.copy(); Ye[:, 0:2] -= Xe[:, 2:4]
+        assert np.array_equal(Yd.numpy(), Ye)
+        gpu.check(lib.rails_mv_axpy(Yd.h, 3, 0.7, Xd.h, 0, 1), "axpy")
+        assert np.max(np.abs(Yd.numpy()[:, 3] - (Ye[:, 3] + 0.7 * Xe[:, 0]))) < 1e-15
+        Ye = Yd.numpy()
+        gpu.check(lib.rails_mv_add_scaled(Yd.h, 4, -1.0, 0.123, Xd.h, 4, 1), "add_scaled")
+        assert np.array_equal(Yd.numpy()[:, 4], Ye[:, 4] - 0.123 * Xe[:, 4])
+        gpu.check(lib.rails_mv_scaled_copy(Yd.h, 0, 2.5, Xd.h, 1, 2), "scaled_copy")
+        assert np.array_equal(Yd.numpy()[:, 0:2], 2.5 * Xe[:, 1:3])
+        gpu.check(lib.rails_mv_fill(Yd.h, 2, 2, -4.25), "fill")
+        assert np.all(Yd.numpy()[:, 2:4] == -4.25)
+        assert np.array_equal(Yd.numpy()[:, 4], Ye[:, 4] - 0.123 * Xe[:, 4])
+        gpu.check(lib.rails_mv_copy_cols(Yd.h, 1, Xd.h, 0, 3), "copy_cols")
+        assert np.array_equal(Yd.numpy()[:, 1:4], Xe[:, 0:3])
+        out = ctypes.c_double(0)
+        gpu.check(lib.rails_mv_norm_inf(Xd.h, 0, 5, ctypes.byref(out)), "norm_inf")
+        assert out.value == harness.oracle().oracle_norm_inf(LL(m), 5, harness.dptr(np.asfortranarray(Xe)), LL(m))
+        val = ctypes.c_double(0)
+        gpu.check(lib.rails_mv_set(Xd.h, m - 1, 4, 3.5), "set")
+        gpu.check(lib.rails_mv_get(Xd.h, m - 1, 4, ctypes.byref(val)), "get")
+        assert val.value == 3.5
+
+
+def test_argument_errors_are_reported_not_fatal(gpu):
+    lib = gpu.cuda()
+    X = gpu.MultiVector(10, 2)
+    Y = gpu.MultiVector(11, 2)
+    assert lib.rails_mv_axpy(Y.h, 0, 1.0, X.h, 0, 1) == 2          # row mismatch
+    assert lib.rails_mv_fill(X.h, 1, 2, 0.0) == 2                  # range
+    G = np.zeros((2, 2), order="F")
+    assert lib.rails_mv_dot(X.h, 0, 2, Y.h, 0, 2, gpu.dptr(G), 2) == 2
+    assert b"rows" in lib.rails_cuda_last_error()
+    # empty shapes are fine
+    E = gpu.MultiVector(0, 3)
+    assert lib.rails_mv_fill(E.h, 0, 3, 1.0) == 0
+    assert lib.rails_mv_dot(E.h, 0, 3, E.h, 0, 3, gpu.dptr(np.zeros((3, 3), order="F")), 3) == 0
+
+
+def test_cgs2_known_answer_and_golden(gpu, golden):
+    lib = gpu.cuda()
+    # test/GenericMultiVectorWrapper_test.cpp:270-311
+    X = np.zeros((10, 2), order="F")
+    X[0, 0], X[0, 1], X[1, 1] = 2.3, 5.3, 2.7
+    Xd = gpu.MultiVector.from_numpy(X)
+    gpu.check(lib.rails_mv_orthogonalize(Xd.h, 0, 0, 1), "orthogonalize")
+    E = np.zeros((10, 2)); E[0, 0] = E[1, 1] = 1.0
+    assert np.max(np.abs(Xd.numpy() - E)) <= 4 * np.finfo(float).eps
+    # reference CGS2 output on a random 50 x 6 block
+    Xd = gpu.MultiVector.from_numpy(golden["cgs2_in"])
+    gpu.check(lib.rails_mv_orthogonalize(Xd.h, 0, 0, 5), "orthogonalize")
+    Q = Xd.numpy()
+    assert np.max(np.abs(Q - golden["cgs2_out"])) < 1e-14
+    assert np.max(np.abs(Q.T @ Q - np.eye(6))) < 1e-14
+
+
+@pytest.mark.parametrize("m,k,first", [(100003, 12, 0), (100003, 40, 37), (2000, 130, 120)])
+def test_cgs2_vs_oracle(gpu, m, k, first):
+    rs = np.random.RandomState(k)
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, k)))
+    if first:
+        X[:, :first] = np.linalg.qr(X[:, :first])[0]
+    Xo = X.copy(order="F")
+    harness.oracle().oracle_orthogonalize(LL(m), k, harness.dptr(Xo), LL(m), first)
+    Xd = gpu.MultiVector.from_numpy(X)
+    gpu.check(gpu.cuda().rails_mv_orthogonalize(Xd.h, 0, first, k - 1), "orthogonalize")
+    Q = Xd.numpy()
+    assert np.max(np.abs(Q - Xo)) < 1e-12
+    assert np.max(np.abs(Q.T @ Q - np.eye(k))) < 1e-13
+    assert np.array_equal(Q[:, :first], X[:, :first])
+
+
+def test_linearity_at_full_size(gpu):
+    """Size-independent properties at the C3 row count (m = 256^3), where the
+    oracle is too slow to be the checker: A(x + 2y) = Ax + 2Ay on the 3-D
+    Laplacian, <x, A y> = <A x, y> (symmetry), V'(V c) = (V'V) c."""
+    lib = gpu.cuda()
+    g = 256
+    rp, ci, v = problems.laplacian(g, 3)
+    m = rp.size - 1
+    A = _csr(gpu, rp, ci, v, m)
+    X = gpu.MultiVector(m, 4)
+    gpu.check(lib.rails_mv_random(X.h, 0, 2, 0, ctypes.c_uint(99)), "random")
+    gpu.check(lib.rails_mv_copy_cols(X.h, 2, X.h, 0, 1), "copy")
+    gpu.check(lib.rails_mv_axpy(X.h, 2, 2.0, X.h, 1, 1), "axpy")          # col2 = x + 2y
+    Y = gpu.MultiVector(m, 4)
+    gpu.check(lib.rails_csr_spmm(A, 0, X.h, 0, 3, Y.h, 0), "spmm")
+    gpu.check(lib.rails_mv_axpy(Y.h, 2, -1.0, Y.h, 0, 1), "axpy")
+    gpu.check(lib.rails_mv_axpy(Y.h, 2, -2.0, Y.h, 1, 1), "axpy")
+    out = ctypes.c_double(0)
+    gpu.check(lib.rails_mv_norm_inf(Y.h, 2, 1, ctypes.byref(out)), "norm_inf")
+    assert out.value < 1e-13 * 12 * 3
+    G = np.zeros((2, 2), order="F")
+    gpu.check(lib.rails_mv_dot(X.h, 0, 2, Y.h, 0, 2, gpu.dptr(G), 2), "dot")
+    assert abs(G[0, 1] - G[1, 0]) < 1e-12 * m
+    # one row of A x checked on the host: interior row
+    r = g * g * 5 + g * 7 + 9
+    xs = X.numpy(0, 1)[:, 0]
+    want = -6 * xs[r] + xs[r - 1] + xs[r + 1] + xs[r - g] + xs[r + g] + xs[r - g * g] + xs[r + g * g]
+    got = ctypes.c_double(0)
+    gpu.check(lib.rails_mv_get(Y.h, r, 0, ctypes.byref(got)), "get")
+    assert abs(got.value - want) < 1e-14
+    lib.rails_csr_free(A)

@@ -57,6 +57,10 @@ def parse_args():
                     help="override the grid size g of the workload (testing)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true")
+    ap.add_argument("--kernels-only", action="store_true",
+                    help="only the per-kernel timings (the command profiled with ncu --set full)")
+    ap.add_argument("--kernel-k", type=int, default=64)
+    ap.add_argument("--kernel-reps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=25.0,
                     help="time budget of the bounded CPU sample")
     return ap.parse_args()
@@ -288,6 +292,11 @@ def run_b200(args):
     # B on the host (so that it is an uploaded input), same for every arm
     B_full = np.random.RandomState(1).uniform(-1.0, 1.0, (m, n_b))
     B = np.asfortranarray(B_full[r0:r1])
+    if args.kernels_only:
+        kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps)
+        if rank == 0:
+            print(json.dumps({"kernels": kernels, "rows": rows}), flush=True)
+        return
     W, K = args.warmup, args.steps
     P = dict(params)
     P["Maximum iterations"] = W + K
@@ -322,7 +331,7 @@ def run_b200(args):
 
     kernels = None
     if not args.no_kernels:
-        kernels = time_kernels(api, rows, rp, ci, v, m, r0)
+        kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps)
     if rank != 0:
         return
 

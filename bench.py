@@ -394,6 +394,21 @@ def run_b200(args):
 
 def main():
     args = parse_args()
+    # The contract is ONE JSON line on stdout.  Native libraries (NCCL's
+    # version banner, build recipes) write to file descriptor 1 directly, so
+    # fd 1 is pointed at stderr for the duration of the run and the JSON line
+    # goes to the saved descriptor.
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    out = os.fdopen(saved, "w")
+    real_print = print
+
+    def emit(*a, **kw):
+        kw["file"] = out
+        real_print(*a, **kw)
+        out.flush()
+    globals()["print"] = emit
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -183,6 +183,24 @@ def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
     # orthonormal for the traffic to be the same)
     ms = timed(lambda: api.check(lib.rails_mv_orthogonalize(V.h, 0, k, k), "cgs2"), reps=4, warm=1)
     rec("cgs2_1_vs_k", ms, 32.0 * m * k + 128.0 * m, 12)
+    # fused Lanczos step kernels on [V(:, :k/2), V(:, k/2:k), q1] (2 * (k/2) + 1 columns)
+    h = k // 2
+    hs = (P * 3)(V.h, V.h, q.h)
+    c0 = (ctypes.c_int * 3)(0, h, 1)
+    nn = (ctypes.c_int * 3)(h, h, 1)
+    g = np.zeros(2 * h + 1)
+    cf = np.full(2 * h + 1, 1e-3)
+    al = ctypes.c_double(0)
+    ms = timed(lambda: api.check(lib.rails_mv_multi_dot(3, hs, c0, nn, q.h, 0, 1.0, api.dptr(g)), "multi_dot"))
+    rec("multi_dot", ms, 8.0 * m * (2 * h + 2), 2)
+    ms = timed(lambda: api.check(lib.rails_mv_multi_dot(3, hs, c0, nn, q.h, 0, 1.0000001, api.dptr(g)), "multi_dot"))
+    rec("multi_dot_scale_q", ms, 8.0 * m * (2 * h + 3), 2)
+    ms = timed(lambda: api.check(lib.rails_mv_multi_gemv(3, hs, c0, nn, api.dptr(cf), V.h, k, q.h, 0,
+                                                         ctypes.byref(al)), "multi_gemv"))
+    rec("multi_gemv_alpha", ms, 8.0 * m * (2 * h + 3), 2)
+    ms = timed(lambda: api.check(lib.rails_mv_lanczos_update(V.h, k, 1e-3, q.h, 0, 1e-3, q.h, 1,
+                                                             ctypes.byref(al)), "update"))
+    rec("lanczos_update", ms, 32.0 * m, 2)
     for o in out.values():
         o["k"] = k
     V.free(); q.free(); small.free()

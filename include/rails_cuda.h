@@ -134,6 +134,29 @@ int rails_mv_gemm(rails_mv_t V, int vc0, int k, const double *C, int ldc, int c,
 int rails_mv_gemm_dev(rails_mv_t V, int vc0, int k, rails_mv_t C, int cc0, int c,
                       double alpha, double beta, rails_mv_t Out, int oc0);
 
+/* ---- fused residual-Lanczos step (Solver::resid_lanczos,
+ *      src/LyapunovSolver.hpp:384-434).  Up to 4 column blocks
+ *      X_b[:, xc0_b : xc0_b + xn_b) -- in the solver [V, AV, B] -- are treated
+ *      as one wide multivector so that each is streamed once per kernel. ----- */
+/* out (host, sum_b xn_b doubles, block after block) = [X_0 X_1 ..]' (qscale * q[:, qc]);
+ * when qscale != 1 the scaled column is written back in the same pass (the
+ * `q /= beta` of :431, deferred from the previous step).  Replaces the three
+ * dots of :389,394,400. */
+int rails_mv_multi_dot(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                       rails_mv_t q, int qc, double qscale, double *out);
+/* out[:, oc] = sum_b X_b * coef_b  (coef: the blocks' coefficient vectors
+ * concatenated, host); with q != NULL also *alpha = out[:, oc]' q[:, qc].
+ * Replaces `next = B*Y; next += AV*Z; next += V*Z; alpha = next.dot(q)`
+ * (:390,396,402,406). */
+int rails_mv_multi_gemv(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                        const double *coef, rails_mv_t out, int oc,
+                        rails_mv_t q, int qc, double *alpha);
+/* next[:, nc] -= alpha * q[:, qc]; next[:, nc] -= beta * p[:, pc] (p may be
+ * NULL); *norm = |next[:, nc]|_2.  Each product is rounded before it is
+ * subtracted, as the scaled temporaries of :411-413 are; the norm is :417. */
+int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, rails_mv_t q, int qc,
+                            double beta, rails_mv_t p, int pc, double *norm);
+
 /* ---- Gram-Schmidt: column-wise CGS2 of columns [first, last] against all
  *      earlier columns (StlWrapper::orthogonalize :305-321), executed as one
  *      device-side chain with no host round trip. ------------------------ */

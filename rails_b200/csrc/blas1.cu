@@ -126,18 +126,24 @@ __device__ __forceinline__ unsigned long long powmod31(unsigned long long base, 
     return r;
 }
 
+// Thread t fills rows t, t + stride, ...: one jump-ahead power per thread for
+// its first row, then the state at the start of the next row is the current
+// row start times `jump` = a^(2 * ncols * stride) (computed on the host).
 __global__ void __launch_bounds__(EW_THREADS)
 random_kernel(double *__restrict__ x, long long ld, long long rows, int ncols,
-              long long row_offset, unsigned long long x0)
+              long long row_offset, unsigned long long x0, unsigned long long jump)
 {
     const double R = 2147483646.0;
     const double R2 = 4611686009837453316.0;   // double(R*R), exact product rounded
-    for (long long i = (long long)blockIdx.x * EW_THREADS + threadIdx.x; i < rows;
-         i += (long long)gridDim.x * EW_THREADS)
+    long long i = (long long)blockIdx.x * EW_THREADS + threadIdx.x;
+    if (i >= rows)
+        return;
+    const unsigned long long first = 2ull * (unsigned long long)(row_offset + i) * (unsigned long long)ncols;
+    // state after `first` draws
+    unsigned long long row_state = mulmod31(powmod31(LCG_A, first), x0);
+    for (; i < rows; i += (long long)gridDim.x * EW_THREADS)
     {
-        unsigned long long first = 2ull * (unsigned long long)(row_offset + i) * (unsigned long long)ncols;
-        // state after `first` draws
-        unsigned long long s = mulmod31(powmod31(LCG_A, first), x0);
+        unsigned long long s = row_state;
         for (int j = 0; j < ncols; ++j)
         {
             s = mulmod31(s, LCG_A);
@@ -150,7 +156,26 @@ random_kernel(double *__restrict__ x, long long ld, long long rows, int ncols,
                 u = 0.99999999999999989;        // nextafter(1, 0), as libstdc++
             x[i + (size_t)j * ld] = __dadd_rn(__dmul_rn(u, 2.0), -1.0);
         }
+        row_state = mulmod31(row_state, jump);
     }
+}
+
+unsigned long long host_mulmod31(unsigned long long a, unsigned long long b)
+{
+    return (unsigned long long)((unsigned __int128)a * b % LCG_P);
+}
+
+unsigned long long host_powmod31(unsigned long long base, unsigned long long e)
+{
+    unsigned long long r = 1;
+    base %= LCG_P;
+    while (e)
+    {
+        if (e & 1ull) r = host_mulmod31(r, base);
+        base = host_mulmod31(base, base);
+        e >>= 1;
+    }
+    return r;
 }
 
 int ew_grid(long long work)
@@ -264,8 +289,11 @@ extern "C" int rails_mv_random(rails_mv_t mv, int col0, int ncols, long long row
     // linear_congruential_engine(seed): state = seed mod p, 0 -> 1
     unsigned long long x0 = (unsigned long long)seed % LCG_P;
     if (x0 == 0) x0 = 1;
-    RAILS_LAUNCH(random_kernel, ew_grid(mv->rows), EW_THREADS, 0,
-                 mv->data + (size_t)col0 * mv->ld, mv->ld, mv->rows, ncols, row_offset, x0);
+    const int grid = ew_grid(mv->rows);
+    const unsigned long long stride = (unsigned long long)grid * EW_THREADS;
+    const unsigned long long jump = host_powmod31(LCG_A, 2ull * (unsigned long long)ncols * stride);
+    RAILS_LAUNCH(random_kernel, grid, EW_THREADS, 0,
+                 mv->data + (size_t)col0 * mv->ld, mv->ld, mv->rows, ncols, row_offset, x0, jump);
     RAILS_CHECK_LAUNCH();
     return RAILS_OK;
 }

@@ -1,0 +1,549 @@
+// Fused kernels for one step of the residual Lanczos recurrence
+// (Solver::resid_lanczos, /root/reference/src/LyapunovSolver.hpp:384-434):
+//
+//     g    = [V AV B]' q                         rails_mv_multi_dot
+//     next = V z_V + AV z_AV + B y ; a = next'q  rails_mv_multi_gemv
+//     next -= a q + b q_prev ; b' = |next|       rails_mv_lanczos_update
+//
+// The reference issues these as ~19 wrapper calls per step (three dots, three
+// V*C products with temporaries, two scaled copies, two axpys, a norm, a
+// scale), i.e. m (32k + 16n + 264) bytes; fused, a step moves
+// m (16 (2k + n) + 64) bytes in three launches: every column of V, AV and B
+// is read exactly twice (once per kernel: the coefficients of the second pass
+// depend on the complete result of the first), q three times, `next` is
+// written twice.  All three are pure HBM streams (<= 0.25 flop/B).
+//
+// Reductions are deterministic: per-warp shuffle trees, per-CTA partials in
+// global memory, a second kernel adds the partials in a fixed order; with a
+// communicator the small result is all-reduced over the ranks (NCCL).
+#include "internal.h"
+
+#include <cmath>
+#include <cstring>
+
+using rails::ctx;
+
+namespace
+{
+
+constexpr int MAX_SEGS = 4;
+constexpr int MD_THREADS = 256;
+constexpr int MD_WARPS = MD_THREADS / 32;
+constexpr int MD_RP = 4;                         // double2 per thread and column
+constexpr long long MD_TILE = 512LL * MD_RP;     // rows per CTA iteration
+constexpr int MD_U = 4;                          // columns in flight
+constexpr int MD_MAXCOLS = 1024;                 // 64 KB of per-warp accumulators
+
+struct Segs
+{
+    const double *p[MAX_SEGS];
+    long long ld[MAX_SEGS];
+    int n[MAX_SEGS];
+    int nseg;
+};
+
+template<bool FULL>
+__device__ __forceinline__ double2 ld2(const double *__restrict__ p, long long r, long long rows)
+{
+    if (FULL)
+        return __ldg(reinterpret_cast<const double2 *>(p + r));
+    double2 v = make_double2(0.0, 0.0);
+    if (r < rows) v.x = __ldg(p + r);
+    if (r + 1 < rows) v.y = __ldg(p + r + 1);
+    return v;
+}
+
+template<bool FULL>
+__device__ __forceinline__ void md_tile(const Segs &S, double *__restrict__ q, double qscale,
+                                        bool write_q, long long rows, long long base,
+                                        double *wacc, int lane)
+{
+    // q tile: scaled on the fly (the pending `q /= beta` of the previous
+    // step, :431) and written back once
+    double2 qv[MD_RP];
+#pragma unroll
+    for (int v = 0; v < MD_RP; ++v)
+    {
+        const long long r = base + v * 512;
+        if (FULL)
+            qv[v] = *reinterpret_cast<const double2 *>(q + r);
+        else
+        {
+            qv[v] = make_double2(0.0, 0.0);
+            if (r < rows) qv[v].x = q[r];
+            if (r + 1 < rows) qv[v].y = q[r + 1];
+        }
+        if (write_q)
+        {
+            qv[v].x *= qscale;
+            qv[v].y *= qscale;
+            if (FULL)
+                *reinterpret_cast<double2 *>(q + r) = qv[v];
+            else
+            {
+                if (r < rows) q[r] = qv[v].x;
+                if (r + 1 < rows) q[r + 1] = qv[v].y;
+            }
+        }
+    }
+
+    int off = 0;
+#pragma unroll
+    for (int s = 0; s < MAX_SEGS; ++s)
+    {
+        if (s >= S.nseg) break;
+        const double *__restrict__ X = S.p[s];
+        const long long ldx = S.ld[s];
+        const int ac = S.n[s];
+        for (int j = 0; j < ac; j += MD_U)
+        {
+            double2 xv[MD_U][MD_RP];
+#pragma unroll
+            for (int u = 0; u < MD_U; ++u)
+            {
+                const int jj = (j + u < ac) ? (j + u) : (ac - 1);
+#pragma unroll
+                for (int v = 0; v < MD_RP; ++v)
+                    xv[u][v] = ld2<FULL>(X + (size_t)jj * ldx, base + v * 512, rows);
+            }
+            double p[MD_U];
+#pragma unroll
+            for (int u = 0; u < MD_U; ++u)
+            {
+                double acc = 0.0;
+#pragma unroll
+                for (int v = 0; v < MD_RP; ++v)
+                {
+                    acc = fma(xv[u][v].x, qv[v].x, acc);
+                    acc = fma(xv[u][v].y, qv[v].y, acc);
+                }
+                p[u] = acc;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                for (int u = 0; u < MD_U; ++u)
+                    p[u] += __shfl_xor_sync(0xffffffffu, p[u], o);
+            if (lane == 0)
+            {
+#pragma unroll
+                for (int u = 0; u < MD_U; ++u)
+                    if (j + u < ac)
+                        wacc[off + j + u] += p[u];
+            }
+        }
+        off += ac;
+    }
+}
+
+// partial[blockIdx.x][c] = sum over this CTA's row tiles of X_c . (qscale q)
+__global__ void __launch_bounds__(MD_THREADS)
+multi_dot_kernel(Segs S, int total, double *__restrict__ q, double qscale, int write_q,
+                 long long rows, double *__restrict__ partial)
+{
+    extern __shared__ double sacc[];
+    for (int i = threadIdx.x; i < total * MD_WARPS; i += MD_THREADS)
+        sacc[i] = 0.0;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double *wacc = sacc + warp * total;
+    const long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+    {
+        const long long base = tile * MD_TILE + 2 * threadIdx.x;
+        if ((tile + 1) * MD_TILE <= rows)
+            md_tile<true>(S, q, qscale, write_q != 0, rows, base, wacc, lane);
+        else
+            md_tile<false>(S, q, qscale, write_q != 0, rows, base, wacc, lane);
+    }
+    __syncthreads();
+    double *out = partial + (size_t)blockIdx.x * total;
+    for (int i = threadIdx.x; i < total; i += MD_THREADS)
+    {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < MD_WARPS; ++w)
+            s += sacc[w * total + i];
+        out[i] = s;
+    }
+}
+
+// out[i] = sum_b partial[b * n + i], one CTA per output, fixed order:
+// thread t adds blocks t, t+256, ...; then a shared-memory tree.
+__global__ void __launch_bounds__(256)
+sum_partials_kernel(const double *__restrict__ partial, int nblocks, int n,
+                    double *__restrict__ out, int take_sqrt)
+{
+    __shared__ double red[256];
+    const int i = blockIdx.x;
+    double s = 0.0;
+    for (int b = threadIdx.x; b < nblocks; b += 256)
+        s += partial[(size_t)b * n + i];
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1)
+    {
+        if (threadIdx.x < w)
+            red[threadIdx.x] += red[threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0)
+        out[i] = take_sqrt ? sqrt(fabs(red[0])) : red[0];
+}
+
+int collect_segs(int nblk, const rails_mv_t *X, const int *xc0, const int *xn, long long rows,
+                 Segs *S, int *total, bool *distributed, const char *what)
+{
+    if (nblk < 1 || nblk > MAX_SEGS || !X || !xc0 || !xn)
+        return rails::fail(RAILS_ERR_ARG, "%s: between 1 and %d column blocks", what, MAX_SEGS);
+    S->nseg = 0;
+    *total = 0;
+    *distributed = false;
+    for (int b = 0; b < nblk; ++b)
+    {
+        if (!X[b] || xc0[b] < 0 || xn[b] < 0 || xc0[b] + xn[b] > X[b]->cols)
+            return rails::fail(RAILS_ERR_ARG, "%s: block %d column range outside capacity", what, b);
+        if (X[b]->rows != rows)
+            return rails::fail(RAILS_ERR_ARG, "%s: block %d has %lld rows, expected %lld", what, b,
+                               X[b]->rows, rows);
+        if (X[b]->flags == RAILS_MV_DISTRIBUTED)
+            *distributed = true;
+        *total += xn[b];
+        if (xn[b] == 0)
+            continue;                 // empty blocks keep their (empty) slot in the output
+        const int s = S->nseg++;
+        S->p[s] = X[b]->data + (size_t)xc0[b] * X[b]->ld;
+        S->ld[s] = X[b]->ld;
+        S->n[s] = xn[b];
+    }
+    return RAILS_OK;
+}
+
+// device result (n doubles at c.d_small) -> all-reduce over ranks -> host
+int finish_to_host(int n, bool distributed, double *out)
+{
+    rails::Context &c = ctx();
+    if (distributed && c.comm)
+        RAILS_NCCL_TRY(ncclAllReduce(c.d_small, c.d_small, (size_t)n, ncclDouble, ncclSum, c.comm, c.stream));
+    RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, (size_t)n * sizeof(double),
+                                   cudaMemcpyDeviceToHost, c.stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    memcpy(out, c.h_small, (size_t)n * sizeof(double));
+    return RAILS_OK;
+}
+
+}
+
+// out (host, sum of xn doubles) = [X_0 X_1 ...]' (qscale * q); when
+// qscale != 1 the scaled q is written back in the same pass.
+extern "C" int rails_mv_multi_dot(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                                  rails_mv_t q, int qc, double qscale, double *out)
+{
+    RAILS_REQUIRE_READY();
+    if (!q || qc < 0 || qc >= q->cols || !out)
+        return rails::fail(RAILS_ERR_ARG, "multi_dot: bad q or result");
+    Segs S;
+    int total = 0;
+    bool dist = false;
+    int rc = collect_segs(nblk, X, xc0, xn, q->rows, &S, &total, &dist, "multi_dot");
+    if (rc) return rc;
+    if (total > MD_MAXCOLS)
+        return rails::fail(RAILS_ERR_ARG, "multi_dot: %d columns, at most %d per call", total, MD_MAXCOLS);
+    for (int s = 0; s < S.nseg; ++s)
+        if (S.p[s] <= q->data + (size_t)qc * q->ld && q->data + (size_t)qc * q->ld < S.p[s] + (size_t)S.n[s] * S.ld[s]
+            && qscale != 1.0)
+            return rails::fail(RAILS_ERR_ARG, "multi_dot: q is rescaled and lies inside a block");
+    rails::Context &c = ctx();
+    const long long rows = q->rows;
+    const int write_q = qscale != 1.0 ? 1 : 0;
+    if (total == 0 && !write_q)
+        return RAILS_OK;
+    rc = rails::ensure_small((size_t)std::max(total, 1));
+    if (rc) return rc;
+    if (rows == 0)
+    {
+        RAILS_CUDA_TRY(cudaMemsetAsync(c.d_small, 0, (size_t)std::max(total, 1) * sizeof(double), c.stream));
+    }
+    else
+    {
+        long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
+        const int nb = (int)std::min<long long>(ntiles, (long long)c.sm_count * 4);
+        rc = rails::ensure_partial((size_t)nb * std::max(total, 1));
+        if (rc) return rc;
+        static bool attr_set = false;
+        if (!attr_set)
+        {
+            RAILS_CUDA_TRY(cudaFuncSetAttribute(multi_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                MD_MAXCOLS * MD_WARPS * (int)sizeof(double)));
+            attr_set = true;
+        }
+        const size_t smem = (size_t)std::max(total, 1) * MD_WARPS * sizeof(double);
+        RAILS_LAUNCH(multi_dot_kernel, nb, MD_THREADS, smem, S, total, q->data + (size_t)qc * q->ld,
+                     qscale, write_q, rows, c.d_partial);
+        RAILS_CHECK_LAUNCH();
+        if (total > 0)
+        {
+            RAILS_LAUNCH(sum_partials_kernel, total, 256, 0, c.d_partial, nb, total, c.d_small, 0);
+            RAILS_CHECK_LAUNCH();
+        }
+    }
+    if (total == 0)
+        return RAILS_OK;
+    return finish_to_host(total, dist && q->flags == RAILS_MV_DISTRIBUTED, out);
+}
+
+namespace
+{
+
+constexpr int MG_THREADS = 256;
+constexpr int MG_RP = 2;              // double2 per thread: 4 rows
+constexpr int MG_U = 8;               // columns in flight
+
+// out = sum_s X_s coef_s  (one output column), optionally partial[blockIdx.x]
+// = sum over this CTA's rows of out * q.  The sum over all columns is one
+// fma chain per row, in block order.
+__global__ void __launch_bounds__(MG_THREADS)
+multi_gemv_kernel(Segs S, int total, const double *__restrict__ coef, double *__restrict__ out,
+                  const double *__restrict__ q, long long rows, double *__restrict__ partial)
+{
+    const long long rows2 = (rows + 1) / 2;
+    extern __shared__ double cs[];
+    __shared__ double red[MG_THREADS / 32];
+    for (int i = threadIdx.x; i < total; i += MG_THREADS)
+        cs[i] = coef[i];
+    __syncthreads();
+
+    long long r2[MG_RP];
+#pragma unroll
+    for (int v = 0; v < MG_RP; ++v)
+        r2[v] = ((long long)blockIdx.x * MG_RP + v) * MG_THREADS + threadIdx.x;
+    double2 acc[MG_RP];
+#pragma unroll
+    for (int v = 0; v < MG_RP; ++v)
+        acc[v] = make_double2(0.0, 0.0);
+
+    int off = 0;
+#pragma unroll
+    for (int s = 0; s < MAX_SEGS; ++s)
+    {
+        if (s >= S.nseg) break;
+        const double2 *__restrict__ X = reinterpret_cast<const double2 *>(S.p[s]);
+        const long long ld2 = S.ld[s] / 2;
+        const int kc = S.n[s];
+        int j = 0;
+        for (; j + MG_U <= kc; j += MG_U)
+        {
+            double2 x[MG_U][MG_RP];
+#pragma unroll
+            for (int u = 0; u < MG_U; ++u)
+#pragma unroll
+                for (int v = 0; v < MG_RP; ++v)
+                    x[u][v] = (r2[v] < rows2) ? __ldg(X + (size_t)(j + u) * ld2 + r2[v])
+                                              : make_double2(0.0, 0.0);
+#pragma unroll
+            for (int u = 0; u < MG_U; ++u)
+            {
+                const double cf = cs[off + j + u];
+#pragma unroll
+                for (int v = 0; v < MG_RP; ++v)
+                {
+                    acc[v].x = fma(x[u][v].x, cf, acc[v].x);
+                    acc[v].y = fma(x[u][v].y, cf, acc[v].y);
+                }
+            }
+        }
+        for (; j < kc; ++j)
+        {
+            const double cf = cs[off + j];
+#pragma unroll
+            for (int v = 0; v < MG_RP; ++v)
+            {
+                const double2 x = (r2[v] < rows2) ? __ldg(X + (size_t)j * ld2 + r2[v])
+                                                  : make_double2(0.0, 0.0);
+                acc[v].x = fma(x.x, cf, acc[v].x);
+                acc[v].y = fma(x.y, cf, acc[v].y);
+            }
+        }
+        off += kc;
+    }
+
+    double dotp = 0.0;
+#pragma unroll
+    for (int v = 0; v < MG_RP; ++v)
+    {
+        if (r2[v] >= rows2) continue;
+        reinterpret_cast<double2 *>(out)[r2[v]] = acc[v];
+        if (q)
+        {
+            const double2 qq = __ldg(reinterpret_cast<const double2 *>(q) + r2[v]);
+            dotp = fma(acc[v].x, qq.x, dotp);
+            if (2 * r2[v] + 1 < rows)          // the pad element of an odd row count stays out
+                dotp = fma(acc[v].y, qq.y, dotp);
+        }
+    }
+    if (q)
+    {
+        for (int o = 16; o > 0; o >>= 1)
+            dotp += __shfl_xor_sync(0xffffffffu, dotp, o);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = dotp;
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            double t = 0.0;
+#pragma unroll
+            for (int w = 0; w < MG_THREADS / 32; ++w) t += red[w];
+            partial[blockIdx.x] = t;
+        }
+    }
+}
+
+constexpr int LU_THREADS = 256;
+
+// next = (next - round(alpha q)) - round(beta p)   (p optional), and
+// partial[blockIdx.x] = sum of next^2 over this CTA's rows (:411-417)
+__global__ void __launch_bounds__(LU_THREADS)
+lanczos_update_kernel(double *__restrict__ next, const double *__restrict__ q,
+                      const double *__restrict__ p, double alpha, double beta, long long rows,
+                      double *__restrict__ partial)
+{
+    __shared__ double red[LU_THREADS / 32];
+    const long long rows2 = rows / 2;
+    double2 *n2 = reinterpret_cast<double2 *>(next);
+    const double2 *q2 = reinterpret_cast<const double2 *>(q);
+    const double2 *p2 = reinterpret_cast<const double2 *>(p);
+    double s = 0.0;
+    for (long long i = (long long)blockIdx.x * LU_THREADS + threadIdx.x; i < rows2;
+         i += (long long)gridDim.x * LU_THREADS)
+    {
+        double2 x = n2[i];
+        const double2 a = __ldg(q2 + i);
+        x.x = __dadd_rn(x.x, -__dmul_rn(alpha, a.x));
+        x.y = __dadd_rn(x.y, -__dmul_rn(alpha, a.y));
+        if (p)
+        {
+            const double2 b = __ldg(p2 + i);
+            x.x = __dadd_rn(x.x, -__dmul_rn(beta, b.x));
+            x.y = __dadd_rn(x.y, -__dmul_rn(beta, b.y));
+        }
+        n2[i] = x;
+        s = fma(x.x, x.x, s);
+        s = fma(x.y, x.y, s);
+    }
+    if ((rows & 1) && blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        const long long r = rows - 1;
+        double x = __dadd_rn(next[r], -__dmul_rn(alpha, q[r]));
+        if (p) x = __dadd_rn(x, -__dmul_rn(beta, p[r]));
+        next[r] = x;
+        s = fma(x, x, s);
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < LU_THREADS / 32; ++w) t += red[w];
+        partial[blockIdx.x] = t;
+    }
+}
+
+}
+
+// out[:, oc] = sum_b X_b[:, xc0_b : xc0_b + xn_b) * coef_b, coef = the blocks'
+// coefficient vectors concatenated (host).  With q != NULL also
+// *alpha = out[:, oc]' q[:, qc] (summed over ranks).
+extern "C" int rails_mv_multi_gemv(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                                   const double *coef, rails_mv_t out, int oc,
+                                   rails_mv_t q, int qc, double *alpha)
+{
+    RAILS_REQUIRE_READY();
+    if (!out || oc < 0 || oc >= out->cols)
+        return rails::fail(RAILS_ERR_ARG, "multi_gemv: bad result column");
+    if (q && (qc < 0 || qc >= q->cols || q->rows != out->rows || !alpha))
+        return rails::fail(RAILS_ERR_ARG, "multi_gemv: bad q");
+    Segs S;
+    int total = 0;
+    bool dist = false;
+    int rc = collect_segs(nblk, X, xc0, xn, out->rows, &S, &total, &dist, "multi_gemv");
+    if (rc) return rc;
+    if (total > MD_MAXCOLS)
+        return rails::fail(RAILS_ERR_ARG, "multi_gemv: %d columns, at most %d per call", total, MD_MAXCOLS);
+    if (total > 0 && !coef)
+        return rails::fail(RAILS_ERR_ARG, "multi_gemv: null coefficients");
+    double *o = out->data + (size_t)oc * out->ld;
+    for (int s = 0; s < S.nseg; ++s)
+        if (S.p[s] <= o && o < S.p[s] + (size_t)S.n[s] * S.ld[s])
+            return rails::fail(RAILS_ERR_ARG, "multi_gemv: result column lies inside a block");
+    rails::Context &c = ctx();
+    const long long rows = out->rows;
+    if (alpha) *alpha = 0.0;
+    if (rows == 0)
+        return RAILS_OK;
+    const double *dC = nullptr;
+    if (total > 0)
+    {
+        rc = rails::upload_small(coef, total, 1, total, &dC);
+        if (rc) return rc;
+    }
+    const long long rows2 = (rows + 1) / 2;
+    const long long per_block = (long long)MG_THREADS * MG_RP;
+    const int nb = (int)((rows2 + per_block - 1) / per_block);
+    rc = rails::ensure_partial((size_t)nb);
+    if (rc) return rc;
+    rc = rails::ensure_small(1);
+    if (rc) return rc;
+    const size_t smem = (size_t)std::max(total, 1) * sizeof(double);
+    RAILS_LAUNCH(multi_gemv_kernel, nb, MG_THREADS, smem, S, total, dC, o,
+                 q ? q->data + (size_t)qc * q->ld : (const double *)nullptr, rows, c.d_partial);
+    RAILS_CHECK_LAUNCH();
+    if (!q)
+        return RAILS_OK;
+    RAILS_LAUNCH(sum_partials_kernel, 1, 256, 0, c.d_partial, nb, 1, c.d_small, 0);
+    RAILS_CHECK_LAUNCH();
+    return finish_to_host(1, out->flags == RAILS_MV_DISTRIBUTED, alpha);
+}
+
+// next[:, nc] -= alpha * q[:, qc];  next[:, nc] -= beta * p[:, pc] (p may be
+// NULL);  *norm = |next[:, nc]|_2 over all ranks
+// (src/LyapunovSolver.hpp:411-417 in one pass)
+extern "C" int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, rails_mv_t q, int qc,
+                                       double beta, rails_mv_t p, int pc, double *norm)
+{
+    RAILS_REQUIRE_READY();
+    if (!next || !q || !norm || nc < 0 || nc >= next->cols || qc < 0 || qc >= q->cols ||
+        q->rows != next->rows)
+        return rails::fail(RAILS_ERR_ARG, "lanczos_update: bad next or q");
+    if (p && (pc < 0 || pc >= p->cols || p->rows != next->rows))
+        return rails::fail(RAILS_ERR_ARG, "lanczos_update: bad p");
+    rails::Context &c = ctx();
+    const long long rows = next->rows;
+    *norm = 0.0;
+    int rc = rails::ensure_small(1);
+    if (rc) return rc;
+    if (rows == 0)
+    {
+        RAILS_CUDA_TRY(cudaMemsetAsync(c.d_small, 0, sizeof(double), c.stream));
+    }
+    else
+    {
+        long long want = (rows / 2 + LU_THREADS - 1) / LU_THREADS;
+        const int nb = (int)std::max<long long>(1, std::min<long long>(want, (long long)c.sm_count * 8));
+        rc = rails::ensure_partial((size_t)nb);
+        if (rc) return rc;
+        RAILS_LAUNCH(lanczos_update_kernel, nb, LU_THREADS, 0, next->data + (size_t)nc * next->ld,
+                     q->data + (size_t)qc * q->ld,
+                     p ? p->data + (size_t)pc * p->ld : (const double *)nullptr, alpha, beta, rows,
+                     c.d_partial);
+        RAILS_CHECK_LAUNCH();
+        RAILS_LAUNCH(sum_partials_kernel, 1, 256, 0, c.d_partial, nb, 1, c.d_small, 0);
+        RAILS_CHECK_LAUNCH();
+    }
+    double sq = 0.0;
+    rc = finish_to_host(1, next->flags == RAILS_MV_DISTRIBUTED, &sq);
+    if (rc) return rc;
+    *norm = std::sqrt(std::fabs(sq));
+    return RAILS_OK;
+}

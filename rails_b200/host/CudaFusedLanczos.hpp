@@ -1,0 +1,120 @@
+// Fused residual-Lanczos recurrence for the CUDA wrappers: the specialisation
+// of RAILS::b200::FusedLanczos that the product loop picks up
+// (RailsSolverImpl.hpp, resid_lanczos).  Same recurrence as
+// /root/reference/src/LyapunovSolver.hpp:384-434, three kernels per step
+// (rails_mv_multi_dot, rails_mv_multi_gemv, rails_mv_lanczos_update; see
+// rails_b200/csrc/lanczos.cu) instead of ~19 wrapper calls:
+//
+//   g = [V AV B]' q                      (the `q /= beta` of the previous step
+//                                         is applied on the fly and written back)
+//   next = V (T AV'q) + AV (T V'q) + B (B'q);   alpha = next' q
+//   next -= alpha q;  next -= beta q_prev;      beta = |next|
+//
+// The k x k products T * (V'q), T * (AV'q) stay on the host, as in the
+// reference.  Set RAILS_FUSED_LANCZOS=0 to run the operation-by-operation
+// sequence instead (A/B comparisons in the tests).
+#ifndef RAILS_B200_CUDAFUSEDLANCZOS_HPP
+#define RAILS_B200_CUDAFUSEDLANCZOS_HPP
+
+#include "CudaMultiVectorWrapper.hpp"
+#include "HostDenseMatrix.hpp"
+#include "RailsSolver.hpp"
+
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <vector>
+
+namespace RAILS
+{
+namespace b200
+{
+
+template<>
+struct FusedLanczos<CudaMultiVectorWrapper, HostDenseMatrix>
+{
+    static const bool enabled = true;
+
+    static bool active()
+    {
+        const char *e = std::getenv("RAILS_FUSED_LANCZOS");
+        return !(e && std::strcmp(e, "0") == 0);
+    }
+
+    static void report(int rc, const char *what)
+    {
+        if (rc)
+            std::cerr << "FusedLanczos::" << what << " failed (" << rc << "): "
+                      << rails_cuda_last_error() << std::endl;
+    }
+
+    // Q holds the un-normalised random start vector in column 0 and has room
+    // for max_iter + 1 columns.  Returns the number of Lanczos steps.
+    static int run(CudaMultiVectorWrapper const &AV, CudaMultiVectorWrapper const &V,
+                   HostDenseMatrix const &T, CudaMultiVectorWrapper const &B,
+                   HostDenseMatrix &H, CudaMultiVectorWrapper &Q, int max_iter)
+    {
+        const int k = V.N(), n = B.N();
+        if (AV.N() != k || T.M() != k || T.N() != k)
+        {
+            std::cerr << "FusedLanczos: inconsistent sizes" << std::endl;
+            return 0;
+        }
+        // `Q.view(0) /= Q.norm()` (:375): the reciprocal is rounded first, the
+        // scaling itself happens inside the first multi_dot
+        double qscale = 1.0 / Q.norm();
+
+        Q.resize(max_iter + 1);
+        rails_mv_t hq = Q.device_handle();
+        const int q0 = Q.device_col0();
+        rails_mv_t blocks[3] = {V.device_handle(), AV.device_handle(), B.device_handle()};
+        int col0[3] = {V.device_col0(), AV.device_col0(), B.device_col0()};
+        int ncols[3] = {k, k, n};
+
+        std::vector<double> g(2 * k + n), coef(2 * k + n);
+        HostDenseMatrix Z(k, 1);
+        double alpha = 0.0, beta = 0.0;
+        int steps = 0;
+        for (int i = 0; i < max_iter; i++)
+        {
+            const int cq = q0 + steps, cn = q0 + steps + 1;
+            report(rails_mv_multi_dot(3, blocks, col0, ncols, hq, cq, qscale, g.data()), "multi_dot");
+
+            // coefficient of V is T * (AV'q), of AV is T * (V'q), of B is B'q
+            for (int j = 0; j < k; ++j) Z(j, 0) = g[j];
+            HostDenseMatrix TZ = T * Z;
+            for (int j = 0; j < k; ++j) coef[k + j] = TZ(j, 0);
+            for (int j = 0; j < k; ++j) Z(j, 0) = g[k + j];
+            TZ = T * Z;
+            for (int j = 0; j < k; ++j) coef[j] = TZ(j, 0);
+            for (int j = 0; j < n; ++j) coef[2 * k + j] = g[2 * k + j];
+
+            report(rails_mv_multi_gemv(3, blocks, col0, ncols, coef.data(), hq, cn, hq, cq, &alpha),
+                   "multi_gemv");
+            H(steps, steps) = alpha;
+
+            double norm = 0.0;
+            report(rails_mv_lanczos_update(hq, cn, alpha, hq, cq, beta,
+                                           steps > 0 ? hq : (rails_mv_t) nullptr, cq - 1, &norm),
+                   "lanczos_update");
+            beta = norm;
+            if (beta < 1e-14)
+            {
+                steps++;
+                break;
+            }
+            H(steps + 1, steps) = beta;
+            H(steps, steps + 1) = beta;
+            qscale = 1.0 / beta;         // applied by the next step's multi_dot
+            steps++;
+        }
+        // the last `next` is dropped by the caller (Q.resize(steps)), so its
+        // pending scale is never needed
+        return steps;
+    }
+};
+
+}
+}
+
+#endif

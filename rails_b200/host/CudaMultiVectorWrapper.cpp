@@ -285,7 +285,6 @@ CudaMultiVectorWrapper CudaMultiVectorWrapper::view(int m, int n) const
 {
     // view() = all columns, view(i) = column i, view(a, b) = columns a..b
     // inclusive and only when b > 0 (src/StlWrapper.cpp:323-340)
-    materialize();
     int num = 1;
     if (n > 0 && m >= 0)
         num = n - m + 1;
@@ -294,6 +293,25 @@ CudaMultiVectorWrapper CudaMultiVectorWrapper::view(int m, int n) const
         m = 0;
         num = N();
     }
+    if (lazy_ && !lazy_->result && lazy_->has_coef && !lazy_->dev_coef && !transpose_ &&
+        m + num <= n_)
+    {
+        // columns of a pending product V * C are the product with the matching
+        // columns of C: `eigenvectors.view(i)` (src/LyapunovSolver.hpp:339)
+        // then costs one m x 1 product instead of the whole m x L block
+        auto l = std::make_shared<Lazy>(*lazy_);
+        HostDenseMatrix c(lazy_->coef.M(), num);
+        for (int j = 0; j < num; ++j)
+            for (int i = 0; i < lazy_->coef.M(); ++i)
+                c(i, j) = lazy_->coef(i, m + j);
+        l->coef = c;
+        l->n = num;
+        l->result.reset();
+        CudaMultiVectorWrapper out = make_lazy(l);
+        out.orthogonalized_ = 0;
+        return out;
+    }
+    materialize();
     CudaMultiVectorWrapper out;
     out.buf_ = buf_;
     out.col0_ = col0_ + m;
@@ -331,9 +349,24 @@ CudaMultiVectorWrapper CudaMultiVectorWrapper::transpose() const
 
 void CudaMultiVectorWrapper::push_back(CudaMultiVectorWrapper const &other)
 {
-    other.materialize();
     int n = N();
     int other_n = other.N();
+    if (other.lazy_ && !other.lazy_->result && other.lazy_->has_coef && !other.lazy_->dev_coef &&
+        other_n > 0)
+    {
+        // push_back(V * C): the product is formed directly in the new columns
+        std::shared_ptr<Lazy> l = other.lazy_;
+        resize(other_n + n);
+        if (buf_ && !l->reads(buf_.get(), col0_ + n, other_n))
+        {
+            buf_->before_write(col0_ + n, other_n);
+            check(rails_mv_gemm(l->src->h, l->src_col0, l->src_k, l->coef, l->coef.LDA(), other_n,
+                                l->alpha, 0.0, buf_->h, col0_ + n), "push_back(V * C)");
+            return;
+        }
+        n_ = n;                 // fall through to the general path
+    }
+    other.materialize();
     resize(other_n + n);
     if (other_n > 0 && buf_)
         buf_->before_write(col0_ + n, other_n);

@@ -105,6 +105,23 @@ HostDenseMatrix HostDenseMatrix::operator*(HostDenseMatrix const &o) const
     char ta = transpose_ ? 'T' : 'N', tb = o.transpose_ ? 'T' : 'N';
     int mm = M(), nn = o.N(), kk = N();
     int lda = ld_, ldb = o.ld_, ldc = out.ld_;
+    if ((long long)mm * nn * kk <= 200000)
+    {
+        // k x k times k x 1 (Z = T * Z, twice per Lanczos step): a plain loop;
+        // a threaded BLAS would wake its whole pool for ~100 flops
+        const double *a = buf_->data(), *b = o.buf_->data();
+        double *c = out.buf_->data();
+        for (int j = 0; j < nn; ++j)
+            for (int i = 0; i < mm; ++i)
+            {
+                double sum = 0.0;
+                for (int l = 0; l < kk; ++l)
+                    sum += (transpose_ ? a[l + (size_t)i * lda] : a[i + (size_t)l * lda]) *
+                           (o.transpose_ ? b[j + (size_t)l * ldb] : b[l + (size_t)j * ldb]);
+                c[i + (size_t)j * ldc] = sum;
+            }
+        return out;
+    }
     double one = 1.0, zero = 0.0;
     dgemm_(&ta, &tb, &mm, &nn, &kk, &one, buf_->data(), &lda, o.buf_->data(), &ldb, &zero,
            out.buf_->data(), &ldc);

@@ -25,6 +25,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <functional>
 #include <iostream>
 #include <locale>
@@ -64,6 +65,8 @@ public:
     { return is_matrix_ ? matrix_ * x : vector_ * x; }
     MultiVector apply_transposed(MultiVector const &x) const
     { return is_matrix_ ? matrix_.transpose() * x : vector_.transpose() * x; }
+    bool is_multivector() const { return !is_matrix_; }
+    MultiVector const &multivector() const { return vector_; }
 };
 
 // Matrix and MultiVector are one type (StlWrapper, ScalarWrapper)
@@ -79,6 +82,23 @@ public:
     double norm() const { return b_.norm(); }
     Type apply(Type const &x) const { return b_ * x; }
     Type apply_transposed(Type const &x) const { return b_.transpose() * x; }
+    bool is_multivector() const { return true; }
+    Type const &multivector() const { return b_; }
+};
+
+// Customisation point: a backend may supply the whole Lanczos recurrence of
+// resid_lanczos as fused kernels.  The primary template is disabled, so any
+// backend (StlWrapper, ScalarWrapper, ...) runs the operation-by-operation
+// sequence of the reference; CudaFusedLanczos.hpp specialises it for the CUDA
+// wrappers.  run() fills H (steps x steps tridiagonal) and Q (m x steps) and
+// returns the number of steps taken.
+template<class MultiVector, class DenseMatrix>
+struct FusedLanczos
+{
+    static const bool enabled = false;
+    static bool active() { return false; }
+    static int run(MultiVector const &, MultiVector const &, DenseMatrix const &,
+                   MultiVector const &, DenseMatrix &, MultiVector &, int) { return -1; }
 };
 
 struct IterationRecord

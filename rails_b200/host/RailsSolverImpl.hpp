@@ -124,6 +124,18 @@ template<class Matrix, class MultiVector, class DenseMatrix>
 int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix &T)
 {
     const auto t_begin = std::chrono::steady_clock::now();
+    const bool trace = std::getenv("RAILS_TRACE") != nullptr;
+    std::map<std::string, double> traced;
+    auto trace_iteration = [&](int it) {
+        if (!trace) return;
+        std::cerr << "trace " << it << ":";
+        for (auto const &kv : sections_)
+        {
+            std::cerr << " " << kv.first << "=" << 1e3 * (kv.second - traced[kv.first]);
+            traced[kv.first] = kv.second;
+        }
+        std::cerr << std::endl;
+    };
     history_.clear();
     sections_.clear();
 
@@ -208,6 +220,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
                           << res / r0 / r0 << ". The size of the space used "
                           << "for the solution is " << V.N() << std::endl;
             rec.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+            trace_iteration(iter + 1);
             history_.push_back(rec);
             if (observer_)
                 observer_(rec);
@@ -239,6 +252,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
 
             rec.restarted = true;
             rec.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+            trace_iteration(iter + 1);
             history_.push_back(rec);
             if (observer_)
                 observer_(rec);
@@ -283,6 +297,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         W = V.view(cols_before, cols_before + grow_by - 1);
 
         rec.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+        trace_iteration(iter + 1);
         history_.push_back(rec);
         if (observer_)
             observer_(rec);
@@ -339,12 +354,22 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
     MultiVector Q(V, max_iter + 1);
     Q.resize(1);
     Q.random();
-    Q.view(0) /= Q.norm();
 
     H = 0.0;
 
-    double alpha = 0.0, beta = 0.0;
     int steps = 0;
+    if (FusedLanczos<MultiVector, DenseMatrix>::enabled && B_.is_multivector() &&
+        FusedLanczos<MultiVector, DenseMatrix>::active())
+    {
+        // same recurrence, three fused kernels per step (backend-supplied)
+        steps = FusedLanczos<MultiVector, DenseMatrix>::run(AV, V, T, B_.multivector(), H, Q,
+                                                            max_iter);
+    }
+    else
+    {
+    Q.view(0) /= Q.norm();
+
+    double alpha = 0.0, beta = 0.0;
     for (int i = 0; i < max_iter; i++)
     {
         Q.resize(steps + 2);
@@ -384,6 +409,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
 
         next /= beta;
         steps++;
+    }
     }
 
     H.resize(steps, steps);

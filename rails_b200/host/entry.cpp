@@ -8,8 +8,10 @@
 #include "CudaOperatorWrapper.hpp"
 #include "HostDenseMatrix.hpp"
 #include "RailsSolver.hpp"
+#include "CudaFusedLanczos.hpp"
 
 #include <chrono>
+#include <dlfcn.h>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -44,6 +46,23 @@ public:
 typedef b200::Solver<CudaOperatorWrapper, CudaMultiVectorWrapper, HostDenseMatrix> CudaSolver;
 
 std::string g_sections;
+
+// The host BLAS only ever sees k x k matrices (k <= a few hundred): keep its
+// thread pool small.  On a 200-core host OpenBLAS otherwise starts one thread
+// per core the first time a call crosses its threading threshold (measured:
+// a 700 ms stall in the middle of a solve).  RAILS_BLAS_THREADS overrides.
+void limit_blas_threads()
+{
+    static bool done = false;
+    if (done) return;
+    done = true;
+    typedef void (*setter)(int);
+    setter f = (setter)dlsym(RTLD_DEFAULT, "openblas_set_num_threads");
+    if (!f) return;
+    const char *e = std::getenv("RAILS_BLAS_THREADS");
+    int n = e ? std::atoi(e) : 4;
+    if (n > 0) f(n);
+}
 long long g_timed_launches = 0;
 
 }
@@ -79,6 +98,7 @@ int rails_host_solve(int rows, int global_rows, int row_offset,
         std::cerr << "rails_host_solve: rails_cuda_init has not been called" << std::endl;
         return 200;
     }
+    limit_blas_threads();
     auto t_setup = std::chrono::steady_clock::now();
     std::srand(seed);
 

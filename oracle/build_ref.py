@@ -66,6 +66,19 @@ def build(verbose=True):
     run(common + ["-o", os.path.join(OUT, "librails_ref_stl.so"),
                   os.path.join(HERE, "ref_entry_stl.cpp")] + ref_srcs + [shim] + link)
 
+    # reference loop over the product's CUDA wrappers (drop-in proof); links
+    # the product libraries, which must have been built first
+    prod = os.path.join(ROOT, "rails_b200")
+    cuda_entry = os.path.join(HERE, "ref_entry_cuda.cpp")
+    if os.path.exists(os.path.join(prod, "librails_host.so")):
+        loop_srcs = [os.path.join(REF, "src", f) for f in
+                     ("LapackWrapper.cpp", "SlicotWrapper.cpp", "Timer.cpp")]
+        run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-I" + REF, "-I" + HERE,
+             "-I" + os.path.join(prod, "host"), "-I" + os.path.join(ROOT, "include"),
+             "-o", os.path.join(OUT, "librails_refloop_cuda.so"), cuda_entry] + loop_srcs +
+            ["-L" + prod, "-lrails_host", "-lrails_cuda", blas,
+             "-Wl,--disable-new-dtags,-rpath," + libdir + ":$ORIGIN/../../rails_b200"])
+
     csr_entry = os.path.join(HERE, "ref_entry_csr.cpp")
     if os.path.exists(csr_entry):
         # StlWrapper stays the DenseMatrix of this arm, as in the reference

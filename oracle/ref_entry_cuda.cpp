@@ -25,6 +25,8 @@
 
 using namespace RAILS;
 
+extern "C" void rails_host_limit_blas_threads(void);
+
 extern "C" int refloop_cuda_solve(
     int m, const int *rowptr, const int *colidx, const double *vals,
     int n_b, const double *B_in, unsigned seed,
@@ -35,6 +37,7 @@ extern "C" int refloop_cuda_solve(
 {
     if (!rails_cuda_is_initialized())
         return 200;
+    rails_host_limit_blas_threads();      // same k x k BLAS threading as the product entry
     std::srand(seed);
 
     CudaOperatorWrapper A(m, m, rowptr, colidx, vals);

@@ -205,6 +205,11 @@ int rails_host_solve(int rows, int global_rows, int row_offset,
 // "name=seconds;" list of the last solve's host-side section totals
 const char *rails_host_last_sections(void) { return g_sections.c_str(); }
 
+// cap the host BLAS pool as rails_host_solve does (idempotent); exported so
+// that a caller driving the wrappers with its own loop sees the same k x k
+// summation order
+void rails_host_limit_blas_threads(void) { limit_blas_threads(); }
+
 // kernels launched between the two timing marks of the last solve
 long long rails_host_last_timed_launches(void) { return g_timed_launches; }
 

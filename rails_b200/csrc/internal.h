@@ -39,6 +39,7 @@ struct rails_csr_s
     int *blk_row;
     int nblk;
     int max_blk_nnz;
+    int blk_cap;                         // staging capacity (nnz) the blocks were cut for
     // halo plan (distributed only)
     int nghost;                          // ghost rows of X needed here
     std::vector<int> recv_count;         // per peer, ghost rows received

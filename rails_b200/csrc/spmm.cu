@@ -6,11 +6,14 @@
 // src/LyapunovSolver.hpp:146.  Algorithmic traffic:
 // 12 nnz + 4 (m+1) + 16 m e bytes; 1/6 flop per byte per column -> HBM bound.
 //
-// Kernel: rows are cut on the host into blocks of <= 256 rows and
-// <= SPMM_NNZ_CAP non-zeros.  A CTA first stages its block's values and column
-// indices into shared memory with fully coalesced loads (the CSR arrays are
-// read from HBM exactly once per call, whatever the number of columns e), then
-// each thread walks ONE row sequentially out of shared memory for EC columns
+// Kernel: rows are cut on the host into blocks of <= 256 rows whose non-zeros
+// fit a shared-memory stage (sized for the matrix at creation, <= 6144 nnz).
+// Persistent CTAs (SMs x resident CTAs) walk the blocks; one thread moves the
+// NEXT block's values and column indices into the other stage with two 1-D
+// bulk copies (cp.async.bulk + mbarrier, the TMA engine) while the CTA computes
+// the current block, so the CSR arrays are read from HBM exactly once per call,
+// whatever the number of columns e, without passing through registers.  Each
+// thread then walks ONE row sequentially out of shared memory for EC columns
 // of X at a time.  Row sums are therefore accumulated in CSR order with a
 // separately rounded multiply and add, which makes the result bit-identical
 // to the scalar CPU loop y_i = sum_j a_ij x_j of the oracle.  Gathers from X
@@ -30,88 +33,184 @@ using rails::ctx;
 namespace
 {
 
-constexpr int SPMM_THREADS = 256;
-constexpr int SPMM_NNZ_CAP = 3072;      // 36 KB of shared memory per CTA
+constexpr int SPMM_THREADS = 256;       // rows per block (one thread per row)
+constexpr int SPMM_STAGES = 2;
+constexpr int SPMM_NNZ_CAP_MAX = 6144;  // largest staging buffer (nnz per block)
 
-template<int EC>
+// ---- mbarrier / bulk-copy (TMA 1-D) primitives --------------------------
+__device__ __forceinline__ unsigned smem_u32(const void *p)
+{
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy, completion counted in bytes on `bar`
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// Persistent CTAs walk the row blocks cyclically (block b, b + grid, ...), so
+// that at any moment the whole GPU works on one narrow band of rows and the
+// gathers from X are served by L2.  One thread issues the two bulk copies of
+// the NEXT block (values, column indices) into the other stage while the CTA
+// computes the current one: the CSR arrays never pass through registers and
+// every SM keeps tens of KB of loads in flight.
+//
+// Shared memory per stage: cap + 2 doubles, then cap + 4 ints.  Bulk copies
+// need 16-byte aligned addresses and sizes, so a copy starts at the aligned
+// element at or before p0 (the arrays carry 64 bytes of slack at the end).
+template<int EC, bool GHOST>
 __global__ void __launch_bounds__(SPMM_THREADS)
 spmm_kernel(const int *__restrict__ rowptr, const int *__restrict__ colidx,
-            const double *__restrict__ vals, const int *__restrict__ blk_row,
+            const double *__restrict__ vals, const int *__restrict__ blk_row, int nblk, int cap,
             const double *__restrict__ X, long long ldx, long long nlocal,
             const double *__restrict__ G, long long ldg,
             double *__restrict__ Y, long long ldy, int ncols)
 {
-    __shared__ double sv[SPMM_NNZ_CAP];
-    __shared__ int sc[SPMM_NNZ_CAP];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ unsigned long long full[SPMM_STAGES];
     __shared__ double red[SPMM_THREADS / 32];
 
-    const int r0 = blk_row[blockIdx.x], r1 = blk_row[blockIdx.x + 1];
-    const int p0 = rowptr[r0], p1 = rowptr[r1];
-    const int nnzb = p1 - p0;
+    const size_t v_bytes = (size_t)(cap + 2) * sizeof(double);
+    const size_t stage_bytes = v_bytes + (size_t)(cap + 4) * sizeof(int);   // multiple of 16
+    const int tid = threadIdx.x;
 
-    if (nnzb <= SPMM_NNZ_CAP)
+    if (tid == 0)
     {
-        for (int i = threadIdx.x; i < nnzb; i += SPMM_THREADS)
-        {
-            sv[i] = __ldg(vals + p0 + i);
-            sc[i] = __ldg(colidx + p0 + i);
-        }
-        __syncthreads();
-        const int row = r0 + threadIdx.x;
-        if (row >= r1)
-            return;
-        const int a = rowptr[row] - p0, e = rowptr[row + 1] - p0;
-        for (int c0 = 0; c0 < ncols; c0 += EC)
-        {
-            double acc[EC];
-#pragma unroll
-            for (int t = 0; t < EC; ++t)
-                acc[t] = 0.0;
-            for (int p = a; p < e; ++p)
-            {
-                const int col = sc[p];
-                const double v = sv[p];
-                const double *xp;
-                long long ld;
-                if (col < nlocal) { xp = X + col; ld = ldx; }
-                else              { xp = G + (col - nlocal); ld = ldg; }
-#pragma unroll
-                for (int t = 0; t < EC; ++t)
-                    if (EC == 1 || c0 + t < ncols)
-                        acc[t] = __dadd_rn(acc[t], __dmul_rn(v, __ldg(xp + (size_t)(c0 + t) * ld)));
-            }
-#pragma unroll
-            for (int t = 0; t < EC; ++t)
-                if (EC == 1 || c0 + t < ncols)
-                    Y[row + (size_t)(c0 + t) * ldy] = acc[t];
-        }
+        for (int s = 0; s < SPMM_STAGES; ++s)
+            mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    else
-    {
-        // a single row longer than the staging buffer: whole CTA on one row
-        const int row = r0;
-        for (int c = 0; c < ncols; ++c)
+    __syncthreads();
+
+    auto issue = [&](int b, int s) {
+        const int r0 = blk_row[b], r1 = blk_row[b + 1];
+        const int p0 = rowptr[r0], p1 = rowptr[r1];
+        if (p1 - p0 > cap || p1 == p0)
         {
-            double s = 0.0;
-            for (int p = p0 + threadIdx.x; p < p1; p += SPMM_THREADS)
+            mbar_arrive(&full[s]);      // nothing staged: a long single row, or an empty block
+            return;
+        }
+        unsigned char *base = smem_raw + (size_t)s * stage_bytes;
+        const int pv = p0 & ~1, pc = p0 & ~3;
+        const unsigned bv = (unsigned)(((p1 - pv) * 8 + 15) & ~15);
+        const unsigned bc = (unsigned)(((p1 - pc) * 4 + 15) & ~15);
+        mbar_expect_tx(&full[s], bv + bc);
+        bulk_g2s(base, vals + pv, bv, &full[s]);
+        bulk_g2s(base + v_bytes, colidx + pc, bc, &full[s]);
+    };
+
+    int blk = blockIdx.x;
+    if (tid == 0 && blk < nblk)
+        issue(blk, 0);
+
+    for (int it = 0; blk < nblk; blk += gridDim.x, ++it)
+    {
+        const int s = it & (SPMM_STAGES - 1);
+        if (tid == 0 && blk + (int)gridDim.x < nblk)
+            issue(blk + gridDim.x, s ^ 1);
+
+        const int r0 = blk_row[blk], r1 = blk_row[blk + 1];
+        const int p0 = rowptr[r0], p1 = rowptr[r1];
+        const int row = r0 + tid;
+        int a = 0, e = 0;
+        if (row < r1)
+        {
+            a = rowptr[row];
+            e = rowptr[row + 1];
+        }
+        mbar_wait(&full[s], (unsigned)(it / SPMM_STAGES) & 1u);
+
+        if (p1 - p0 <= cap)
+        {
+            const unsigned char *base = smem_raw + (size_t)s * stage_bytes;
+            const double *sv = reinterpret_cast<const double *>(base) - (p0 & ~1);
+            const int *sc = reinterpret_cast<const int *>(base + v_bytes) - (p0 & ~3);
+            if (row < r1)
             {
-                const int col = __ldg(colidx + p);
-                const double x = col < nlocal ? __ldg(X + col + (size_t)c * ldx)
-                                              : __ldg(G + (col - nlocal) + (size_t)c * ldg);
-                s = fma(__ldg(vals + p), x, s);
-            }
-            for (int off = 16; off > 0; off >>= 1)
-                s += __shfl_xor_sync(0xffffffffu, s, off);
-            __syncthreads();
-            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
-            __syncthreads();
-            if (threadIdx.x == 0)
-            {
-                double tot = 0.0;
-                for (int w = 0; w < SPMM_THREADS / 32; ++w) tot += red[w];
-                Y[row + (size_t)c * ldy] = tot;
+                for (int c0 = 0; c0 < ncols; c0 += EC)
+                {
+                    double acc[EC];
+#pragma unroll
+                    for (int t = 0; t < EC; ++t)
+                        acc[t] = 0.0;
+#pragma unroll 4
+                    for (int p = a; p < e; ++p)
+                    {
+                        const int col = sc[p];
+                        const double v = sv[p];
+                        const double *xp = X + col;
+                        long long ld = ldx;
+                        if (GHOST && col >= nlocal) { xp = G + (col - nlocal); ld = ldg; }
+                        xp += (size_t)c0 * ld;
+#pragma unroll
+                        for (int t = 0; t < EC; ++t)
+                            if (EC == 1 || c0 + t < ncols)
+                                acc[t] = __dadd_rn(acc[t], __dmul_rn(v, __ldg(xp + (size_t)t * ld)));
+                    }
+#pragma unroll
+                    for (int t = 0; t < EC; ++t)
+                        if (EC == 1 || c0 + t < ncols)
+                            Y[row + (size_t)(c0 + t) * ldy] = acc[t];
+                }
             }
         }
+        else
+        {
+            // a single row longer than the staging buffer: whole CTA on one row
+            for (int c = 0; c < ncols; ++c)
+            {
+                double sum = 0.0;
+                for (int p = p0 + tid; p < p1; p += SPMM_THREADS)
+                {
+                    const int col = __ldg(colidx + p);
+                    const double x = (!GHOST || col < nlocal) ? __ldg(X + col + (size_t)c * ldx)
+                                                              : __ldg(G + (col - nlocal) + (size_t)c * ldg);
+                    sum = fma(__ldg(vals + p), x, sum);
+                }
+                for (int off = 16; off > 0; off >>= 1)
+                    sum += __shfl_xor_sync(0xffffffffu, sum, off);
+                if ((tid & 31) == 0) red[tid >> 5] = sum;
+                __syncthreads();
+                if (tid == 0)
+                {
+                    double tot = 0.0;
+                    for (int w = 0; w < SPMM_THREADS / 32; ++w) tot += red[w];
+                    Y[r0 + (size_t)c * ldy] = tot;
+                }
+                __syncthreads();
+            }
+        }
+        __syncthreads();        // every thread is done with stage s before it is refilled
     }
 }
 
@@ -144,6 +243,12 @@ int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const doubl
 {
     const long long rows = A->rows, nnz = A->nnz;
     // row blocks
+    // staging capacity: what a full block of SPMM_THREADS rows needs, bounded
+    int cap = 256;
+    for (long long r = 0; r < rows; r += SPMM_THREADS)
+        cap = std::max(cap, rowptr[std::min(rows, r + SPMM_THREADS)] - rowptr[r]);
+    cap = std::min((cap + 63) & ~63, SPMM_NNZ_CAP_MAX);
+    A->blk_cap = cap;
     std::vector<int> blk;
     blk.push_back(0);
     int maxnnz = 0;
@@ -152,7 +257,7 @@ int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const doubl
     {
         long long end = std::min(rows, r + SPMM_THREADS);
         // shrink until the block fits the staging buffer (keep >= 1 row)
-        while (end > r + 1 && rowptr[end] - rowptr[r] > SPMM_NNZ_CAP)
+        while (end > r + 1 && rowptr[end] - rowptr[r] > cap)
             --end;
         maxnnz = std::max(maxnnz, rowptr[end] - rowptr[r]);
         blk.push_back((int)end);
@@ -160,8 +265,9 @@ int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const doubl
     }
     A->nblk = (int)blk.size() - 1;
     A->max_blk_nnz = maxnnz;
-    size_t b_rp = (size_t)(rows + 1) * sizeof(int), b_ci = (size_t)std::max<long long>(nnz, 1) * sizeof(int),
-           b_v = (size_t)std::max<long long>(nnz, 1) * sizeof(double), b_blk = blk.size() * sizeof(int);
+    // 64 bytes of slack: bulk copies are rounded up to 16 bytes
+    size_t b_rp = (size_t)(rows + 1) * sizeof(int), b_ci = (size_t)nnz * sizeof(int) + 64,
+           b_v = (size_t)nnz * sizeof(double) + 64, b_blk = blk.size() * sizeof(int);
     RAILS_CUDA_TRY(cudaMalloc(&A->rowptr, b_rp));
     RAILS_CUDA_TRY(cudaMalloc(&A->colidx, b_ci));
     RAILS_CUDA_TRY(cudaMalloc(&A->vals, b_v));
@@ -237,15 +343,32 @@ int launch_spmm(rails_csr_s *A, const double *X, long long ldx, int ncols, doubl
     if (A->rows == 0 || ncols == 0) return RAILS_OK;
     const double *G = A->ghost_buf;
     const long long ldg = A->nghost;
-    if (ncols >= 4)
-        RAILS_LAUNCH(spmm_kernel<4>, A->nblk, SPMM_THREADS, 0, A->rowptr, A->colidx, A->vals, A->blk_row,
-                     X, ldx, A->ncols_local, G, ldg, Y, ldy, ncols);
-    else if (ncols >= 2)
-        RAILS_LAUNCH(spmm_kernel<2>, A->nblk, SPMM_THREADS, 0, A->rowptr, A->colidx, A->vals, A->blk_row,
-                     X, ldx, A->ncols_local, G, ldg, Y, ldy, ncols);
-    else
-        RAILS_LAUNCH(spmm_kernel<1>, A->nblk, SPMM_THREADS, 0, A->rowptr, A->colidx, A->vals, A->blk_row,
-                     X, ldx, A->ncols_local, G, ldg, Y, ldy, ncols);
+    const size_t smem = SPMM_STAGES * ((size_t)(A->blk_cap + 2) * sizeof(double) + (size_t)(A->blk_cap + 4) * sizeof(int));
+#define RAILS_SPMM_CASE(EC, GH)                                                                      \
+    do {                                                                                             \
+        static int per_sm = 0;                                                                       \
+        static size_t attr = 0, sized_for = ~(size_t)0;                                              \
+        if (smem > attr)                                                                             \
+        {                                                                                            \
+            RAILS_CUDA_TRY(cudaFuncSetAttribute(spmm_kernel<EC, GH>,                                 \
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            attr = smem;                                                                             \
+        }                                                                                            \
+        if (smem != sized_for)                                                                       \
+        {                                                                                            \
+            RAILS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmm_kernel<EC, GH>, \
+                                                                         SPMM_THREADS, smem));       \
+            sized_for = smem;                                                                        \
+        }                                                                                            \
+        const int grid = std::min(A->nblk, std::max(per_sm, 1) * rails::ctx().sm_count);             \
+        RAILS_LAUNCH((spmm_kernel<EC, GH>), grid, SPMM_THREADS, smem, A->rowptr, A->colidx, A->vals, \
+                     A->blk_row, A->nblk, A->blk_cap, X, ldx, A->ncols_local, G, ldg, Y, ldy, ncols); \
+    } while (0)
+    const bool gh = A->nghost > 0;
+    if (ncols >= 4)      { if (gh) RAILS_SPMM_CASE(4, true); else RAILS_SPMM_CASE(4, false); }
+    else if (ncols >= 2) { if (gh) RAILS_SPMM_CASE(2, true); else RAILS_SPMM_CASE(2, false); }
+    else                 { if (gh) RAILS_SPMM_CASE(1, true); else RAILS_SPMM_CASE(1, false); }
+#undef RAILS_SPMM_CASE
     RAILS_CHECK_LAUNCH();
     return RAILS_OK;
 }

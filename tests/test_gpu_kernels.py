@@ -68,6 +68,38 @@ def test_spmm_bit_exact(gpu, kind, g, dim, e):
     gpu.cuda().rails_csr_free(A)
 
 
+def test_spmm_row_longer_than_the_staging_buffer(gpu):
+    # one row with 7000 non-zeros (> the 6144-entry stage): whole-CTA fallback,
+    # surrounded by ordinary rows and an empty block of rows
+    rs = np.random.RandomState(11)
+    m, n = 900, 7000
+    rp = np.zeros(m + 1, dtype=np.int32)
+    ci, v = [], []
+    for i in range(m):
+        if i == 300:
+            cols = np.arange(n)
+        elif 400 <= i < 700:
+            cols = np.zeros(0, dtype=np.int64)
+        else:
+            cols = np.sort(rs.choice(n, size=rs.randint(0, 9), replace=False))
+        ci.extend(cols); v.extend(rs.uniform(-1, 1, cols.size)); rp[i + 1] = len(ci)
+    ci, v = np.array(ci, dtype=np.int32), np.array(v, dtype=np.float64)
+    A = ctypes.c_void_p()
+    gpu.check(gpu.cuda().rails_csr_create(m, m, n, 0, gpu.iptr(rp), gpu.iptr(ci), gpu.dptr(v),
+                                          ctypes.byref(A)), "csr_create")
+    for e in (1, 3):
+        X = np.asfortranarray(rs.uniform(-1, 1, (n, e)))
+        Xd, Yd = gpu.MultiVector.from_numpy(X), gpu.MultiVector(m, e)
+        gpu.check(gpu.cuda().rails_mv_fill(Yd.h, 0, e, ctypes.c_double(7.0)), "fill")
+        gpu.check(gpu.cuda().rails_csr_spmm(A, 0, Xd.h, 0, e, Yd.h, 0), "spmm")
+        ref = np.zeros((m, e))
+        for i in range(m):
+            ref[i] = v[rp[i]:rp[i + 1]] @ X[ci[rp[i]:rp[i + 1]]]
+        assert np.max(np.abs(Yd.numpy() - ref)) < 1e-12
+        assert np.array_equal(Yd.numpy()[400:700], np.zeros((300, e)))
+    gpu.cuda().rails_csr_free(A)
+
+
 def test_spmm_transpose_and_irregular_rows(gpu):
     # random sparse rectangular matrix with empty rows and one very long row
     rs = np.random.RandomState(3)

@@ -178,6 +178,17 @@ int rails_csr_create(long long rows, long long global_rows, long long global_col
                      long long row_offset, const int *rowptr, const int *colidx,
                      const double *vals, rails_csr_t *out);
 int rails_csr_free(rails_csr_t A);
+/* Host-only halo plan of a row-partitioned operator: what Epetra_CrsMatrix's
+ * column map + Epetra_Import hold for the ghost import of
+ * src/Epetra_OperatorWrapper.cpp:87.  local_col[nnz] = column indices
+ * renumbered [owned | ghost]; the *nghost ghost rows in ascending global order
+ * (ghost_global), as row ids in their owner's numbering (ghost_owner_row), and
+ * need_from[nranks] = how many come from each rank.  No CUDA call is made;
+ * rails_csr_create uses it and exchanges the lists over NCCL. */
+int rails_csr_halo_plan(long long rows, long long global_rows, long long row_offset,
+                        int nranks, const int *rowptr, const int *colidx,
+                        int *local_col, int *nghost, int *ghost_global,
+                        int *ghost_owner_row, int *need_from);
 long long rails_csr_rows(rails_csr_t A);
 long long rails_csr_nnz(rails_csr_t A);
 /* Y[:, yc0..yc0+ncols) = op(A) * X[:, xc0..xc0+ncols);  trans != 0 applies A'

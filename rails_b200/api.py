@@ -102,6 +102,8 @@ CUDA_SYMBOLS = [
     ("rails_mv_random", I, [P, I, I, LL, ctypes.c_uint]),
     ("rails_csr_create", I, [LL, LL, LL, LL, c_int_p, c_int_p, c_double_p, ctypes.POINTER(P)]),
     ("rails_csr_free", I, [P]),
+    ("rails_csr_halo_plan", I, [LL, LL, LL, I, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p,
+                                c_int_p]),
     ("rails_csr_rows", LL, [P]),
     ("rails_csr_nnz", LL, [P]),
     ("rails_csr_spmm", I, [P, I, P, I, I, P, I]),

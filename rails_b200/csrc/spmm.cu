@@ -375,6 +375,51 @@ int launch_spmm(rails_csr_s *A, const double *X, long long ldx, int ncols, doubl
 
 }
 
+// Host-only part of the halo plan (no CUDA call; tested on CPU with gloo):
+// renumbers the global column indices of this rank's rows to [owned | ghost],
+// lists the ghost rows in ascending global order (so they are grouped by owner
+// in rank order), their row ids in the owner's local numbering, and how many
+// are needed from each rank.  Arrays of nnz entries are enough for the outputs.
+extern "C" int rails_csr_halo_plan(long long rows, long long global_rows, long long row_offset, int nranks,
+                                   const int *rowptr, const int *colidx, int *local_col, int *nghost,
+                                   int *ghost_global, int *ghost_owner_row, int *need_from)
+{
+    if (rows < 0 || nranks < 1 || !rowptr || !local_col || !nghost || !need_from)
+        return rails::fail(RAILS_ERR_ARG, "halo_plan: bad arguments");
+    const long long nnz = rowptr[rows];
+    std::vector<int> ghosts;
+    for (long long p = 0; p < nnz; ++p)
+    {
+        long long g = colidx[p];
+        if (g < 0 || g >= global_rows)
+            return rails::fail(RAILS_ERR_ARG, "halo_plan: column %lld out of range", g);
+        if (g < row_offset || g >= row_offset + rows)
+            ghosts.push_back((int)g);
+    }
+    std::sort(ghosts.begin(), ghosts.end());
+    ghosts.erase(std::unique(ghosts.begin(), ghosts.end()), ghosts.end());
+    *nghost = (int)ghosts.size();
+    for (long long p = 0; p < nnz; ++p)
+    {
+        long long g = colidx[p];
+        if (g >= row_offset && g < row_offset + rows)
+            local_col[p] = (int)(g - row_offset);
+        else
+            local_col[p] = (int)(rows + (std::lower_bound(ghosts.begin(), ghosts.end(), (int)g) - ghosts.begin()));
+    }
+    for (int p = 0; p < nranks; ++p) need_from[p] = 0;
+    for (size_t i = 0; i < ghosts.size(); ++i)
+    {
+        int p = owner_of(ghosts[i], global_rows, nranks);
+        need_from[p]++;
+        long long b, e;
+        rails_partition_rows(global_rows, nranks, p, &b, &e);
+        if (ghost_global) ghost_global[i] = ghosts[i];
+        if (ghost_owner_row) ghost_owner_row[i] = (int)(ghosts[i] - b);
+    }
+    return RAILS_OK;
+}
+
 extern "C" int rails_csr_create(long long rows, long long global_rows, long long global_cols,
                                 long long row_offset, const int *rowptr, const int *colidx,
                                 const double *vals, rails_csr_t *out)
@@ -421,44 +466,17 @@ extern "C" int rails_csr_create(long long rows, long long global_rows, long long
 
     // ---- row-partitioned: renumber columns [owned | ghost], build halo plan
     A->ncols_local = rows;
-    std::vector<int> ghosts;
-    for (long long p = 0; p < nnz; ++p)
-    {
-        long long g = colidx[p];
-        if (g < 0 || g >= global_cols)
-        {
-            delete A;
-            return rails::fail(RAILS_ERR_ARG, "csr_create: column %lld out of range", g);
-        }
-        if (g < row_offset || g >= row_offset + rows)
-            ghosts.push_back((int)g);
-    }
-    std::sort(ghosts.begin(), ghosts.end());
-    ghosts.erase(std::unique(ghosts.begin(), ghosts.end()), ghosts.end());
-    A->nghost = (int)ghosts.size();
-    std::vector<int> lcol(nnz);
-    for (long long p = 0; p < nnz; ++p)
-    {
-        long long g = colidx[p];
-        if (g >= row_offset && g < row_offset + rows)
-            lcol[p] = (int)(g - row_offset);
-        else
-            lcol[p] = (int)(rows + (std::lower_bound(ghosts.begin(), ghosts.end(), (int)g) - ghosts.begin()));
-    }
+    const int P = c.nranks;
+    std::vector<int> lcol(std::max<long long>(nnz, 1)), ghosts(std::max<long long>(nnz, 1)),
+        ghost_local(std::max<long long>(nnz, 1)), need(P, 0);
+    int nghost = 0;
+    rc = rails_csr_halo_plan(rows, global_rows, row_offset, P, rowptr, colidx, lcol.data(), &nghost,
+                             ghosts.data(), ghost_local.data(), need.data());
+    if (rc) { delete A; return rc; }
+    A->nghost = nghost;
+    ghost_local.resize(nghost);
     rc = upload_csr(A, rowptr, lcol.data(), vals);
     if (rc) { free_csr(A); return rc; }
-
-    const int P = c.nranks;
-    std::vector<int> need(P, 0);
-    std::vector<int> ghost_local(ghosts.size());
-    for (size_t i = 0; i < ghosts.size(); ++i)
-    {
-        int p = owner_of(ghosts[i], global_rows, P);
-        need[p]++;
-        long long b, e;
-        rails_partition_rows(global_rows, P, p, &b, &e);
-        ghost_local[i] = (int)(ghosts[i] - b);       // row id in the owner's numbering
-    }
     A->recv_count = need;
     // need matrix: all[r * P + p] = rows rank r needs from rank p
     int *d_all = nullptr, *d_ids = nullptr;

@@ -1,0 +1,134 @@
+"""CPU tests (gloo, world_size 2 and 3) of the host side of the row-partitioned
+path: the Epetra-style linear map, the halo plan rails_csr_halo_plan builds for
+a rank's rows (column renumbering [owned | ghost], ghost lists grouped by
+owner), and the id exchange rails_csr_create performs over NCCL -- replayed here
+with gloo send/recv pairs.  The distributed SpMM assembled from the plan must equal
+the global SpMM bit for bit (same CSR order within every row).  No GPU and no
+compute entry point of the library is used."""
+import ctypes
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _csr_apply(rp, ci, v, X):
+    Y = np.zeros((rp.size - 1, X.shape[1]))
+    for i in range(rp.size - 1):
+        acc = np.zeros(X.shape[1])
+        for p in range(rp[i], rp[i + 1]):
+            acc = acc + v[p] * X[ci[p]]
+        Y[i] = acc
+    return Y
+
+
+def _exchange(dist, rank, recv_list, send_list):
+    """grouped point-to-point exchange, as the ncclSend/ncclRecv group of the product"""
+    reqs = []
+    for p in range(len(send_list)):
+        if p == rank:
+            continue
+        if send_list[p].numel():
+            reqs.append(dist.isend(send_list[p].contiguous(), p))
+        if recv_list[p].numel():
+            reqs.append(dist.irecv(recv_list[p], p))
+    for r in reqs:
+        r.wait()
+
+
+def _worker(rank, world, port, kind, g, dim, q):
+    try:
+        sys.path.insert(0, ROOT)
+        import torch
+        import torch.distributed as dist
+        from rails_b200 import api, problems
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        lib = api.cuda()
+        m = g ** dim
+        r0, r1 = problems.partition_rows(m, world, rank)
+        rows = r1 - r0
+        rp, ci, v = problems.build(kind, g, dim, r0, r1)
+        nnz = int(rp[-1])
+        lcol = np.zeros(max(nnz, 1), dtype=np.int32)
+        gg = np.zeros(max(nnz, 1), dtype=np.int32)
+        gl = np.zeros(max(nnz, 1), dtype=np.int32)
+        need = np.zeros(world, dtype=np.int32)
+        ng = ctypes.c_int(0)
+        rc = lib.rails_csr_halo_plan(rows, m, r0, world, api.iptr(rp), api.iptr(ci), api.iptr(lcol),
+                                     ctypes.byref(ng), api.iptr(gg), api.iptr(gl), api.iptr(need))
+        assert rc == 0
+        ng = ng.value
+        gg, gl = gg[:ng], gl[:ng]
+        # plan invariants
+        assert need.sum() == ng and need[rank] == 0
+        assert np.all(np.diff(gg) > 0)
+        owned = (ci >= r0) & (ci < r1)
+        assert np.array_equal(lcol[:nnz][owned], ci[owned] - r0)
+        assert np.array_equal(gg[lcol[:nnz][~owned] - rows], ci[~owned])
+        off = 0
+        for p in range(world):
+            b, e = problems.partition_rows(m, world, p)
+            seg = gg[off:off + need[p]]
+            assert np.all((seg >= b) & (seg < e))
+            assert np.array_equal(gl[off:off + need[p]], seg - b)
+            off += need[p]
+
+        # the exchange rails_csr_create does with ncclAllGather + Send/Recv
+        counts = [torch.zeros(world, dtype=torch.int32) for _ in range(world)]
+        dist.all_gather(counts, torch.from_numpy(need.copy()))
+        send_count = [int(counts[p][rank]) for p in range(world)]
+        ids_out = list(torch.from_numpy(gl.copy()).split([int(x) for x in need]))
+        ids_in = [torch.zeros(c, dtype=torch.int32) for c in send_count]
+        _exchange(dist, rank, ids_in, ids_out)
+        send_rows = torch.cat(ids_in).numpy() if world > 1 else np.zeros(0, dtype=np.int32)
+
+        # one halo exchange + local apply, against the global apply
+        e_cols = 3
+        Xg = np.random.RandomState(7).uniform(-1, 1, (m, e_cols))
+        Xl = Xg[r0:r1]
+        packed = torch.from_numpy(np.ascontiguousarray(Xl[send_rows]))
+        ghost_in = [torch.zeros((int(c), e_cols), dtype=torch.float64) for c in need]
+        _exchange(dist, rank, ghost_in, list(packed.split(send_count)))
+        ghost = torch.cat(ghost_in).numpy()
+        assert np.array_equal(ghost, Xg[gg])
+        Y = _csr_apply(rp, lcol, v, np.vstack([Xl, ghost]))
+        rpg, cig, vg = problems.build(kind, g, dim)
+        Yg = _csr_apply(rpg[r0:r1 + 1] - rpg[r0], cig[rpg[r0]:], vg[rpg[r0]:], Xg)
+        assert np.array_equal(Y, Yg)
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, "ok"))
+    except Exception as exc:           # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc() + repr(exc)))
+
+
+@pytest.mark.parametrize("world,kind,g,dim", [(2, "laplacian", 9, 2), (2, "convdiff", 6, 3),
+                                             (3, "laplacian", 5, 3)])
+def test_halo_plan_and_exchange(world, kind, g, dim):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, kind, g, dim, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)

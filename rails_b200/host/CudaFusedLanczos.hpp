@@ -98,6 +98,9 @@ struct FusedLanczos<CudaMultiVectorWrapper, HostDenseMatrix>
                                            steps > 0 ? hq : (rails_mv_t) nullptr, cq - 1, &norm),
                    "lanczos_update");
             beta = norm;
+            if (std::getenv("RAILS_DEBUG_LANCZOS"))
+                std::cerr << "lanczos fused step " << steps << " alpha " << alpha << " beta " << beta
+                          << " g0 " << g[0] << " gB " << g[2 * k] << " qscale " << qscale << std::endl;
             if (beta < 1e-14)
             {
                 steps++;

@@ -397,6 +397,9 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
             next -= beta * Q.view(steps - 1);
 
         beta = next.norm();
+        if (std::getenv("RAILS_DEBUG_LANCZOS"))
+            std::cerr << "lanczos plain step " << steps << " alpha " << alpha << " beta " << beta
+                      << std::endl;
         if (beta < 1e-14)
         {
             // invariant subspace: keep H as it is, cannot normalise

@@ -38,11 +38,19 @@ def main():
         dist.all_gather_object(parts, a)
         return np.vstack(parts)
 
-    for kind, g, dim, n_b, P in [
-        ("laplacian", 24, 3, 1, {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 12,
-                                 "Restart size": 60, "Reduced size": 30}),
+    # strict = the history is reproducible to rounding: the residual operator
+    # has rank 2k+n >= L from the first iteration on, so Lanczos never runs past
+    # a breakdown.  The third case (n = 1, L = 12: rank 3 at k = 1) does break
+    # down; what the reference algorithm returns then is decided by rounding
+    # noise (DESIGN.md "Reproducibility"), so only the converged answer is
+    # compared.
+    for kind, g, dim, n_b, P, strict in [
+        ("laplacian", 24, 3, 2, {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 4,
+                                 "Restart size": 60, "Reduced size": 30}, True),
         ("convdiff", 20, 3, 2, {"Tolerance": 1e-4, "Expand size": 1, "Lanczos iterations": 10,
-                                "Minimize solution space": 0}),
+                                "Minimize solution space": 0}, True),
+        ("laplacian", 24, 3, 1, {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 12,
+                                 "Restart size": 60, "Reduced size": 30}, False),
     ]:
         m = g ** dim
         r0, r1 = problems.partition_rows(m, world, rank)
@@ -75,6 +83,36 @@ def main():
         assert np.max(np.abs(out - ref)) <= 1e-12 * np.max(np.abs(ref)), "distributed dot"
         lib.rails_csr_free(A)
 
+        # 2b. fused Lanczos kernels on row blocks against numpy on the global data
+        rs = np.random.RandomState(11)
+        ks = (5, 5, n_b)
+        mats = [np.asfortranarray(rs.uniform(-1, 1, (m, k))) for k in ks]
+        F = np.hstack(mats)
+        q0 = np.asfortranarray(rs.uniform(-1, 1, (m, 3)))
+        mvs = [api.MultiVector.from_numpy(a[r0:r1]) for a in mats]
+        hs = (ctypes.c_void_p * 3)(*[mv.h for mv in mvs])
+        c0 = (ctypes.c_int * 3)(0, 0, 0)
+        nn = (ctypes.c_int * 3)(*ks)
+        Q = api.MultiVector.from_numpy(q0[r0:r1])
+        gvec = np.zeros(F.shape[1])
+        sc = 1.0 / 3.7
+        api.check(lib.rails_mv_multi_dot(3, hs, c0, nn, Q.h, 1, sc, api.dptr(gvec)), "multi_dot")
+        qs = q0[:, 1] * sc
+        assert np.max(np.abs(gvec - F.T @ qs)) < 1e-11, ("multi_dot", gvec, F.T @ qs)
+        coef = rs.uniform(-1, 1, F.shape[1])
+        alpha = ctypes.c_double(0)
+        api.check(lib.rails_mv_multi_gemv(3, hs, c0, nn, api.dptr(coef), Q.h, 2, Q.h, 1,
+                                          ctypes.byref(alpha)), "multi_gemv")
+        nxt = F @ coef
+        assert abs(alpha.value - nxt @ qs) < 1e-10 * (1 + abs(nxt @ qs)), ("alpha", alpha.value, nxt @ qs)
+        nrm = ctypes.c_double(0)
+        api.check(lib.rails_mv_lanczos_update(Q.h, 2, alpha.value, Q.h, 1, 0.3, Q.h, 0,
+                                              ctypes.byref(nrm)), "update")
+        want = nxt - alpha.value * qs - 0.3 * q0[:, 0]
+        assert abs(nrm.value - np.linalg.norm(want)) < 1e-11 * np.linalg.norm(want), ("beta", nrm.value)
+        got = gather_rows(Q.numpy())
+        assert np.max(np.abs(got[:, 2] - want)) < 1e-12, "update values"
+
         # 3. the solve
         B_full = np.asfortranarray(np.random.RandomState(1).uniform(-1, 1, (m, n_b)))
         d = api.solve(rp, ci, v, n_b, P, B=np.asfortranarray(B_full[r0:r1]), global_rows=m,
@@ -84,6 +122,19 @@ def main():
         if rank == 0:
             import harness
             o = harness.oracle_solve(rpg, cig, vg, n_b, P, B=B_full, v_cap_cols=300)
+            if not strict:
+                assert abs(d["iterations"] - o["iterations"]) <= 0.25 * o["iterations"]
+                dx = harness.lowrank_rel_diff(V, d["T"], o["V"], o["T"])
+                assert dx < 30 * P["Tolerance"], dx
+                print("%s g=%d on %d GPUs (breakdown case): %d vs %d iterations, |dX|/|X| %.1e"
+                      % (kind, g, world, d["iterations"], o["iterations"], dx), flush=True)
+                continue
+            if (d["ret"], d["iterations"], d["k"]) != (o["ret"], o["iterations"], o["k"]):
+                n = min(d["iterations"], o["iterations"])
+                print("history (gpu, oracle, rel diff):", flush=True)
+                for i in range(n):
+                    print(i + 1, d["space"][i], d["rel"][i], o["rel"][i],
+                          "%.1e" % (abs(d["rel"][i] - o["rel"][i]) / o["rel"][i]), flush=True)
             assert (d["ret"], d["iterations"], d["k"]) == (o["ret"], o["iterations"], o["k"]), \
                 (d["iterations"], o["iterations"])
             rel = np.abs(d["rel"] - o["rel"]) / o["rel"]

@@ -30,6 +30,10 @@ int oracle_resid_lanczos(long long m, int k, const double *V, long long ldv, con
                          double *H, int ldh);
 void dsyev_(const char *jobz, const char *uplo, const int *n, double *a, const int *lda,
             double *w, double *work, const int *lwork, int *info);
+void dpotrf_(const char *uplo, const int *n, double *a, const int *lda, int *info);
+void dtrsm_(const char *side, const char *uplo, const char *transa, const char *diag, const int *m,
+            const int *n, const double *alpha, const double *a, const int *lda, double *b,
+            const int *ldb);
 }
 
 namespace
@@ -120,10 +124,47 @@ struct Square
     double &operator()(int i, int j) { return a[i + (size_t)j * ld]; }
 };
 
+// Generalised projected problem A X E + E X A' + C = 0, E = V'MV symmetric
+// positive definite (MATLAB lyap(VAV, VBV, [], VMV), matlab/RAILSsolver.m:381,
+// i.e. SLICOT sg03ad in matlab/mex/lyap.c:55-84).  Restated through the
+// Cholesky factor E = L L':  (L^-1 A L^-T) Y + Y (L^-1 A L^-T)' + L^-1 C L^-T = 0,
+// X = L^-T Y L^-1 -- deliberately a different reduction from the product's
+// (which forms E^-1 A by LU), so that agreement is a real cross-check.
+int generalized_dense_solve(int k, const double *A, int lda, const double *E, int lde,
+                            const double *C, int ldc, double *X, int ldx)
+{
+    if (k == 0) return 0;
+    vec L((size_t)k * k), At((size_t)k * k), Ct((size_t)k * k), Y((size_t)k * k);
+    for (int j = 0; j < k; ++j)
+        for (int i = 0; i < k; ++i)
+        {
+            // symmetrised: V'MV is symmetric up to rounding
+            L[i + (size_t)j * k] = 0.5 * (E[i + (size_t)j * lde] + E[j + (size_t)i * lde]);
+            At[i + (size_t)j * k] = A[i + (size_t)j * lda];
+            Ct[i + (size_t)j * k] = C[i + (size_t)j * ldc];
+        }
+    int info = 0;
+    dpotrf_("L", &k, L.data(), &k, &info);
+    if (info) return 1000 + info;
+    const double one = 1.0;
+    // At <- L^-1 At L^-T, Ct <- L^-1 Ct L^-T
+    dtrsm_("L", "L", "N", "N", &k, &k, &one, L.data(), &k, At.data(), &k);
+    dtrsm_("R", "L", "T", "N", &k, &k, &one, L.data(), &k, At.data(), &k);
+    dtrsm_("L", "L", "N", "N", &k, &k, &one, L.data(), &k, Ct.data(), &k);
+    dtrsm_("R", "L", "T", "N", &k, &k, &one, L.data(), &k, Ct.data(), &k);
+    info = oracle_dense_solve(k, At.data(), k, Ct.data(), k, Y.data(), k);
+    // X = L^-T Y L^-1
+    dtrsm_("L", "L", "T", "N", &k, &k, &one, L.data(), &k, Y.data(), &k);
+    dtrsm_("R", "L", "N", "N", &k, &k, &one, L.data(), &k, Y.data(), &k);
+    for (int j = 0; j < k; ++j)
+        for (int i = 0; i < k; ++i)
+            X[i + (size_t)j * ldx] = Y[i + (size_t)j * k];
+    return info;
 }
 
-extern "C" int oracle_solve(
+int solve_impl(
     int m, const int *rowptr, const int *colidx, const double *vals,
+    const int *m_rowptr, const int *m_colidx, const double *m_vals,
     int n_b, const double *B_in, unsigned seed,
     int nparams, const char *const *keys, const double *pvals,
     int hist_cap, double *hist_abs, double *hist_rel, int *hist_k, double *hist_sec, int *hist_len,
@@ -145,8 +186,15 @@ extern "C" int oracle_solve(
     // checker-only key (bench.py's bounded CPU samples): stop with code -2
     // after the first iteration that ends later than this many seconds
     const double time_limit = P.get("Oracle time limit", 0.0);
+    // extension following matlab/RAILSsolver.m:368-392 (the C++ reference never
+    // reads M): MV = M V, VMV = V'MV, generalised projected problem,
+    // residual operator AV T MV' + MV T AV' + B B'.  PARITY UNPINNED: no
+    // reference test fixes values for this branch.
+    const bool use_mass = P.get("Use mass matrix", 0.0) != 0.0;
     if (L <= expand_size)
         return 101;
+    if (use_mass && !m_rowptr)
+        return 102;
 
     std::srand(seed);
     const long long ld = m;
@@ -170,8 +218,14 @@ extern "C" int oracle_solve(
 
     int w0 = 0, we = kV;               // W = V(:, w0 : w0+we)
     int kAV = 0;
-    Square VAV, VBV;
+    Square VAV, VBV, VMV;
     VAV.reserve(cap); VBV.reserve(cap);
+    vec MV;
+    if (use_mass)
+    {
+        MV.resize((size_t)ld * cap);
+        VMV.reserve(cap);
+    }
     vec T;
     int kT = 0;
 
@@ -246,6 +300,24 @@ extern "C" int oracle_solve(
                 for (int j = 0; j < we; ++j)
                     VBV(i + kAV, j + kAV) = WBW[i + (size_t)j * we];
             std::memcpy(BV.data() + (size_t)kAV * n_b, BW.data(), BW.size() * sizeof(double));
+            if (use_mass)
+            {
+                double *MW = MV.data() + (size_t)kAV * ld;
+                oracle_spmm(m, m_rowptr, m_colidx, m_vals, we, W, ld, MW, ld);
+                if (kAV > 0)
+                {
+                    vec WMV((size_t)we * kAV);
+                    oracle_dot(m, we, W, ld, kAV, MV.data(), ld, WMV.data());
+                    for (int i = 0; i < we; ++i)
+                        for (int j = 0; j < kAV; ++j)
+                            VMV(i + kAV, j) = WMV[i + (size_t)j * we];
+                }
+                vec VMW((size_t)kV * we);
+                oracle_dot(m, kV, V.data(), ld, we, MW, ld, VMW.data());
+                for (int i = 0; i < kV; ++i)
+                    for (int j = 0; j < we; ++j)
+                        VMV(i, j + kAV) = VMW[i + (size_t)j * kV];
+            }
             kAV = s;
         }
 
@@ -254,14 +326,18 @@ extern "C" int oracle_solve(
             auto t0 = std::chrono::steady_clock::now();
             kT = kAV;
             T.assign((size_t)kT * kT, 0.0);
-            int info = oracle_dense_solve(kT, VAV.a.data(), VAV.ld, VBV.a.data(), VBV.ld, T.data(), kT);
+            int info = use_mass
+                ? generalized_dense_solve(kT, VAV.a.data(), VAV.ld, VMV.a.data(), VMV.ld,
+                                          VBV.a.data(), VBV.ld, T.data(), kT)
+                : oracle_dense_solve(kT, VAV.a.data(), VAV.ld, VBV.a.data(), VBV.ld, T.data(), kT);
             if (info != 0 && info != kT + 1)
                 std::cerr << "oracle: dense solve returned info = " << info << std::endl;
             dense_sec += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         }
 
         // residual Ritz pairs
-        int steps = oracle_resid_lanczos(m, kV, V.data(), ld, AV.data(), ld, T.data(), kT, n_b,
+        int steps = oracle_resid_lanczos(m, kV, use_mass ? MV.data() : V.data(), ld, AV.data(), ld,
+                                         T.data(), kT, n_b,
                                          B.data(), ld, L, (unsigned)std::rand(), Q.data(), ld,
                                          H.data(), L + 1);
         vec Hs((size_t)steps * steps), theta(steps);
@@ -332,6 +408,15 @@ extern "C" int oracle_solve(
             small_mm(true, false, kept, kept, kT, X.data(), kT, t1.data(), kT, t2.data(), kept);
             for (int j = 0; j < kept; ++j)
                 for (int i = 0; i < kept; ++i) VBV(i, j) = t2[i + (size_t)j * kept];
+            if (use_mass)
+            {
+                oracle_gemm(m, kAV, MV.data(), ld, X.data(), kT, kept, 1.0, 0.0, tmp.data(), ld);
+                std::memcpy(MV.data(), tmp.data(), tmp.size() * sizeof(double));
+                small_mm(false, false, kT, kept, kT, VMV.a.data(), VMV.ld, X.data(), kT, t1.data(), kT);
+                small_mm(true, false, kept, kept, kT, X.data(), kT, t1.data(), kT, t2.data(), kept);
+                for (int j = 0; j < kept; ++j)
+                    for (int i = 0; i < kept; ++i) VMV(i, j) = t2[i + (size_t)j * kept];
+            }
             kV = kAV = kept;
             orth = std::min(orth, kept);
             we = 0;
@@ -345,6 +430,7 @@ extern "C" int oracle_solve(
             cap += 100;
             grow(V, ld, cap); grow(AV, ld, cap); grow(BV, n_b, cap);
             VAV.reserve(cap); VBV.reserve(cap);
+            if (use_mass) { grow(MV, ld, cap); VMV.reserve(cap); }
         }
         // new directions: Ritz vectors Q * y of the largest |theta|
         std::vector<int> idx = by_magnitude(theta.data(), steps);
@@ -357,4 +443,34 @@ extern "C" int oracle_solve(
         w0 = cols_before; we = grow_by;
     }
     return finish(1);
+}
+
+}
+
+extern "C" int oracle_solve(
+    int m, const int *rowptr, const int *colidx, const double *vals,
+    int n_b, const double *B_in, unsigned seed,
+    int nparams, const char *const *keys, const double *pvals,
+    int hist_cap, double *hist_abs, double *hist_rel, int *hist_k, double *hist_sec, int *hist_len,
+    int *k_io, int v_cap_cols, double *V_io, double *T_out,
+    double *solve_seconds, double *dense_solve_seconds)
+{
+    return solve_impl(m, rowptr, colidx, vals, nullptr, nullptr, nullptr, n_b, B_in, seed, nparams, keys,
+                      pvals, hist_cap, hist_abs, hist_rel, hist_k, hist_sec, hist_len, k_io, v_cap_cols,
+                      V_io, T_out, solve_seconds, dense_solve_seconds);
+}
+
+// same, with the CSR arrays of a mass matrix M (params "Use mass matrix" = 1)
+extern "C" int oracle_solve_m(
+    int m, const int *rowptr, const int *colidx, const double *vals,
+    const int *m_rowptr, const int *m_colidx, const double *m_vals,
+    int n_b, const double *B_in, unsigned seed,
+    int nparams, const char *const *keys, const double *pvals,
+    int hist_cap, double *hist_abs, double *hist_rel, int *hist_k, double *hist_sec, int *hist_len,
+    int *k_io, int v_cap_cols, double *V_io, double *T_out,
+    double *solve_seconds, double *dense_solve_seconds)
+{
+    return solve_impl(m, rowptr, colidx, vals, m_rowptr, m_colidx, m_vals, n_b, B_in, seed, nparams,
+                      keys, pvals, hist_cap, hist_abs, hist_rel, hist_k, hist_sec, hist_len, k_io,
+                      v_cap_cols, V_io, T_out, solve_seconds, dense_solve_seconds);
 }

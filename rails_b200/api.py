@@ -170,8 +170,9 @@ class MultiVector:
 
 
 def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, row_offset=0,
-          v_cap_cols=0, V0=None, time_from=0, time_to=0, hist_cap=4096):
-    """rails_host_solve through ctypes.  Returns a dict."""
+          v_cap_cols=0, V0=None, time_from=0, time_to=0, hist_cap=4096, M=None):
+    """rails_host_solve_m through ctypes.  M = (rowptr, colidx, vals) of the mass
+    matrix rows of this rank (used with params["Use mass matrix"] = 1).  Returns a dict."""
     lib = host()
     rows = rowptr.size - 1
     global_rows = rows if global_rows is None else global_rows
@@ -191,9 +192,11 @@ def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, r
     tm = ctypes.c_float(0)
     ss, su, sd = ctypes.c_double(0), ctypes.c_double(0), ctypes.c_double(0)
     Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
-    ret = lib.rails_host_solve(
+    mrp, mci, mv = M if M is not None else (None, None, None)
+    ret = lib.rails_host_solve_m(
         ctypes.c_int(rows), ctypes.c_int(global_rows), ctypes.c_int(row_offset),
-        iptr(rowptr), iptr(colidx), dptr(vals), ctypes.c_int(n_b), dptr(Bc), ctypes.c_uint(seed),
+        iptr(rowptr), iptr(colidx), dptr(vals), iptr(mrp), iptr(mci), dptr(mv),
+        ctypes.c_int(n_b), dptr(Bc), ctypes.c_uint(seed),
         ctypes.c_int(len(keys)), karr, dptr(pv), ctypes.c_int(hist_cap), dptr(ha), dptr(hr),
         iptr(hk), dptr(hs), ctypes.byref(hl), ctypes.byref(k), ctypes.c_int(v_cap_cols),
         dptr(V), dptr(T), ctypes.c_int(time_from), ctypes.c_int(time_to), ctypes.byref(tm),

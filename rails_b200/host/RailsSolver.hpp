@@ -41,6 +41,7 @@ void sb03md_(char *dico, char *job, char *fact, char *trans, int *n, double *A, 
              int *ldwork, int *info);
 void dsyev_(char *jobz, char *uplo, int *n, double *a, int *lda, double *w, double *work,
             int *ldwork, int *info);
+void dgesv_(int *n, int *nrhs, double *a, int *lda, int *ipiv, double *b, int *ldb, int *info);
 }
 
 namespace RAILS
@@ -123,7 +124,7 @@ public:
           max_iter_(1000), tol_(1e-3), expand_size_(3), lanczos_iterations_(10),
           restart_size_(-1), reduced_size_(-1), restart_iterations_(20),
           restart_tolerance_(tol_ * 1e-3), minimize_solution_space_(true),
-          restart_from_solution_(false), verbose_(true)
+          restart_from_solution_(false), use_mass_(false), verbose_(true)
     {}
 
     virtual ~Solver() {}
@@ -145,6 +146,11 @@ public:
     // Restart basis from the dominant eigenvectors of T
     int compute_restart_vectors(DenseMatrix &X, DenseMatrix const &T, int num, double tol);
 
+    // Generalised projected problem A X E' + E X A' + B = 0 ("Use mass matrix";
+    // MATLAB lyap(VAV, VBV, [], VMV), matlab/RAILSsolver.m:381)
+    int dense_solve_generalized(DenseMatrix const &A, DenseMatrix const &E, DenseMatrix const &B,
+                                DenseMatrix &X);
+
     // ---- additions ------------------------------------------------------
     void set_observer(Observer obs) { observer_ = obs; }
     void set_verbose(bool v) { verbose_ = v; }
@@ -155,7 +161,12 @@ public:
 protected:
     Matrix A_;
     InputB<Matrix, MultiVector> B_;
-    Matrix M_;     // kept for interface parity; like the reference loop, unused
+    // The reference C++ loop stores M and never reads it.  With
+    // "Use mass matrix" = true this loop follows the MATLAB implementation
+    // instead (matlab/RAILSsolver.m:368-392): MV = M V, VMV = V'MV, the projected
+    // problem is the generalised one and the residual operator is
+    // AV T MV' + MV T AV' + B B'.
+    Matrix M_;
 
     int max_iter_;
     double tol_;
@@ -167,6 +178,7 @@ protected:
     double restart_tolerance_;
     bool minimize_solution_space_;
     bool restart_from_solution_;
+    bool use_mass_;
     bool verbose_;
 
     Observer observer_;
@@ -187,9 +199,10 @@ protected:
     };
 
     void project(MultiVector const &V, MultiVector const &W, MultiVector &AV, MultiVector &BV,
-                 DenseMatrix &VAV, DenseMatrix &VBV, bool first, int max_size);
-    void compress(MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV,
-                  DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix const &T);
+                 MultiVector &MV, DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, bool first,
+                 int max_size);
+    void compress(MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV, MultiVector &MV,
+                  DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, DenseMatrix const &T);
 };
 
 // A key is looked up as given, then UPPER, lower and Title Case; the last
@@ -235,6 +248,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::set_parameters(ParameterList &para
                                                 minimize_solution_space_);
     restart_from_solution_ = lookup_parameter(params, "Restart from solution",
                                               restart_from_solution_);
+    // extension (not a reference key): generalised equation with the stored M
+    use_mass_ = lookup_parameter(params, "Use mass matrix", use_mass_);
 
     if (lanczos_iterations_ <= expand_size_)
     {

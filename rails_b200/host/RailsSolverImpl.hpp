@@ -34,13 +34,19 @@ std::vector<int> largest_by_magnitude(DenseMatrix const &values, int count)
 // (:141-207).  W holds the columns of V that are new since the last call.
 template<class Matrix, class MultiVector, class DenseMatrix>
 void Solver<Matrix, MultiVector, DenseMatrix>::project(
-    MultiVector const &V, MultiVector const &W, MultiVector &AV, MultiVector &BV,
-    DenseMatrix &VAV, DenseMatrix &VBV, bool first, int max_size)
+    MultiVector const &V, MultiVector const &W, MultiVector &AV, MultiVector &BV, MultiVector &MV,
+    DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, bool first, int max_size)
 {
-    MultiVector AW, BW;
+    MultiVector AW, BW, MW;
     {
         Section s(sections_, "Apply A");
         AW = A_ * W;
+    }
+    if (use_mass_)
+    {
+        // MVnew = M * V(:, new_indices)  (matlab/RAILSsolver.m:368-373)
+        Section s(sections_, "Apply M");
+        MW = M_ * W;
     }
     {
         Section s(sections_, "Apply B");
@@ -82,6 +88,24 @@ void Solver<Matrix, MultiVector, DenseMatrix>::project(
         for (int j = 0; j < WBW.N(); j++)
             VBV(i + old_cols, j + old_cols) = WBW(i, j);
 
+    if (use_mass_)
+    {
+        // VMV = [[VMV; W' MV_old], V' MW]  (matlab/RAILSsolver.m:375-380)
+        VMV.resize(size, size);
+        if (old_cols > 0)
+        {
+            DenseMatrix WMV = W.dot(MV);
+            for (int i = 0; i < WMV.M(); i++)
+                for (int j = 0; j < WMV.N(); j++)
+                    VMV(i + old_cols, j) = WMV(i, j);
+        }
+        DenseMatrix VMW = V.dot(MW);
+        for (int i = 0; i < VMW.M(); i++)
+            for (int j = 0; j < VMW.N(); j++)
+                VMV(i, j + old_cols) = VMW(i, j);
+        MV.push_back(MW);
+    }
+
     AV.push_back(AW);
     BV.push_back(BW);
 }
@@ -90,8 +114,8 @@ void Solver<Matrix, MultiVector, DenseMatrix>::project(
 // with X the dominant eigenvectors of T (:258-303)
 template<class Matrix, class MultiVector, class DenseMatrix>
 void Solver<Matrix, MultiVector, DenseMatrix>::compress(
-    MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV,
-    DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix const &T)
+    MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV, MultiVector &MV,
+    DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, DenseMatrix const &T)
 {
     DenseMatrix X;
     compute_restart_vectors(X, T, std::min(reduced_size_, V.N()), restart_tolerance_);
@@ -118,6 +142,16 @@ void Solver<Matrix, MultiVector, DenseMatrix>::compress(
 
     BV.view(0, kept - 1) = BV * X;
     BV.resize(kept);
+
+    if (use_mass_)
+    {
+        small = X.transpose() * (VMV * X);
+        VMV.resize(kept, kept);
+        VMV.view() = small;
+
+        MV.view(0, kept - 1) = MV * X;
+        MV.resize(kept);
+    }
 }
 
 template<class Matrix, class MultiVector, class DenseMatrix>
@@ -166,6 +200,15 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
     MultiVector BV;
     DenseMatrix VBV(max_size, max_size);
 
+    MultiVector MV;
+    DenseMatrix VMV;
+    if (use_mass_)
+    {
+        MV = MultiVector(V, max_size);
+        MV.resize(0);
+        VMV = DenseMatrix(max_size, max_size);
+    }
+
     bool converged_before = false;
     int last_restart = 0;
     const double r0 = B_.norm();
@@ -174,15 +217,19 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
     {
         const int cols_before = V.N();
         if (W.N())
-            project(V, W, AV, BV, VAV, VBV, iter == 0, max_size);
+            project(V, W, AV, BV, MV, VAV, VBV, VMV, iter == 0, max_size);
 
-        dense_solve(VAV, VBV, T);
+        if (use_mass_)
+            dense_solve_generalized(VAV, VMV, VBV, T);
+        else
+            dense_solve(VAV, VBV, T);
 
         const int L = lanczos_iterations_;
         DenseMatrix H(L + 1, L + 1);
         DenseMatrix ritz_values(L, 1);
         MultiVector ritz_vectors;
-        resid_lanczos(AV, V, T, H, ritz_vectors, ritz_values, L);
+        // generalised residual AV T MV' + MV T AV' + B B' (matlab/RAILSsolver.m:391)
+        resid_lanczos(AV, use_mass_ ? MV : V, T, H, ritz_vectors, ritz_values, L);
 
         const double res = ritz_values.norm_inf();
 
@@ -247,7 +294,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
                           << " vectors" << std::endl;
             }
 
-            compress(V, W, AV, BV, VAV, VBV, T);
+            compress(V, W, AV, BV, MV, VAV, VBV, VMV, T);
             last_restart = iter;
 
             rec.restarted = true;
@@ -283,6 +330,15 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
 
             VBV.resize(max_size, max_size);
             VBV.resize(have, have);
+
+            if (use_mass_)
+            {
+                MV.resize(max_size);
+                MV.resize(have);
+
+                VMV.resize(max_size, max_size);
+                VMV.resize(have, have);
+            }
         }
 
         // expand with the Ritz vectors of the largest residual Ritz values
@@ -339,6 +395,54 @@ int Solver<Matrix, MultiVector, DenseMatrix>::dense_solve(DenseMatrix const &A,
     if (info != 0 && info != n + 1)
         std::cerr << "Error: sb03md returned info = " << info << std::endl;
     return info;
+}
+
+// A X E' + E X A' + B = 0 with E = V'MV (symmetric positive definite for an
+// SPD mass matrix and a full-rank V), reduced to the standard problem
+//     (E^-1 A) X + X (E^-1 A)' + E^-1 B E^-T = 0
+// and handed to dense_solve.  MATLAB calls lyap(A, B, [], E)
+// (matlab/RAILSsolver.m:381 -> matlab/mex/lyap.c:55-84, SLICOT sg03ad).
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::dense_solve_generalized(
+    DenseMatrix const &A, DenseMatrix const &E, DenseMatrix const &B, DenseMatrix &X)
+{
+    int n = A.M();
+    if (n < 1)
+        return dense_solve(A, B, X);
+    DenseMatrix Ah, Bh;
+    {
+        Section s(sections_, "dense_solve");
+        DenseMatrix lu = E.copy();
+        Ah = A.copy();
+        DenseMatrix Y = B.copy();
+        std::vector<int> piv(n);
+        int info = 0, lda = lu.LDA(), ldb = Ah.LDA();
+        // one factorisation, two right-hand-side blocks
+        dgesv_(&n, &n, lu, &lda, piv.data(), Ah, &ldb, &info);
+        if (info)
+        {
+            std::cerr << "Error: V'MV is singular (dgesv info = " << info << ")" << std::endl;
+            return info;
+        }
+        // Y = E^-1 B, then Bh = Y E^-T = (E^-1 Y')'
+        DenseMatrix lu2 = E.copy();
+        int ldy = Y.LDA();
+        lda = lu2.LDA();
+        dgesv_(&n, &n, lu2, &lda, piv.data(), Y, &ldy, &info);
+        DenseMatrix Yt(n, n);
+        for (int j = 0; j < n; j++)
+            for (int i = 0; i < n; i++)
+                Yt(i, j) = Y(j, i);
+        DenseMatrix lu3 = E.copy();
+        int ldt = Yt.LDA();
+        lda = lu3.LDA();
+        dgesv_(&n, &n, lu3, &lda, piv.data(), Yt, &ldt, &info);
+        Bh = DenseMatrix(n, n);
+        for (int j = 0; j < n; j++)
+            for (int i = 0; i < n; i++)
+                Bh(i, j) = Yt(j, i);
+    }
+    return dense_solve(Ah, Bh, X);
 }
 
 // L steps of symmetric Lanczos (no re-orthogonalisation) on the residual

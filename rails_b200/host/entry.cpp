@@ -83,8 +83,14 @@ extern "C" {
 //   timed region: CUDA events are recorded on the library stream when
 //            iteration `time_from` and iteration `time_to` finish; their
 //            distance is returned in *timed_ms (0 if not reached).
-int rails_host_solve(int rows, int global_rows, int row_offset,
+//   m_rowptr/m_colidx/m_vals : this rank's rows of the mass matrix M (same row
+//            block as A), or NULL.  Used only with the parameter
+//            "Use mass matrix" = 1 (generalised equation A X M' + M X A' + B B' = 0,
+//            matlab/RAILSsolver.m:368-392); otherwise M is stored and never read,
+//            like the reference C++ loop.
+int rails_host_solve_m(int rows, int global_rows, int row_offset,
                      const int *rowptr, const int *colidx, const double *vals,
+                     const int *m_rowptr, const int *m_colidx, const double *m_vals,
                      int n_b, const double *B_in, unsigned seed,
                      int nparams, const char *const *keys, const double *pvals,
                      int hist_cap, double *hist_abs, double *hist_rel, int *hist_k,
@@ -115,8 +121,22 @@ int rails_host_solve(int rows, int global_rows, int row_offset,
     else
         B.random();
 
-    CudaSolver solver(A, B, A);
     KeyValueParameters params(nparams, keys, pvals);
+    const bool use_mass = params.get("Use mass matrix", false);
+    CudaOperatorWrapper M = A;
+    if (m_rowptr)
+    {
+        M = CudaOperatorWrapper(rows, global_rows, global_rows, row_offset, m_rowptr, m_colidx, m_vals);
+        if (!M.device_handle())
+            return 200;
+    }
+    else if (use_mass)
+    {
+        std::cerr << "rails_host_solve: \"Use mass matrix\" needs the CSR arrays of M" << std::endl;
+        return 102;
+    }
+
+    CudaSolver solver(A, B, M);
     int ret = solver.set_parameters(params);
     if (ret)
         return 100 + ret;
@@ -200,6 +220,23 @@ int rails_host_solve(int rows, int global_rows, int row_offset,
                 T_out[i + (size_t)j * v_cap_cols] = T(i, j);
     }
     return ret;
+}
+
+int rails_host_solve(int rows, int global_rows, int row_offset,
+                     const int *rowptr, const int *colidx, const double *vals,
+                     int n_b, const double *B_in, unsigned seed,
+                     int nparams, const char *const *keys, const double *pvals,
+                     int hist_cap, double *hist_abs, double *hist_rel, int *hist_k,
+                     double *hist_sec, int *hist_len,
+                     int *k_io, int v_cap_cols, double *V_io, double *T_out,
+                     int time_from, int time_to, float *timed_ms,
+                     double *solve_seconds, double *setup_seconds, double *dense_solve_seconds)
+{
+    return rails_host_solve_m(rows, global_rows, row_offset, rowptr, colidx, vals, nullptr, nullptr,
+                              nullptr, n_b, B_in, seed, nparams, keys, pvals, hist_cap, hist_abs,
+                              hist_rel, hist_k, hist_sec, hist_len, k_io, v_cap_cols, V_io, T_out,
+                              time_from, time_to, timed_ms, solve_seconds, setup_seconds,
+                              dense_solve_seconds);
 }
 
 // "name=seconds;" list of the last solve's host-side section totals

@@ -77,6 +77,18 @@ def shift_diagonal(rowptr, colidx, vals, delta, row_begin=0):
     return out
 
 
+def lumped_mass(m, row_begin=0, row_end=None, seed=2):
+    """Rows [row_begin, row_end) of a lumped (diagonal) mass matrix as CSR:
+    d_i uniform in [0.5, 1.5], the same numbers whatever the
+    partition.  Column indices are GLOBAL."""
+    if row_end is None:
+        row_end = m
+    d = np.random.RandomState(seed).uniform(0.5, 1.5, m)[row_begin:row_end]
+    n = row_end - row_begin
+    return (np.arange(n + 1, dtype=np.int32), np.arange(row_begin, row_end, dtype=np.int32),
+            np.ascontiguousarray(d))
+
+
 def partition_rows(m, nranks, rank):
     """Epetra_Map(m, 0, comm) linear map: first m % P ranks get one more row."""
     base, rem = divmod(m, nranks)

@@ -59,7 +59,7 @@ def _params(params):
 
 
 def oracle_solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, v_cap_cols=0, V0=None,
-                 hist_cap=4096):
+                 hist_cap=4096, M=None):
     lib = oracle()
     m = rowptr.size - 1
     nk, karr, pv = _params(params)
@@ -75,8 +75,10 @@ def oracle_solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, v_cap_cols=0
             V[:, :k.value] = V0
     ss, sd = ctypes.c_double(0), ctypes.c_double(0)
     Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
-    ret = lib.oracle_solve(
-        ctypes.c_int(m), iptr(rowptr), iptr(colidx), dptr(vals), ctypes.c_int(n_b), dptr(Bc),
+    mrp, mci, mv = M if M is not None else (None, None, None)
+    ret = lib.oracle_solve_m(
+        ctypes.c_int(m), iptr(rowptr), iptr(colidx), dptr(vals), iptr(mrp), iptr(mci), dptr(mv),
+        ctypes.c_int(n_b), dptr(Bc),
         ctypes.c_uint(seed), ctypes.c_int(nk), karr, dptr(pv), ctypes.c_int(hist_cap), dptr(ha),
         dptr(hr), iptr(hk), dptr(hs), ctypes.byref(hl), ctypes.byref(k), ctypes.c_int(v_cap_cols),
         dptr(V), dptr(T), ctypes.byref(ss), ctypes.byref(sd))

@@ -103,6 +103,60 @@ def test_no_restart_history_and_solution_to_1e8(gpu):
     assert dx < 5e-8
 
 
+@pytest.mark.parametrize("kind,g,dim,n_b,P", [
+    ("laplacian", 20, 3, 2, {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 5}),
+    ("convdiff", 14, 3, 3, {"Tolerance": 1e-5, "Expand size": 2, "Lanczos iterations": 7,
+                            "Restart size": 50, "Reduced size": 25}),
+])
+def test_generalized_solve_with_lumped_mass(gpu, kind, g, dim, n_b, P):
+    """a16: A X M + M X A' + B B' = 0 with a lumped mass matrix ("Use mass
+    matrix", matlab/RAILSsolver.m:368-392) against the CPU oracle's restatement
+    of the same branch (different projected-solve reduction), fused and
+    operation-by-operation."""
+    import os
+    rp, ci, v = problems.build(kind, g, dim)
+    m = g ** dim
+    M = problems.lumped_mass(m)
+    P = dict(P); P["Use mass matrix"] = 1
+    B = np.asfortranarray(np.random.RandomState(4).uniform(-1, 1, (m, n_b)))
+    o = harness.oracle_solve(rp, ci, v, n_b, P, B=B, v_cap_cols=300, M=M)
+    assert o["ret"] == 0
+    for fused in ("1", "0"):
+        os.environ["RAILS_FUSED_LANCZOS"] = fused
+        try:
+            d = gpu.solve(rp, ci, v, n_b, P, B=B, v_cap_cols=300, M=M)
+        finally:
+            del os.environ["RAILS_FUSED_LANCZOS"]
+        assert d["ret"] == 0
+        if P["Expand size"] == 1:
+            assert (d["iterations"], d["k"]) == (o["iterations"], o["k"])
+            rel = np.abs(d["rel"] - o["rel"]) / o["rel"]
+            assert np.max(rel[:8]) < 1e-8
+            assert harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"]) < 1e-6
+        else:
+            assert abs(d["iterations"] - o["iterations"]) <= 0.1 * o["iterations"] + 1
+            assert harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"]) < 30 * P["Tolerance"]
+
+
+def test_generalized_solve_against_dense_solution(gpu):
+    import scipy.linalg as sl
+    rp, ci, v = problems.laplacian(7, 2)
+    m = 49
+    M = problems.lumped_mass(m)
+    B = np.asfortranarray(np.random.RandomState(5).uniform(-1, 1, (m, 2)))
+    P = {"Tolerance": 1e-10, "Expand size": 2, "Lanczos iterations": 6, "Use mass matrix": 1,
+         "Minimize solution space": 0}
+    d = gpu.solve(rp, ci, v, 2, P, B=B, v_cap_cols=m, M=M)
+    assert d["ret"] == 0
+    A = harness.csr_to_dense(rp, ci, v, m)
+    Mi = np.diag(1.0 / M[2])
+    Xs = sl.solve_continuous_lyapunov(Mi @ A, -(Mi @ B) @ (Mi @ B).T)
+    X = d["V"] @ d["T"] @ d["V"].T
+    assert np.linalg.norm(X - Xs) / np.linalg.norm(Xs) < 1e-8
+    # without the M arrays the key is refused
+    assert gpu.solve(rp, ci, v, 2, P, B=B)["ret"] == 102
+
+
 def test_explicit_residual_with_given_B(gpu):
     """Reference acceptance test (test/TestHelpers.hpp:4-11): every entry of
     A X + X A' + B B' below 1e-3 after a converged solve."""

@@ -176,3 +176,35 @@ def test_explicit_residual_small():
     X = o["V"] @ o["T"] @ o["V"].T
     R = A @ X + X @ A.T + B @ B.T
     assert np.max(np.abs(R)) < 1e-3
+
+
+def test_generalized_branch_against_dense_solution():
+    """a16: "Use mass matrix" follows matlab/RAILSsolver.m:368-392.
+    PARITY UNPINNED in the reference (the C++ loop never reads M, MATLAB tests
+    hold inequalities only), so the oracle is anchored on the dense solution of
+    A X M + M X A' + B B' = 0 instead."""
+    import scipy.linalg as sl
+    g, dim = 6, 2
+    rp, ci, v = problems.build("laplacian", g, dim)
+    m = g ** dim
+    M = problems.lumped_mass(m)
+    B = np.asfortranarray(np.random.RandomState(5).uniform(-1, 1, (m, 1)))
+    P = {"Tolerance": 1e-10, "Expand size": 1, "Lanczos iterations": 6, "Use mass matrix": 1,
+         "Minimize solution space": 0}
+    o = harness.oracle_solve(rp, ci, v, 1, P, B=B, v_cap_cols=m, M=M)
+    assert o["ret"] == 0
+    A = harness.csr_to_dense(rp, ci, v, m)
+    D = np.diag(M[2])
+    X = o["V"] @ o["T"] @ o["V"].T
+    assert np.abs(A @ X @ D + D @ X @ A.T + B @ B.T).max() < 1e-8
+    Mi = np.diag(1.0 / M[2])
+    Xs = sl.solve_continuous_lyapunov(Mi @ A, -(Mi @ B) @ (Mi @ B).T)
+    assert np.linalg.norm(X - Xs) / np.linalg.norm(Xs) < 1e-8
+    # M = I through the generalised branch reproduces the standard branch
+    I = (np.arange(m + 1, dtype=np.int32), np.arange(m, dtype=np.int32), np.ones(m))
+    P1 = {"Tolerance": 1e-6, "Expand size": 1, "Lanczos iterations": 6}
+    a = harness.oracle_solve(rp, ci, v, 1, P1, B=B, v_cap_cols=m)
+    P1["Use mass matrix"] = 1
+    b = harness.oracle_solve(rp, ci, v, 1, P1, B=B, v_cap_cols=m, M=I)
+    assert a["iterations"] == b["iterations"]
+    assert np.max(np.abs(a["rel"] - b["rel"]) / a["rel"]) < 1e-6

@@ -1,6 +1,10 @@
 // Context, communicator and multivector storage of librails_cuda.so.
 #include "internal.h"
 
+#include <algorithm>
+#include <cstring>
+#include <thread>
+
 #include <cstdarg>
 #include <cstring>
 
@@ -76,6 +80,102 @@ int upload_small(const double *host, int k, int c, int ldc, const double **d_out
     RAILS_CUDA_TRY(cudaMemcpyAsync(d, h, n * sizeof(double), cudaMemcpyHostToDevice, cx.stream));
     cx.ring_pos += (n + 15) / 16 * 16;
     *d_out = d;
+    return RAILS_OK;
+}
+
+namespace
+{
+constexpr size_t STAGE_CHUNK = 32u << 20;
+constexpr int STAGE_THREADS = 6;
+
+int ensure_stage()
+{
+    Context &c = ctx();
+    for (int i = 0; i < 2; ++i)
+        if (!c.h_stage[i])
+        {
+            RAILS_CUDA_TRY(cudaMallocHost(&c.h_stage[i], STAGE_CHUNK));
+            RAILS_CUDA_TRY(cudaEventCreateWithFlags(&c.stage_ev[i], cudaEventDisableTiming));
+        }
+    return RAILS_OK;
+}
+
+// memcpy split over a few threads (one core moves ~10 GB/s, PCIe 5 x16 ~50)
+void parallel_memcpy(void *dst, const void *src, size_t bytes)
+{
+    if (bytes < (4u << 20))
+    {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    std::thread th[STAGE_THREADS];
+    const size_t part = (bytes / STAGE_THREADS + 4095) & ~(size_t)4095;
+    int n = 0;
+    for (size_t off = 0; off < bytes; off += part, ++n)
+    {
+        const size_t len = std::min(part, bytes - off);
+        th[n] = std::thread([=] { memcpy((char *)dst + off, (const char *)src + off, len); });
+    }
+    for (int i = 0; i < n; ++i) th[i].join();
+}
+}
+
+int copy_h2d(void *dst, const void *src, size_t bytes)
+{
+    Context &c = ctx();
+    if (bytes < (8u << 20))
+    {
+        RAILS_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream));
+        RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+        return RAILS_OK;
+    }
+    int rc = ensure_stage();
+    if (rc) return rc;
+    int b = 0;
+    for (size_t off = 0; off < bytes; off += STAGE_CHUNK, b ^= 1)
+    {
+        const size_t len = std::min(STAGE_CHUNK, bytes - off);
+        RAILS_CUDA_TRY(cudaEventSynchronize(c.stage_ev[b]));       // buffer b is free again
+        parallel_memcpy(c.h_stage[b], (const char *)src + off, len);
+        RAILS_CUDA_TRY(cudaMemcpyAsync((char *)dst + off, c.h_stage[b], len, cudaMemcpyHostToDevice, c.stream));
+        RAILS_CUDA_TRY(cudaEventRecord(c.stage_ev[b], c.stream));
+    }
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    return RAILS_OK;
+}
+
+int copy_d2h(void *dst, const void *src, size_t bytes)
+{
+    Context &c = ctx();
+    if (bytes < (8u << 20))
+    {
+        RAILS_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.stream));
+        RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+        return RAILS_OK;
+    }
+    int rc = ensure_stage();
+    if (rc) return rc;
+    // chunk i+1 is in flight while chunk i is copied out of its pinned buffer
+    size_t off_prev = 0, len_prev = 0;
+    int b = 0;
+    bool have_prev = false;
+    for (size_t off = 0; off < bytes; off += STAGE_CHUNK, b ^= 1)
+    {
+        const size_t len = std::min(STAGE_CHUNK, bytes - off);
+        RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_stage[b], (const char *)src + off, len, cudaMemcpyDeviceToHost, c.stream));
+        RAILS_CUDA_TRY(cudaEventRecord(c.stage_ev[b], c.stream));
+        if (have_prev)
+        {
+            RAILS_CUDA_TRY(cudaEventSynchronize(c.stage_ev[b ^ 1]));
+            parallel_memcpy((char *)dst + off_prev, c.h_stage[b ^ 1], len_prev);
+        }
+        off_prev = off; len_prev = len; have_prev = true;
+    }
+    if (have_prev)
+    {
+        RAILS_CUDA_TRY(cudaEventSynchronize(c.stage_ev[b ^ 1]));
+        parallel_memcpy((char *)dst + off_prev, c.h_stage[b ^ 1], len_prev);
+    }
     return RAILS_OK;
 }
 
@@ -155,6 +255,12 @@ extern "C" int rails_cuda_finalize(void)
     if (c.h_small) cudaFreeHost(c.h_small);
     if (c.d_coef) cudaFree(c.d_coef);
     if (c.h_ring) cudaFreeHost(c.h_ring);
+    for (int i = 0; i < 2; ++i)
+    {
+        if (c.h_stage[i]) cudaFreeHost(c.h_stage[i]);
+        if (c.stage_ev[i]) cudaEventDestroy(c.stage_ev[i]);
+        c.h_stage[i] = nullptr; c.stage_ev[i] = nullptr;
+    }
     c.h_ring = nullptr; c.ring_cap = c.ring_pos = 0;
     c.d_partial = c.d_small = c.h_small = c.d_coef = nullptr;
     c.partial_cap = c.small_cap = c.coef_cap = 0;
@@ -327,6 +433,17 @@ extern "C" int rails_mv_upload(rails_mv_t mv, int col0, int ncols, const double 
         return RAILS_OK;
     if (!host || ldh < mv->rows)
         return rails::fail(RAILS_ERR_ARG, "upload: bad host block");
+    if ((size_t)mv->rows * sizeof(double) >= (8u << 20))
+    {
+        // large columns: staged, pipelined copies column by column
+        for (int j = 0; j < ncols; ++j)
+        {
+            rc = rails::copy_h2d(mv->data + (size_t)(col0 + j) * mv->ld, host + (size_t)j * ldh,
+                                 (size_t)mv->rows * sizeof(double));
+            if (rc) return rc;
+        }
+        return RAILS_OK;
+    }
     RAILS_CUDA_TRY(cudaMemcpy2DAsync(mv->data + (size_t)col0 * mv->ld, mv->ld * sizeof(double),
                                      host, ldh * sizeof(double),
                                      (size_t)mv->rows * sizeof(double), ncols,
@@ -345,6 +462,16 @@ extern "C" int rails_mv_download(rails_mv_t mv, int col0, int ncols, double *hos
         return RAILS_OK;
     if (!host || ldh < mv->rows)
         return rails::fail(RAILS_ERR_ARG, "download: bad host block");
+    if ((size_t)mv->rows * sizeof(double) >= (8u << 20))
+    {
+        for (int j = 0; j < ncols; ++j)
+        {
+            rc = rails::copy_d2h(host + (size_t)j * ldh, mv->data + (size_t)(col0 + j) * mv->ld,
+                                 (size_t)mv->rows * sizeof(double));
+            if (rc) return rc;
+        }
+        return RAILS_OK;
+    }
     RAILS_CUDA_TRY(cudaMemcpy2DAsync(host, ldh * sizeof(double),
                                      mv->data + (size_t)col0 * mv->ld, mv->ld * sizeof(double),
                                      (size_t)mv->rows * sizeof(double), ncols,

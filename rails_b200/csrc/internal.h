@@ -49,10 +49,8 @@ struct rails_csr_s
     double *send_buf;                    // device staging, nsend x ncols
     double *ghost_buf;                   // device, nghost x ncols
     int halo_cols_cap;                   // columns the staging buffers hold
-    // host copy kept for the lazily built transpose
-    std::vector<int> h_rowptr, h_colidx;
-    std::vector<double> h_vals;
-    rails_csr_s *transposed;
+    bool partitioned;                    // rows != global rows (no transpose available)
+    rails_csr_s *transposed;             // built lazily from the device arrays
     size_t bytes;
 };
 
@@ -78,6 +76,8 @@ struct Context
     double *h_ring = nullptr;     // pinned staging ring for small H2D operands
     size_t ring_cap = 0;
     size_t ring_pos = 0;
+    void *h_stage[2] = {nullptr, nullptr};   // pinned chunks for large pageable transfers
+    cudaEvent_t stage_ev[2] = {nullptr, nullptr};
     // communicator
     ncclComm_t comm = nullptr;
     int rank = 0;
@@ -96,6 +96,12 @@ int ensure_small(size_t doubles);
 // enqueues its upload; *d_out is a compact (ld = k) device copy that stays
 // valid until the ring wraps (thousands of calls later, guarded by a sync).
 int upload_small(const double *host, int k, int c, int ldc, const double **d_out);
+// Large transfers between PAGEABLE host memory and the device: chunks are
+// moved through two pinned buffers, the host-side memcpy of a chunk is split
+// over a few threads and overlaps the DMA of the previous chunk.  Synchronous
+// (the host block may be reused / is complete on return).
+int copy_h2d(void *dst, const void *src, size_t bytes);
+int copy_d2h(void *dst, const void *src, size_t bytes);
 
 // device-side kernels callable across translation units
 int dot_device(const double *X, long long ldx, int a, const double *Y,

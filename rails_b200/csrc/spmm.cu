@@ -214,6 +214,20 @@ spmm_kernel(const int *__restrict__ rowptr, const int *__restrict__ colidx,
     }
 }
 
+// flag = 1 if any column index lies outside [0, ncols)
+__global__ void __launch_bounds__(256)
+check_columns_kernel(const int *__restrict__ colidx, long long nnz, int ncols, int *flag)
+{
+    bool bad = false;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < nnz; i += (long long)gridDim.x * 256)
+    {
+        const int c = colidx[i];
+        bad |= (c < 0) | (c >= ncols);
+    }
+    if (__syncthreads_or(bad) && threadIdx.x == 0)
+        atomicOr(flag, 1);
+}
+
 __global__ void __launch_bounds__(256)
 pack_rows_kernel(const int *__restrict__ rows, int n, const double *__restrict__ X, long long ldx,
                  double *__restrict__ buf, long long ldb)
@@ -274,15 +288,34 @@ int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const doubl
     RAILS_CUDA_TRY(cudaMalloc(&A->blk_row, b_blk));
     A->bytes += b_rp + b_ci + b_v + b_blk;
     ctx().bytes_in_use.fetch_add((long long)(b_rp + b_ci + b_v + b_blk));
-    cudaStream_t s = ctx().stream;
-    RAILS_CUDA_TRY(cudaMemcpyAsync(A->rowptr, rowptr, b_rp, cudaMemcpyHostToDevice, s));
+    int rc = rails::copy_h2d(A->rowptr, rowptr, b_rp);
+    if (rc) return rc;
     if (nnz)
     {
-        RAILS_CUDA_TRY(cudaMemcpyAsync(A->colidx, colidx, (size_t)nnz * sizeof(int), cudaMemcpyHostToDevice, s));
-        RAILS_CUDA_TRY(cudaMemcpyAsync(A->vals, vals, (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice, s));
+        rc = rails::copy_h2d(A->colidx, colidx, (size_t)nnz * sizeof(int));
+        if (rc) return rc;
+        rc = rails::copy_h2d(A->vals, vals, (size_t)nnz * sizeof(double));
+        if (rc) return rc;
     }
-    RAILS_CUDA_TRY(cudaMemcpyAsync(A->blk_row, blk.data(), b_blk, cudaMemcpyHostToDevice, s));
-    RAILS_CUDA_TRY(cudaStreamSynchronize(s));
+    rc = rails::copy_h2d(A->blk_row, blk.data(), b_blk);
+    if (rc) return rc;
+    // column indices are validated where they now live: one streaming pass on
+    // the device instead of a scalar host loop over nnz entries
+    if (nnz)
+    {
+        rc = rails::ensure_small(1);
+        if (rc) return rc;
+        int *flag = reinterpret_cast<int *>(ctx().d_small);
+        RAILS_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), ctx().stream));
+        const int nb = (int)std::min<long long>((nnz + 1023) / 1024, (long long)ctx().sm_count * 8);
+        RAILS_LAUNCH(check_columns_kernel, nb, 256, 0, A->colidx, nnz, (int)(A->ncols_local + A->nghost), flag);
+        RAILS_CHECK_LAUNCH();
+        int bad = 0;
+        RAILS_CUDA_TRY(cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, ctx().stream));
+        RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+        if (bad)
+            return rails::fail(RAILS_ERR_ARG, "csr_create: column index out of range");
+    }
     return RAILS_OK;
 }
 
@@ -441,6 +474,7 @@ extern "C" int rails_csr_create(long long rows, long long global_rows, long long
     A->rowptr = A->colidx = A->blk_row = nullptr; A->vals = nullptr;
     A->send_rows = nullptr; A->send_buf = A->ghost_buf = nullptr;
     A->nghost = A->nsend = 0; A->halo_cols_cap = 0; A->transposed = nullptr; A->bytes = 0;
+    A->partitioned = dist;
     A->recv_count.assign(c.nranks, 0);
     A->send_count.assign(c.nranks, 0);
 
@@ -448,16 +482,6 @@ extern "C" int rails_csr_create(long long rows, long long global_rows, long long
     if (!dist)
     {
         A->ncols_local = global_cols;
-        for (long long p = 0; p < nnz; ++p)
-            if (colidx[p] < 0 || colidx[p] >= global_cols)
-            {
-                delete A;
-                return rails::fail(RAILS_ERR_ARG, "csr_create: column %d out of range", colidx[p]);
-            }
-        // kept for a lazily built transpose (B as an Operator)
-        A->h_rowptr.assign(rowptr, rowptr + rows + 1);
-        A->h_colidx.assign(colidx, colidx + nnz);
-        A->h_vals.assign(vals, vals + nnz);
         rc = upload_csr(A, rowptr, colidx, vals);
         if (rc) { free_csr(A); return rc; }
         *out = A;
@@ -533,20 +557,33 @@ namespace
 int build_transpose(rails_csr_s *A)
 {
     if (A->transposed) return RAILS_OK;
-    if (A->h_rowptr.empty())
+    if (A->partitioned)
         return rails::fail(RAILS_ERR_ARG, "transposed apply is not available on a row-partitioned operator");
     const long long m = A->rows, n = A->global_cols, nnz = A->nnz;
+    // rare path (B given as an Operator, Operator::norm): the CSR arrays are
+    // read back from the device rather than kept on the host for every operator
+    std::vector<int> h_rowptr(m + 1), h_colidx(nnz);
+    std::vector<double> h_vals(nnz);
+    int rc0 = rails::copy_d2h(h_rowptr.data(), A->rowptr, (size_t)(m + 1) * sizeof(int));
+    if (rc0) return rc0;
+    if (nnz)
+    {
+        rc0 = rails::copy_d2h(h_colidx.data(), A->colidx, (size_t)nnz * sizeof(int));
+        if (rc0) return rc0;
+        rc0 = rails::copy_d2h(h_vals.data(), A->vals, (size_t)nnz * sizeof(double));
+        if (rc0) return rc0;
+    }
     std::vector<int> rp(n + 1, 0), ci(nnz);
     std::vector<double> v(nnz);
-    for (long long p = 0; p < nnz; ++p) rp[A->h_colidx[p] + 1]++;
+    for (long long p = 0; p < nnz; ++p) rp[h_colidx[p] + 1]++;
     for (long long j = 0; j < n; ++j) rp[j + 1] += rp[j];
     std::vector<int> next(rp.begin(), rp.end() - 1);
     for (long long i = 0; i < m; ++i)
-        for (int p = A->h_rowptr[i]; p < A->h_rowptr[i + 1]; ++p)
+        for (int p = h_rowptr[i]; p < h_rowptr[i + 1]; ++p)
         {
-            int q = next[A->h_colidx[p]]++;
+            int q = next[h_colidx[p]]++;
             ci[q] = (int)i;
-            v[q] = A->h_vals[p];
+            v[q] = h_vals[p];
         }
     rails_csr_s *T = new rails_csr_s();
     T->rows = n; T->global_rows = n; T->global_cols = m; T->row_offset = 0; T->nnz = nnz;
@@ -554,6 +591,7 @@ int build_transpose(rails_csr_s *A)
     T->rowptr = T->colidx = T->blk_row = nullptr; T->vals = nullptr;
     T->send_rows = nullptr; T->send_buf = T->ghost_buf = nullptr;
     T->nghost = T->nsend = 0; T->halo_cols_cap = 0; T->transposed = nullptr; T->bytes = 0;
+    T->partitioned = false;
     int rc = upload_csr(T, rp.data(), ci.data(), v.data());
     if (rc) { free_csr(T); return rc; }
     A->transposed = T;

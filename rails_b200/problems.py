@@ -104,8 +104,12 @@ CONFIGS = {
                                      "Reduced size": 100, "Expand size": 4,
                                      "Lanczos iterations": 20,
                                      "Restart iterations": -1}),
+    # lumped mass matrix: the generalised branch (matlab/RAILSsolver.m:368-392)
     "C3": ("laplacian", 256, 3, 1, {"Tolerance": 1e-4, "Expand size": 1,
-                                    "Lanczos iterations": 10}),
+                                    "Lanczos iterations": 10, "Use mass matrix": 1}),
+    # the same problem as the C++ reference solves it (M never read)
+    "C3I": ("laplacian", 256, 3, 1, {"Tolerance": 1e-4, "Expand size": 1,
+                                     "Lanczos iterations": 10}),
     "C4": ("convdiff", 256, 3, 16, {"Tolerance": 1e-4, "Expand size": 16,
                                     "Lanczos iterations": 40}),
     "C5": ("laplacian", 512, 3, 1, {"Tolerance": 1e-4, "Expand size": 1,

@@ -68,6 +68,29 @@ def test_spmm_bit_exact(gpu, kind, g, dim, e):
     gpu.cuda().rails_csr_free(A)
 
 
+def test_csr_create_rejects_bad_columns(gpu):
+    rp = np.array([0, 2, 3], dtype=np.int32)
+    v = np.ones(3)
+    A = ctypes.c_void_p()
+    for bad in ([0, 2, 1], [0, 1, -1]):
+        ci = np.array(bad, dtype=np.int32)
+        assert gpu.cuda().rails_csr_create(2, 2, 2, 0, gpu.iptr(rp), gpu.iptr(ci), gpu.dptr(v),
+                                           ctypes.byref(A)) == 2
+    ci = np.array([0, 1, 1], dtype=np.int32)
+    gpu.check(gpu.cuda().rails_csr_create(2, 2, 2, 0, gpu.iptr(rp), gpu.iptr(ci), gpu.dptr(v),
+                                          ctypes.byref(A)), "csr_create")
+    gpu.cuda().rails_csr_free(A)
+
+
+def test_large_upload_download_round_trip(gpu):
+    # columns above 8 MB take the staged (pinned, multi-threaded) transfer path
+    m = (40 << 20) // 8 + 13
+    a = np.asfortranarray(np.random.RandomState(0).uniform(-1, 1, (m, 2)))
+    mv = gpu.MultiVector.from_numpy(a)
+    assert np.array_equal(mv.numpy(), a)
+    assert np.array_equal(mv.numpy(1, 1), a[:, 1:2])
+
+
 def test_spmm_row_longer_than_the_staging_buffer(gpu):
     # one row with 7000 non-zeros (> the 6144-entry stage): whole-CTA fallback,
     # surrounded by ordinary rows and an empty block of rows

@@ -255,6 +255,7 @@ def cpu_sample(rp, ci, v, n_b, params, B, warmup, steps, budget_s, M=None):
     import harness
     P = window_params(params, warmup, steps)
     P["Oracle time limit"] = budget_s
+    harness.oracle().oracle_set_num_threads(os.cpu_count() or 1)      # all host threads
     o = harness.oracle_solve(rp, ci, v, n_b, P, B=B, M=M)
     sec = o["seconds"]
     done = len(sec)

@@ -120,6 +120,12 @@ int rails_mv_norm_inf(rails_mv_t mv, int col0, int ncols, double *out);
  *      cross-rank sum when both operands are distributed. ---------------- */
 int rails_mv_dot(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
                  double *out, int ldo);
+/* `count` such products with one host synchronisation (and one all-reduce):
+ * out[i] (a[i] x b[i], ld = ldo[i]) = X[i][:, xc0[i]..]' Y[i][:, yc0[i]..].  The
+ * projection update (src/LyapunovSolver.hpp:173-195) issues its dots this way. */
+int rails_mv_dot_batch(int count, const rails_mv_t *X, const int *xc0, const int *a,
+                       const rails_mv_t *Y, const int *yc0, const int *b,
+                       double *const *out, const int *ldo);
 /* same product left on the device in a REPLICATED multivector (a rows);
  * used for Y = B' q (src/LyapunovSolver.hpp:150,389) without a host sync */
 int rails_mv_dot_dev(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
@@ -156,6 +162,17 @@ int rails_mv_multi_gemv(int nblk, const rails_mv_t *X, const int *xc0, const int
  * subtracted, as the scaled temporaries of :411-413 are; the norm is :417. */
 int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, rails_mv_t q, int qc,
                             double beta, rails_mv_t p, int pc, double *norm);
+
+/* The whole L-step recurrence (:375-434) as one asynchronous chain: blocks 0 and
+ * 1 (k columns each; V or MV, and AV) exchange their projections through the
+ * host matrix T (k x k, ldt), further blocks (B) use theirs directly.
+ * Q[:, qc0] holds the un-normalised start vector and Q has room for L + 1
+ * columns from qc0.  On return alpha[i] = H(i,i), beta[i] = H(i+1,i) for
+ * i < *steps; *steps < L after a breakdown (beta < 1e-14, :419-427).  One host
+ * synchronisation for the whole call. */
+int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                         const double *T, int ldt, rails_mv_t Q, int qc0, int L,
+                         double *alpha, double *beta, int *steps);
 
 /* ---- Gram-Schmidt: column-wise CGS2 of columns [first, last] against all
  *      earlier columns (StlWrapper::orthogonalize :305-321), executed as one

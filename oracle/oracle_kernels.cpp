@@ -145,5 +145,9 @@ double oracle_norm_inf(long long m, int n, const double *X, long long ld)
 }
 
 int oracle_num_threads(void) { return omp_get_max_threads(); }
+// The partial sums of oracle_dot are combined in thread order, so results are
+// reproducible for a given thread count; tests pin it (the algorithm's path can
+// depend on rounding, DESIGN.md "Reproducibility").
+void oracle_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 }

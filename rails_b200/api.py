@@ -91,6 +91,8 @@ CUDA_SYMBOLS = [
     ("rails_mv_add_scaled", I, [P, I, D, D, P, I, I]),
     ("rails_mv_norm_inf", I, [P, I, I, c_double_p]),
     ("rails_mv_dot", I, [P, I, I, P, I, I, c_double_p, I]),
+    ("rails_mv_dot_batch", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, ctypes.POINTER(P), c_int_p, c_int_p,
+                               ctypes.POINTER(c_double_p), c_int_p]),
     ("rails_mv_dot_dev", I, [P, I, I, P, I, I, P, I]),
     ("rails_mv_gemm", I, [P, I, I, c_double_p, I, I, D, D, P, I]),
     ("rails_mv_gemm_dev", I, [P, I, I, P, I, I, D, D, P, I]),
@@ -98,6 +100,8 @@ CUDA_SYMBOLS = [
     ("rails_mv_multi_gemv", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, c_double_p, P, I, P, I,
                                 c_double_p]),
     ("rails_mv_lanczos_update", I, [P, I, D, P, I, D, P, I, c_double_p]),
+    ("rails_mv_lanczos_run", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, c_double_p, I, P, I, I,
+                                 c_double_p, c_double_p, c_int_p]),
     ("rails_mv_orthogonalize", I, [P, I, I, I]),
     ("rails_mv_random", I, [P, I, I, LL, ctypes.c_uint]),
     ("rails_csr_create", I, [LL, LL, LL, LL, c_int_p, c_int_p, c_double_p, ctypes.POINTER(P)]),

@@ -15,6 +15,8 @@
 // resident CTAs, a second kernel adds the per-CTA partials in CTA order.
 #include "internal.h"
 
+#include <vector>
+
 using rails::ctx;
 
 namespace rails
@@ -280,6 +282,59 @@ extern "C" int rails_mv_dot(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0,
     for (int j = 0; j < b; ++j)
         for (int i = 0; i < a; ++i)
             out[i + (size_t)j * ldo] = c.h_small[i + (size_t)j * a];
+    return RAILS_OK;
+}
+
+// Several inner products with ONE host synchronisation: all are enqueued, the
+// results of the distributed pairs are all-reduced as one buffer, and a single
+// read-back returns everything (the projection update of
+// src/LyapunovSolver.hpp:173-195 issues up to six dots in a row).
+extern "C" int rails_mv_dot_batch(int count, const rails_mv_t *X, const int *xc0, const int *a,
+                                  const rails_mv_t *Y, const int *yc0, const int *b,
+                                  double *const *out, const int *ldo)
+{
+    RAILS_REQUIRE_READY();
+    if (count < 0 || (count > 0 && (!X || !Y || !xc0 || !a || !yc0 || !b || !out || !ldo)))
+        return rails::fail(RAILS_ERR_ARG, "dot_batch: null argument");
+    size_t total = 0;
+    for (int i = 0; i < count; ++i)
+    {
+        int rc = check_pair(X[i], xc0[i], a[i], Y[i], yc0[i], b[i], "dot_batch");
+        if (rc) return rc;
+        if (a[i] && b[i] && (!out[i] || ldo[i] < a[i]))
+            return rails::fail(RAILS_ERR_ARG, "dot_batch: bad result block %d", i);
+        total += (size_t)a[i] * b[i];
+    }
+    if (total == 0) return RAILS_OK;
+    rails::Context &c = ctx();
+    int rc = rails::ensure_small(total);
+    if (rc) return rc;
+    // distributed pairs first (one contiguous all-reduce), then the replicated ones
+    std::vector<size_t> off(count, 0);
+    size_t pos = 0, ndist = 0;
+    for (int pass = 0; pass < 2; ++pass)
+    {
+        for (int i = 0; i < count; ++i)
+        {
+            const bool dist = X[i]->flags == RAILS_MV_DISTRIBUTED && Y[i]->flags == RAILS_MV_DISTRIBUTED;
+            if (dist != (pass == 0) || a[i] == 0 || b[i] == 0) continue;
+            off[i] = pos;
+            rc = rails::dot_device(X[i]->data + (size_t)xc0[i] * X[i]->ld, X[i]->ld, a[i],
+                                   Y[i]->data + (size_t)yc0[i] * Y[i]->ld, Y[i]->ld, b[i], X[i]->rows,
+                                   c.d_small + pos, a[i], false);
+            if (rc) return rc;
+            pos += (size_t)a[i] * b[i];
+        }
+        if (pass == 0) ndist = pos;
+    }
+    if (ndist && c.comm)
+        RAILS_NCCL_TRY(ncclAllReduce(c.d_small, c.d_small, ndist, ncclDouble, ncclSum, c.comm, c.stream));
+    RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, total * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    for (int i = 0; i < count; ++i)
+        for (int j = 0; j < b[i]; ++j)
+            for (int r = 0; r < a[i]; ++r)
+                out[i][r + (size_t)j * ldo[i]] = c.h_small[off[i] + r + (size_t)j * a[i]];
     return RAILS_OK;
 }
 

@@ -137,11 +137,18 @@ __device__ __forceinline__ void md_tile(const Segs &S, double *__restrict__ q, d
 }
 
 // partial[blockIdx.x][c] = sum over this CTA's row tiles of X_c . (qscale q)
+// qscale_sq != NULL: the scale is 1 / sqrt(|*qscale_sq|), read from device memory
+// (the squared norm the previous step left there), and q is written back.
 __global__ void __launch_bounds__(MD_THREADS)
 multi_dot_kernel(Segs S, int total, double *__restrict__ q, double qscale, int write_q,
-                 long long rows, double *__restrict__ partial)
+                 long long rows, double *__restrict__ partial, const double *__restrict__ qscale_sq)
 {
     extern __shared__ double sacc[];
+    if (qscale_sq)
+    {
+        qscale = 1.0 / sqrt(fabs(*qscale_sq));
+        write_q = 1;
+    }
     for (int i = threadIdx.x; i < total * MD_WARPS; i += MD_THREADS)
         sacc[i] = 0.0;
     __syncthreads();
@@ -279,7 +286,7 @@ extern "C" int rails_mv_multi_dot(int nblk, const rails_mv_t *X, const int *xc0,
         }
         const size_t smem = (size_t)std::max(total, 1) * MD_WARPS * sizeof(double);
         RAILS_LAUNCH(multi_dot_kernel, nb, MD_THREADS, smem, S, total, q->data + (size_t)qc * q->ld,
-                     qscale, write_q, rows, c.d_partial);
+                     qscale, write_q, rows, c.d_partial, (const double *)nullptr);
         RAILS_CHECK_LAUNCH();
         if (total > 0)
         {
@@ -404,9 +411,13 @@ constexpr int LU_THREADS = 256;
 __global__ void __launch_bounds__(LU_THREADS)
 lanczos_update_kernel(double *__restrict__ next, const double *__restrict__ q,
                       const double *__restrict__ p, double alpha, double beta, long long rows,
-                      double *__restrict__ partial)
+                      double *__restrict__ partial, const double *__restrict__ alpha_dev,
+                      const double *__restrict__ beta_sq_dev)
 {
     __shared__ double red[LU_THREADS / 32];
+    // device-resident recurrence: alpha and |next_prev|^2 come from device memory
+    if (alpha_dev) alpha = *alpha_dev;
+    if (beta_sq_dev) beta = sqrt(fabs(*beta_sq_dev));
     const long long rows2 = rows / 2;
     double2 *n2 = reinterpret_cast<double2 *>(next);
     const double2 *q2 = reinterpret_cast<const double2 *>(q);
@@ -536,7 +547,7 @@ extern "C" int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, ra
         RAILS_LAUNCH(lanczos_update_kernel, nb, LU_THREADS, 0, next->data + (size_t)nc * next->ld,
                      q->data + (size_t)qc * q->ld,
                      p ? p->data + (size_t)pc * p->ld : (const double *)nullptr, alpha, beta, rows,
-                     c.d_partial);
+                     c.d_partial, (const double *)nullptr, (const double *)nullptr);
         RAILS_CHECK_LAUNCH();
         RAILS_LAUNCH(sum_partials_kernel, 1, 256, 0, c.d_partial, nb, 1, c.d_small, 0);
         RAILS_CHECK_LAUNCH();
@@ -545,5 +556,160 @@ extern "C" int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, ra
     rc = finish_to_host(1, next->flags == RAILS_MV_DISTRIBUTED, &sq);
     if (rc) return rc;
     *norm = std::sqrt(std::fabs(sq));
+    return RAILS_OK;
+}
+
+namespace
+{
+
+// coef = [T g_1 ; T g_0 ; g_rest]: the k x k products `Z = T * Z` of
+// src/LyapunovSolver.hpp:395,401 on the device (T compact, ld = k).  One warp
+// per output row; each lane adds its columns in order, then a shuffle tree.
+__global__ void __launch_bounds__(256)
+lanczos_coef_kernel(const double *__restrict__ T, int k, int total, const double *__restrict__ g,
+                    double *__restrict__ coef)
+{
+    const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp < 2 * k)
+    {
+        const int j = warp < k ? warp : warp - k;
+        // rows [0, k): coefficient of block 0 = T * g(block 1); rows [k, 2k): block 1 = T * g(block 0)
+        const double *gv = warp < k ? g + k : g;
+        double s = 0.0;
+        for (int l = lane; l < k; l += 32)
+            s = fma(T[j + (size_t)l * k], gv[l], s);
+        for (int o = 16; o > 0; o >>= 1)
+            s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) coef[warp] = s;
+    }
+    else
+    {
+        const int i = 2 * k + (warp - 2 * k) * 32 + lane;
+        if (i < total) coef[i] = g[i];
+    }
+}
+
+}
+
+// The whole L-step recurrence of Solver::resid_lanczos
+// (src/LyapunovSolver.hpp:375-434) as ONE asynchronous chain on the library
+// stream: no value returns to the host until the last step has been enqueued.
+// Blocks 0 and 1 (k columns each: V or MV, and AV) exchange their projections
+// through T; the remaining blocks (B) use theirs directly:
+//     R q = X_0 (T X_1'q) + X_1 (T X_0'q) + X_2 (X_2'q).
+// Q[:, qc0] holds the un-normalised start vector; on return Q[:, qc0 .. qc0+steps)
+// are the Lanczos vectors, alpha[i] = H(i,i), beta[i] = H(i+1,i).  A breakdown
+// (beta_i < 1e-14, :419-427) is detected afterwards: *steps = i + 1 and what was
+// computed past it is ignored, which is what the reference's `break` leaves.
+extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                                    const double *T, int ldt, rails_mv_t Q, int qc0, int L,
+                                    double *alpha, double *beta, int *steps)
+{
+    RAILS_REQUIRE_READY();
+    if (!Q || qc0 < 0 || L < 1 || qc0 + L + 1 > Q->cols || !alpha || !beta || !steps)
+        return rails::fail(RAILS_ERR_ARG, "lanczos_run: Q needs L + 1 columns from qc0");
+    if (nblk < 2 || xn[0] != xn[1] || (xn[0] > 0 && (!T || ldt < xn[0])))
+        return rails::fail(RAILS_ERR_ARG, "lanczos_run: blocks 0 and 1 must have k columns each and T be k x k");
+    Segs S;
+    int total = 0;
+    bool dist = false;
+    int rc = collect_segs(nblk, X, xc0, xn, Q->rows, &S, &total, &dist, "lanczos_run");
+    if (rc) return rc;
+    if (total > MD_MAXCOLS)
+        return rails::fail(RAILS_ERR_ARG, "lanczos_run: %d columns, at most %d", total, MD_MAXCOLS);
+    for (int s = 0; s < S.nseg; ++s)
+        if (S.p[s] <= Q->data + (size_t)(qc0 + L + 1) * Q->ld && Q->data + (size_t)qc0 * Q->ld < S.p[s] + (size_t)S.n[s] * S.ld[s])
+            return rails::fail(RAILS_ERR_ARG, "lanczos_run: Q overlaps a block");
+    rails::Context &c = ctx();
+    const int k = xn[0];
+    const long long rows = Q->rows;
+    const bool reduce = dist && Q->flags == RAILS_MV_DISTRIBUTED && c.comm;
+    *steps = 0;
+
+    // device scratch: g[total] | coef[total] | a[L] | b2[L + 1]   (b2[0] = |q_0|^2)
+    const size_t need = 2 * (size_t)std::max(total, 1) + 2 * (size_t)L + 1;
+    rc = rails::ensure_small(need);
+    if (rc) return rc;
+    double *g = c.d_small, *coef = g + std::max(total, 1), *a = coef + std::max(total, 1), *b2 = a + L;
+    const double *dT = nullptr;
+    if (k > 0)
+    {
+        rc = rails::upload_small(T, k, k, ldt, &dT);
+        if (rc) return rc;
+    }
+
+    if (rows == 0)
+        RAILS_CUDA_TRY(cudaMemsetAsync(c.d_small, 0, need * sizeof(double), c.stream));
+    const long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
+    const int nb_dot = (int)std::max<long long>(1, std::min<long long>(ntiles, (long long)c.sm_count * 4));
+    const long long rows2 = (rows + 1) / 2;
+    const int nb_gemv = (int)std::max<long long>(1, (rows2 + (long long)MG_THREADS * MG_RP - 1) / ((long long)MG_THREADS * MG_RP));
+    const int nb_upd = (int)std::max<long long>(1, std::min<long long>((rows / 2 + LU_THREADS - 1) / LU_THREADS,
+                                                                      (long long)c.sm_count * 8));
+    rc = rails::ensure_partial(std::max<size_t>((size_t)nb_dot * std::max(total, 1), std::max(nb_gemv, nb_upd)));
+    if (rc) return rc;
+    static bool attr_set = false;
+    if (!attr_set)
+    {
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(multi_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            MD_MAXCOLS * MD_WARPS * (int)sizeof(double)));
+        attr_set = true;
+    }
+    auto allreduce = [&](double *p, size_t n) -> int {
+        if (reduce)
+            RAILS_NCCL_TRY(ncclAllReduce(p, p, n, ncclDouble, ncclSum, c.comm, c.stream));
+        return RAILS_OK;
+    };
+
+    if (rows > 0)
+    {
+        // |q_0|^2 -> b2[0]  (`Q.view(0) /= Q.norm()`, :375; applied by step 0's multi_dot)
+        const double *q0 = Q->data + (size_t)qc0 * Q->ld;
+        rc = rails::dot_device(q0, Q->ld, 1, q0, Q->ld, 1, rows, b2, 1, reduce);
+        if (rc) return rc;
+        for (int i = 0; i < L; ++i)
+        {
+            double *q = Q->data + (size_t)(qc0 + i) * Q->ld;
+            double *next = q + Q->ld;
+            // g = [X_0 X_1 ..]' (q / |q|), q normalised in place
+            RAILS_LAUNCH(multi_dot_kernel, nb_dot, MD_THREADS, (size_t)std::max(total, 1) * MD_WARPS * sizeof(double),
+                         S, total, q, 1.0, 1, rows, c.d_partial, (const double *)(b2 + i));
+            if (total > 0)
+            {
+                RAILS_LAUNCH(sum_partials_kernel, total, 256, 0, c.d_partial, nb_dot, total, g, 0);
+                rc = allreduce(g, total);
+                if (rc) return rc;
+                const int warps = 2 * k + (total - 2 * k + 31) / 32;
+                RAILS_LAUNCH(lanczos_coef_kernel, (warps * 32 + 255) / 256, 256, 0, dT, k, total, g, coef);
+            }
+            // next = sum_b X_b coef_b ; a[i] = next' q
+            RAILS_LAUNCH(multi_gemv_kernel, nb_gemv, MG_THREADS, (size_t)std::max(total, 1) * sizeof(double),
+                         S, total, coef, next, q, rows, c.d_partial);
+            RAILS_LAUNCH(sum_partials_kernel, 1, 256, 0, c.d_partial, nb_gemv, 1, a + i, 0);
+            rc = allreduce(a + i, 1);
+            if (rc) return rc;
+            // next -= a[i] q + beta_{i-1} q_prev ; b2[i + 1] = |next|^2
+            RAILS_LAUNCH(lanczos_update_kernel, nb_upd, LU_THREADS, 0, next, q,
+                         i > 0 ? (const double *)(q - Q->ld) : (const double *)nullptr, 0.0, 0.0, rows,
+                         c.d_partial, (const double *)(a + i), i > 0 ? (const double *)(b2 + i) : (const double *)nullptr);
+            RAILS_LAUNCH(sum_partials_kernel, 1, 256, 0, c.d_partial, nb_upd, 1, b2 + i + 1, 0);
+            RAILS_CHECK_LAUNCH();
+            rc = allreduce(b2 + i + 1, 1);
+            if (rc) return rc;
+        }
+    }
+    // one read-back for the whole recurrence
+    RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, a, (2 * (size_t)L + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    int done = 0;
+    for (int i = 0; i < L; ++i)
+    {
+        alpha[i] = c.h_small[i];
+        beta[i] = std::sqrt(std::fabs(c.h_small[L + 1 + i]));
+        done = i + 1;
+        if (beta[i] < 1e-14)
+            break;
+    }
+    *steps = done;
     return RAILS_OK;
 }

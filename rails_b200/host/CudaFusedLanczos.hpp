@@ -30,15 +30,69 @@ namespace RAILS
 namespace b200
 {
 
+// The projection dots with one host round trip (rails_mv_dot_batch).
+template<>
+struct BatchedDots<CudaMultiVectorWrapper, HostDenseMatrix>
+{
+    static void run(std::vector<std::pair<CudaMultiVectorWrapper const *, CudaMultiVectorWrapper const *> > const &pairs,
+                    std::vector<HostDenseMatrix> &out)
+    {
+        const int n = (int)pairs.size();
+        out.clear();
+        std::vector<rails_mv_t> X(n), Y(n);
+        std::vector<int> xc(n), a(n), yc(n), b(n), ld(n);
+        std::vector<double *> ptr(n);
+        bool ok = true;
+        for (int i = 0; i < n; ++i)
+        {
+            CudaMultiVectorWrapper const &x = *pairs[i].first, &y = *pairs[i].second;
+            out.push_back(HostDenseMatrix(x.N(), y.N()));
+            X[i] = x.device_handle(); Y[i] = y.device_handle();
+            xc[i] = x.device_col0(); yc[i] = y.device_col0();
+            a[i] = x.N(); b[i] = y.N();
+            if (x.M() != y.M() || ((!X[i] || !Y[i]) && a[i] > 0 && b[i] > 0))
+                ok = false;
+            if (!X[i] || !Y[i]) { a[i] = 0; b[i] = 0; X[i] = X[i] ? X[i] : Y[i]; Y[i] = Y[i] ? Y[i] : X[i]; }
+        }
+        for (int i = 0; i < n; ++i)
+        {
+            ptr[i] = out[i];
+            ld[i] = std::max(out[i].LDA(), 1);
+            if (!X[i]) ok = false;
+        }
+        if (!ok)
+        {
+            // irregular operands: the plain sequence reports the problem as dot() does
+            out.clear();
+            for (int i = 0; i < n; ++i)
+                out.push_back(pairs[i].first->dot(*pairs[i].second));
+            return;
+        }
+        int rc = rails_mv_dot_batch(n, X.data(), xc.data(), a.data(), Y.data(), yc.data(), b.data(),
+                                    ptr.data(), ld.data());
+        if (rc)
+            std::cerr << "BatchedDots failed (" << rc << "): " << rails_cuda_last_error() << std::endl;
+    }
+};
+
 template<>
 struct FusedLanczos<CudaMultiVectorWrapper, HostDenseMatrix>
 {
     static const bool enabled = true;
 
+    // RAILS_FUSED_LANCZOS: unset / "1" = the device-resident chain
+    // (rails_mv_lanczos_run: no host round trip inside the recurrence),
+    // "step" = three fused kernels per step with the k x k products on the host,
+    // "0" = the operation-by-operation sequence of the reference.
     static bool active()
     {
         const char *e = std::getenv("RAILS_FUSED_LANCZOS");
         return !(e && std::strcmp(e, "0") == 0);
+    }
+    static bool per_step()
+    {
+        const char *e = std::getenv("RAILS_FUSED_LANCZOS");
+        return e && std::strcmp(e, "step") == 0;
     }
 
     static void report(int rc, const char *what)
@@ -60,16 +114,37 @@ struct FusedLanczos<CudaMultiVectorWrapper, HostDenseMatrix>
             std::cerr << "FusedLanczos: inconsistent sizes" << std::endl;
             return 0;
         }
-        // `Q.view(0) /= Q.norm()` (:375): the reciprocal is rounded first, the
-        // scaling itself happens inside the first multi_dot
-        double qscale = 1.0 / Q.norm();
-
         Q.resize(max_iter + 1);
         rails_mv_t hq = Q.device_handle();
         const int q0 = Q.device_col0();
         rails_mv_t blocks[3] = {V.device_handle(), AV.device_handle(), B.device_handle()};
         int col0[3] = {V.device_col0(), AV.device_col0(), B.device_col0()};
         int ncols[3] = {k, k, n};
+
+        if (!per_step())
+        {
+            std::vector<double> a(max_iter), b(max_iter);
+            int done = 0;
+            report(rails_mv_lanczos_run(3, blocks, col0, ncols, T, T.LDA(), hq, q0, max_iter, a.data(),
+                                        b.data(), &done), "lanczos_run");
+            for (int i = 0; i < done; ++i)
+            {
+                H(i, i) = a[i];
+                if (b[i] < 1e-14)
+                    break;                      // breakdown: no off-diagonal entry (:419-427)
+                H(i + 1, i) = b[i];
+                H(i, i + 1) = b[i];
+                if (std::getenv("RAILS_DEBUG_LANCZOS"))
+                    std::cerr << "lanczos chain step " << i << " alpha " << a[i] << " beta " << b[i] << std::endl;
+            }
+            return done;
+        }
+
+        // `Q.view(0) /= Q.norm()` (:375): the reciprocal is rounded first, the
+        // scaling itself happens inside the first multi_dot
+        Q.resize(1);
+        double qscale = 1.0 / Q.norm();
+        Q.resize(max_iter + 1);
 
         std::vector<double> g(2 * k + n), coef(2 * k + n);
         HostDenseMatrix Z(k, 1);

@@ -102,6 +102,20 @@ struct FusedLanczos
                    MultiVector const &, DenseMatrix &, MultiVector &, int) { return -1; }
 };
 
+// Customisation point: several independent inner products X_i' Y_i returned
+// with one host round trip.  The primary template just calls dot() in order.
+template<class MultiVector, class DenseMatrix>
+struct BatchedDots
+{
+    static void run(std::vector<std::pair<MultiVector const *, MultiVector const *> > const &pairs,
+                    std::vector<DenseMatrix> &out)
+    {
+        out.clear();
+        for (size_t i = 0; i < pairs.size(); ++i)
+            out.push_back(pairs[i].first->dot(*pairs[i].second));
+    }
+};
+
 struct IterationRecord
 {
     int iteration;        // 1-based

@@ -65,10 +65,34 @@ void Solver<Matrix, MultiVector, DenseMatrix>::project(
     VAV.resize(size, size);          // keeps the old entries
     VBV.resize(size, size);
 
+    // the dots of :173-195 (and of the mass-matrix branch), same operands and
+    // the same order as the reference; a backend may return them with one host
+    // round trip (BatchedDots)
+    typedef std::pair<MultiVector const *, MultiVector const *> Pair;
+    std::vector<Pair> pairs;
+    int i_wav = -1, i_wbv = -1, i_vaw = -1, i_wbw = -1, i_wmv = -1, i_vmw = -1;
     if (old_cols > 0)
     {
-        DenseMatrix WAV = W.dot(AV);
-        DenseMatrix WBV = BW.dot(BV);
+        i_wav = (int)pairs.size(); pairs.push_back(Pair(&W, &AV));
+        i_wbv = (int)pairs.size(); pairs.push_back(Pair(&BW, &BV));
+    }
+    i_vaw = (int)pairs.size(); pairs.push_back(Pair(&V, &AW));
+    i_wbw = (int)pairs.size(); pairs.push_back(Pair(&BW, &BW));
+    if (use_mass_)
+    {
+        if (old_cols > 0)
+        {
+            i_wmv = (int)pairs.size(); pairs.push_back(Pair(&W, &MV));
+        }
+        i_vmw = (int)pairs.size(); pairs.push_back(Pair(&V, &MW));
+    }
+    std::vector<DenseMatrix> G;
+    BatchedDots<MultiVector, DenseMatrix>::run(pairs, G);
+
+    if (old_cols > 0)
+    {
+        DenseMatrix const &WAV = G[i_wav];
+        DenseMatrix const &WBV = G[i_wbv];
         for (int i = 0; i < WAV.M(); i++)
             for (int j = 0; j < WAV.N(); j++)
             {
@@ -78,12 +102,12 @@ void Solver<Matrix, MultiVector, DenseMatrix>::project(
             }
     }
 
-    DenseMatrix VAW = V.dot(AW);
+    DenseMatrix const &VAW = G[i_vaw];
     for (int i = 0; i < VAW.M(); i++)
         for (int j = 0; j < VAW.N(); j++)
             VAV(i, j + old_cols) = VAW(i, j);
 
-    DenseMatrix WBW = BW.dot(BW);
+    DenseMatrix const &WBW = G[i_wbw];
     for (int i = 0; i < WBW.M(); i++)
         for (int j = 0; j < WBW.N(); j++)
             VBV(i + old_cols, j + old_cols) = WBW(i, j);
@@ -94,12 +118,12 @@ void Solver<Matrix, MultiVector, DenseMatrix>::project(
         VMV.resize(size, size);
         if (old_cols > 0)
         {
-            DenseMatrix WMV = W.dot(MV);
+            DenseMatrix const &WMV = G[i_wmv];
             for (int i = 0; i < WMV.M(); i++)
                 for (int j = 0; j < WMV.N(); j++)
                     VMV(i + old_cols, j) = WMV(i, j);
         }
-        DenseMatrix VMW = V.dot(MW);
+        DenseMatrix const &VMW = G[i_vmw];
         for (int i = 0; i < VMW.M(); i++)
             for (int j = 0; j < VMW.N(); j++)
                 VMV(i, j + old_cols) = VMW(i, j);

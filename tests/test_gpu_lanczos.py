@@ -81,6 +81,55 @@ def test_lanczos_update(gpu, m):
         assert abs(nrm.value - np.linalg.norm(want)) <= 1e-14 * np.linalg.norm(want) * 10
 
 
+@pytest.mark.parametrize("m,k,n,L", [(5000, 7, 2, 6), (100003, 33, 1, 10), (2048, 0, 3, 2), (64, 3, 1, 12)])
+def test_lanczos_run_matches_the_recurrence(gpu, m, k, n, L):
+    """rails_mv_lanczos_run (device-resident chain) against a numpy restatement
+    of src/LyapunovSolver.hpp:375-434 on the same blocks."""
+    lib = gpu.cuda()
+    rs = np.random.RandomState(m + k)
+    V = np.linalg.qr(rs.uniform(-1, 1, (m, max(k, 1))))[0][:, :k]
+    AV = rs.uniform(-1, 1, (m, k))
+    B = rs.uniform(-1, 1, (m, n))
+    T = rs.uniform(-1, 1, (k, k)); T = np.asfortranarray(T + T.T)
+    q0 = rs.uniform(-1, 1, m)
+    # reference recurrence
+    Q = np.zeros((m, L + 1)); Q[:, 0] = q0 / np.linalg.norm(q0)
+    al, be = [], []
+    for i in range(L):
+        q = Q[:, i]
+        nxt = B @ (B.T @ q) + AV @ (T @ (V.T @ q)) + V @ (T @ (AV.T @ q))
+        a = nxt @ q
+        nxt = nxt - a * q - (be[-1] * Q[:, i - 1] if i else 0.0)
+        b = np.linalg.norm(nxt)
+        al.append(a); be.append(b)
+        if b < 1e-14:
+            break
+        Q[:, i + 1] = nxt / b
+    mvs, hs, c0, nn = _blocks(gpu, [np.asfortranarray(V), np.asfortranarray(AV), np.asfortranarray(B)])
+    Qd = gpu.MultiVector(m, L + 2)
+    gpu.check(lib.rails_mv_upload(Qd.h, 1, 1, gpu.dptr(np.asfortranarray(q0.reshape(-1, 1))), m), "upload")
+    a_out, b_out = np.zeros(L), np.zeros(L)
+    steps = ctypes.c_int(0)
+    Tp = T if k else np.zeros((1, 1), order="F")
+    gpu.check(lib.rails_mv_lanczos_run(3, hs, c0, nn, gpu.dptr(Tp), max(k, 1), Qd.h, 1, L, gpu.dptr(a_out),
+                                       gpu.dptr(b_out), ctypes.byref(steps)), "lanczos_run")
+    assert steps.value == len(al)
+    # without re-orthogonalisation rounding differences grow along the recurrence
+    scale = max(abs(x) for x in al + be)
+    for i in range(min(steps.value, 4)):
+        assert abs(a_out[i] - al[i]) <= 1e-10 * scale, (i, a_out[i], al[i])
+        assert abs(b_out[i] - be[i]) <= 1e-10 * scale, (i, b_out[i], be[i])
+    got = Qd.numpy(1, 3)
+    assert np.max(np.abs(got[:, 0] - Q[:, 0])) < 1e-15
+    assert np.max(np.abs(got[:, 1] - Q[:, 1])) < 1e-11
+    # the tridiagonal's extreme Ritz value is what the solver uses
+    def top(a, b):
+        H = np.diag(a) + np.diag(b[:-1], 1) + np.diag(b[:-1], -1)
+        return np.max(np.abs(np.linalg.eigvalsh(H)))
+    n_ok = steps.value
+    assert abs(top(a_out[:n_ok], b_out[:n_ok]) - top(np.array(al), np.array(be))) <= 1e-8 * scale
+
+
 def test_block_errors(gpu):
     lib = gpu.cuda()
     A = gpu.MultiVector(10, 3)
@@ -100,14 +149,18 @@ def test_block_errors(gpu):
 def test_fused_loop_matches_unfused_loop(gpu, kind, g, dim, n_b):
     rp, ci, v = problems.build(kind, g, dim)
     Pm = {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 10}
-    fused = gpu.solve(rp, ci, v, n_b, Pm, v_cap_cols=400)
-    os.environ["RAILS_FUSED_LANCZOS"] = "0"
-    try:
-        plain = gpu.solve(rp, ci, v, n_b, Pm, v_cap_cols=400)
-    finally:
-        del os.environ["RAILS_FUSED_LANCZOS"]
-    assert (fused["ret"], fused["iterations"], fused["k"]) == (plain["ret"], plain["iterations"], plain["k"])
-    rel = np.abs(fused["rel"] - plain["rel"]) / plain["rel"]
-    assert np.max(rel[:10]) < 1e-8
-    assert np.max(rel) < 1e-4
-    assert harness.lowrank_rel_diff(fused["V"], fused["T"], plain["V"], plain["T"]) < 1e-6
+    runs = {}
+    for mode in ("1", "step", "0"):      # device-resident chain, per-step fused, operation by operation
+        os.environ["RAILS_FUSED_LANCZOS"] = mode
+        try:
+            runs[mode] = gpu.solve(rp, ci, v, n_b, Pm, v_cap_cols=400)
+        finally:
+            del os.environ["RAILS_FUSED_LANCZOS"]
+    plain = runs["0"]
+    for mode in ("1", "step"):
+        fused = runs[mode]
+        assert (fused["ret"], fused["iterations"], fused["k"]) == (plain["ret"], plain["iterations"], plain["k"])
+        rel = np.abs(fused["rel"] - plain["rel"]) / plain["rel"]
+        assert np.max(rel[:10]) < 1e-8
+        assert np.max(rel) < 1e-4
+        assert harness.lowrank_rel_diff(fused["V"], fused["T"], plain["V"], plain["T"]) < 1e-6

@@ -427,6 +427,8 @@ def run_b200(args):
                    "window": "iterations W+1..W+K of one solve, convergence test off",
                    "l2": "inputs >> L2 (no flush): V is %.0f MB per column" % (rows * 8 / 1e6),
                    "parallelism": "row partition over %d GPU(s)" % world,
+                   "small_reductions": ("peer-memory mailboxes (NVLink P2P)" if lib.rails_cuda_comm_p2p()
+                                        else "NCCL all-reduce") if world > 1 else "local",
                    "space_size_in_window": [int(res["space"][W]) if W < len(res["space"]) else None,
                                             int(res["space"][min(W + K, len(res["space"])) - 1])]},
         "e2e": {"value": e2e["iterations"] / wall, "unit": "iterations/s",

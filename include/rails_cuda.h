@@ -75,6 +75,9 @@ int rails_cuda_event_elapsed_ms(int start_slot, int stop_slot, float *ms);
  *      src/main.cpp:47) ------------------------------------------------- */
 int rails_cuda_comm_unique_id(char id[RAILS_NCCL_ID_BYTES]);
 int rails_cuda_comm_init(int rank, int nranks, const char id[RAILS_NCCL_ID_BYTES]);
+/* 1 when small reductions go through the peer-memory mailboxes (NVLink/NVSwitch,
+ * CUDA IPC), 0 when they use NCCL all-reduce */
+int rails_cuda_comm_p2p(void);
 int rails_cuda_comm_rank(void);
 int rails_cuda_comm_size(void);
 /* Epetra_Map(m, 0, comm) linear map: rows [begin, end) of rank r of P */

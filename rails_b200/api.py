@@ -70,6 +70,7 @@ CUDA_SYMBOLS = [
     ("rails_cuda_event_elapsed_ms", I, [I, I, ctypes.POINTER(ctypes.c_float)]),
     ("rails_cuda_comm_unique_id", I, [ctypes.c_char_p]),
     ("rails_cuda_comm_init", I, [I, I, ctypes.c_char_p]),
+    ("rails_cuda_comm_p2p", I, []),
     ("rails_cuda_comm_rank", I, []),
     ("rails_cuda_comm_size", I, []),
     ("rails_partition_rows", I, [LL, I, I, ctypes.POINTER(LL), ctypes.POINTER(LL)]),

@@ -247,6 +247,7 @@ extern "C" int rails_cuda_finalize(void)
     if (!c.ready)
         return RAILS_OK;
     cudaStreamSynchronize(c.stream);
+    rails::release_mailboxes();
     if (c.comm) { ncclCommDestroy(c.comm); c.comm = nullptr; }
     for (auto &ev : c.events)
         if (ev) { cudaEventDestroy(ev); ev = nullptr; }
@@ -327,6 +328,7 @@ extern "C" int rails_cuda_comm_init(int rank, int nranks, const char id[RAILS_NC
     rails::Context &c = ctx();
     if (nranks < 1 || rank < 0 || rank >= nranks)
         return rails::fail(RAILS_ERR_ARG, "bad rank %d of %d", rank, nranks);
+    rails::release_mailboxes();
     if (c.comm) { ncclCommDestroy(c.comm); c.comm = nullptr; }
     c.rank = rank;
     c.nranks = nranks;
@@ -335,9 +337,21 @@ extern "C" int rails_cuda_comm_init(int rank, int nranks, const char id[RAILS_NC
     ncclUniqueId uid;
     memcpy(&uid, id, sizeof(uid));
     RAILS_NCCL_TRY(ncclCommInitRank(&c.comm, nranks, uid, rank));
-    return RAILS_OK;
+    // NCCL connects lazily: pay for that here, not inside the first solve
+    {
+        double *w = nullptr;
+        RAILS_CUDA_TRY(cudaMalloc(&w, 65536 * sizeof(double)));
+        RAILS_CUDA_TRY(cudaMemset(w, 0, 65536 * sizeof(double)));
+        for (size_t n : {(size_t)1, (size_t)256, (size_t)65536})
+            RAILS_NCCL_TRY(ncclAllReduce(w, w, n, ncclDouble, ncclSum, c.comm, c.stream));
+        RAILS_NCCL_TRY(ncclAllReduce(w, w, 1, ncclDouble, ncclMax, c.comm, c.stream));
+        RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+        cudaFree(w);
+    }
+    return rails::setup_mailboxes();
 }
 
+extern "C" int rails_cuda_comm_p2p(void) { return ctx().p2p ? 1 : 0; }
 extern "C" int rails_cuda_comm_rank(void) { return ctx().rank; }
 extern "C" int rails_cuda_comm_size(void) { return ctx().nranks; }
 

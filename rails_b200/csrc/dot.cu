@@ -237,7 +237,8 @@ int dot_device(const double *X, long long ldx, int a, const double *Y, long long
     {
         if (ldo != a)
             return fail(RAILS_ERR_ARG, "dot_device: rank reduction needs a compact result");
-        RAILS_NCCL_TRY(ncclAllReduce(d_out, d_out, (size_t)a * b, ncclDouble, ncclSum, c.comm, c.stream));
+        int rc = finish_reduction(d_out, 1, a * b, d_out, true);
+        if (rc) return rc;
     }
     return RAILS_OK;
 }
@@ -328,7 +329,10 @@ extern "C" int rails_mv_dot_batch(int count, const rails_mv_t *X, const int *xc0
         if (pass == 0) ndist = pos;
     }
     if (ndist && c.comm)
-        RAILS_NCCL_TRY(ncclAllReduce(c.d_small, c.d_small, ndist, ncclDouble, ncclSum, c.comm, c.stream));
+    {
+        rc = rails::finish_reduction(c.d_small, 1, (int)ndist, c.d_small, true);
+        if (rc) return rc;
+    }
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, total * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
     for (int i = 0; i < count; ++i)

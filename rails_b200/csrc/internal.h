@@ -57,6 +57,19 @@ struct rails_csr_s
 namespace rails
 {
 
+// Peer-memory mailboxes for small reductions over NVLink/NVSwitch: every rank
+// maps every other rank's mailbox (CUDA IPC) and the reduction kernel stores
+// its contribution straight into the peers' memory (exchange.cu).
+constexpr int MB_MAX_RANKS = 8;
+constexpr int MB_SLOTS = 4;
+constexpr int MB_MAXN = 2048;          // doubles per contribution
+struct Mailbox
+{
+    double *data[MB_MAX_RANKS];               // rank p's data area: [slot][writer][MB_MAXN]
+    unsigned long long *flags[MB_MAX_RANKS];  // rank p's flags:     [slot][writer]
+    int rank, nranks;
+};
+
 struct Context
 {
     bool ready = false;
@@ -82,6 +95,13 @@ struct Context
     ncclComm_t comm = nullptr;
     int rank = 0;
     int nranks = 1;
+    // peer mailboxes (nranks > 1 and all peers reachable over NVLink)
+    bool p2p = false;
+    Mailbox mb;
+    void *mb_local = nullptr;
+    void *mb_mapped[MB_MAX_RANKS] = {nullptr};
+    unsigned long long mb_seq = 0;           // exchanges issued so far (same on every rank)
+    int *d_mb_error = nullptr;               // set by a kernel whose wait timed out
     std::atomic<long long> launches{0};
     std::atomic<long long> bytes_in_use{0};
     std::vector<cudaEvent_t> events;
@@ -102,6 +122,17 @@ int upload_small(const double *host, int k, int c, int ldc, const double **d_out
 // (the host block may be reused / is complete on return).
 int copy_h2d(void *dst, const void *src, size_t bytes);
 int copy_d2h(void *dst, const void *src, size_t bytes);
+
+// Finishes a reduction and, with a communicator, sums it over the ranks, in ONE
+// kernel: out[i] = sum over ranks of (sum_b partial[b * n + i]), b < nblocks.
+// `partial` may alias `out` when nblocks == 1 (plain all-reduce of n doubles).
+// With T != NULL (k x k, compact) it continues with the Lanczos coefficient
+// products: coef = [T out[k:2k) ; T out[0:k) ; out[2k:n)].
+// Uses the peer mailboxes when available, otherwise a second-stage kernel + NCCL.
+int finish_reduction(const double *partial, int nblocks, int n, double *out, bool over_ranks,
+                     const double *T = nullptr, int k = 0, double *coef = nullptr);
+int setup_mailboxes();
+void release_mailboxes();
 
 // device-side kernels callable across translation units
 int dot_device(const double *X, long long ldx, int a, const double *Y,

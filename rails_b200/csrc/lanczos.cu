@@ -231,7 +231,10 @@ int finish_to_host(int n, bool distributed, double *out)
 {
     rails::Context &c = ctx();
     if (distributed && c.comm)
-        RAILS_NCCL_TRY(ncclAllReduce(c.d_small, c.d_small, (size_t)n, ncclDouble, ncclSum, c.comm, c.stream));
+    {
+        int rc = rails::finish_reduction(c.d_small, 1, n, c.d_small, true);
+        if (rc) return rc;
+    }
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, (size_t)n * sizeof(double),
                                    cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
@@ -559,38 +562,6 @@ extern "C" int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, ra
     return RAILS_OK;
 }
 
-namespace
-{
-
-// coef = [T g_1 ; T g_0 ; g_rest]: the k x k products `Z = T * Z` of
-// src/LyapunovSolver.hpp:395,401 on the device (T compact, ld = k).  One warp
-// per output row; each lane adds its columns in order, then a shuffle tree.
-__global__ void __launch_bounds__(256)
-lanczos_coef_kernel(const double *__restrict__ T, int k, int total, const double *__restrict__ g,
-                    double *__restrict__ coef)
-{
-    const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (warp < 2 * k)
-    {
-        const int j = warp < k ? warp : warp - k;
-        // rows [0, k): coefficient of block 0 = T * g(block 1); rows [k, 2k): block 1 = T * g(block 0)
-        const double *gv = warp < k ? g + k : g;
-        double s = 0.0;
-        for (int l = lane; l < k; l += 32)
-            s = fma(T[j + (size_t)l * k], gv[l], s);
-        for (int o = 16; o > 0; o >>= 1)
-            s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) coef[warp] = s;
-    }
-    else
-    {
-        const int i = 2 * k + (warp - 2 * k) * 32 + lane;
-        if (i < total) coef[i] = g[i];
-    }
-}
-
-}
-
 // The whole L-step recurrence of Solver::resid_lanczos
 // (src/LyapunovSolver.hpp:375-434) as ONE asynchronous chain on the library
 // stream: no value returns to the host until the last step has been enqueued.
@@ -655,12 +626,6 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
                                             MD_MAXCOLS * MD_WARPS * (int)sizeof(double)));
         attr_set = true;
     }
-    auto allreduce = [&](double *p, size_t n) -> int {
-        if (reduce)
-            RAILS_NCCL_TRY(ncclAllReduce(p, p, n, ncclDouble, ncclSum, c.comm, c.stream));
-        return RAILS_OK;
-    };
-
     if (rows > 0)
     {
         // |q_0|^2 -> b2[0]  (`Q.view(0) /= Q.norm()`, :375; applied by step 0's multi_dot)
@@ -676,31 +641,33 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
                          S, total, q, 1.0, 1, rows, c.d_partial, (const double *)(b2 + i));
             if (total > 0)
             {
-                RAILS_LAUNCH(sum_partials_kernel, total, 256, 0, c.d_partial, nb_dot, total, g, 0);
-                rc = allreduce(g, total);
+                // partials -> g, summed over the ranks, and coef = [T g_1; T g_0; g_rest]: one kernel
+                rc = rails::finish_reduction(c.d_partial, nb_dot, total, g, reduce, dT, k, coef);
                 if (rc) return rc;
-                const int warps = 2 * k + (total - 2 * k + 31) / 32;
-                RAILS_LAUNCH(lanczos_coef_kernel, (warps * 32 + 255) / 256, 256, 0, dT, k, total, g, coef);
             }
             // next = sum_b X_b coef_b ; a[i] = next' q
             RAILS_LAUNCH(multi_gemv_kernel, nb_gemv, MG_THREADS, (size_t)std::max(total, 1) * sizeof(double),
                          S, total, coef, next, q, rows, c.d_partial);
-            RAILS_LAUNCH(sum_partials_kernel, 1, 256, 0, c.d_partial, nb_gemv, 1, a + i, 0);
-            rc = allreduce(a + i, 1);
+            RAILS_CHECK_LAUNCH();
+            rc = rails::finish_reduction(c.d_partial, nb_gemv, 1, a + i, reduce);
             if (rc) return rc;
             // next -= a[i] q + beta_{i-1} q_prev ; b2[i + 1] = |next|^2
             RAILS_LAUNCH(lanczos_update_kernel, nb_upd, LU_THREADS, 0, next, q,
                          i > 0 ? (const double *)(q - Q->ld) : (const double *)nullptr, 0.0, 0.0, rows,
                          c.d_partial, (const double *)(a + i), i > 0 ? (const double *)(b2 + i) : (const double *)nullptr);
-            RAILS_LAUNCH(sum_partials_kernel, 1, 256, 0, c.d_partial, nb_upd, 1, b2 + i + 1, 0);
             RAILS_CHECK_LAUNCH();
-            rc = allreduce(b2 + i + 1, 1);
+            rc = rails::finish_reduction(c.d_partial, nb_upd, 1, b2 + i + 1, reduce);
             if (rc) return rc;
         }
     }
     // one read-back for the whole recurrence
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, a, (2 * (size_t)L + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    int xerr = 0;
+    if (c.d_mb_error)
+        RAILS_CUDA_TRY(cudaMemcpyAsync(&xerr, c.d_mb_error, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    if (xerr)
+        return rails::fail(RAILS_ERR_CUDA, "lanczos_run: a peer did not answer a reduction (mailbox wait timed out)");
     int done = 0;
     for (int i = 0; i < L; ++i)
     {

@@ -32,6 +32,8 @@ def main():
         ident[0] = buf.raw
     dist.broadcast_object_list(ident, src=0)
     api.check(lib.rails_cuda_comm_init(rank, world, ident[0]), "comm_init")
+    if rank == 0:
+        print("small reductions:", "peer mailboxes" if lib.rails_cuda_comm_p2p() else "NCCL", flush=True)
 
     def gather_rows(a):
         parts = [None] * world

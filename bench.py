@@ -15,7 +15,9 @@ M)  With N > 1 the SAME matrix is row-partitioned over the ranks
 (Epetra linear map): "scaling": "strong".
 
 Timed region (`value`): iterations W+1 .. W+K of one solve started from scratch
-with the convergence test off (so exactly K iterations run for any K),
+with the convergence test off (so exactly K iterations run for any K), after
+one untimed solve of the same kind that absorbs the process's one-off costs
+(memory-pool growth, lazy kernel loading; reported as first_solve_wall_s),
 bracketed by CUDA events on the library stream with everything resident in HBM
 (each rank reports its own event time; the max over ranks is used).  Inputs are
 far larger than the 126 MB L2 (V alone is 134 MB per column), so there is no
@@ -337,6 +339,18 @@ def run_b200(args):
         return
     W, K = args.warmup, args.steps
 
+    # ---- warm-up solve (untimed): the first solve of a process pays one-off
+    #      costs that are not per-iteration work -- growth of the stream-ordered
+    #      memory pool (V/AV/Q/restart temporaries, tens of ms per GB), lazy
+    #      loading of each kernel on first launch, NCCL/peer-mapping first use.
+    #      Measured on C3: first solve 456 ms for the window, second 358 ms.
+    t_cold = time.time()
+    cold = api.solve(rp, ci, v, n_b, window_params(params, W, K), B=B, global_rows=m, row_offset=r0, M=M)
+    lib.rails_cuda_sync()
+    t_cold = time.time() - t_cold
+    if cold["ret"] >= 100:
+        raise SystemExit("rails_host_solve (warm-up) failed with code %d" % cold["ret"])
+
     # ---- leg 1: device-timed window, everything resident in HBM -------------
     sampler = ClockSampler(local)
     if dist is not None:
@@ -444,6 +458,7 @@ def run_b200(args):
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
         "kernels": kernels,
+        "first_solve_wall_s": t_cold,
         "dense_solve_seconds": res["dense_solve_seconds"],
         "solve_seconds": res["solve_seconds"], "setup_seconds": res["setup_seconds"],
         "relative_residual": [float(e2e["rel"][0]), float(e2e["rel"][-1])],

@@ -49,7 +49,7 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __global__ void __launch_bounds__(FX_THREADS)
 finish_exchange_kernel(const double *partial, int nblocks, int n, double *out, Mailbox mb,
                        unsigned long long seq, int *error, const double *__restrict__ T, int k,
-                       double *__restrict__ coef)
+                       double *__restrict__ coef, double *norm_out, const double *scale_sq)
 {
     __shared__ double sm[FX_THREADS];
     extern __shared__ double res[];          // n doubles: the finished result
@@ -137,6 +137,25 @@ finish_exchange_kernel(const double *partial, int nblocks, int n, double *out, M
         }
         __syncthreads();
     }
+    // optional scaling by a squared norm held on the device
+    if (norm_out)
+    {
+        const double sq = res[n - 1];
+        __syncthreads();
+        if (t == 0) *norm_out = sq;
+        n -= 1;
+        const double sc = 1.0 / sqrt(fabs(sq));
+        for (int i = t; i < n; i += FX_THREADS)
+            res[i] *= sc;
+        __syncthreads();
+    }
+    else if (scale_sq)
+    {
+        const double sc = 1.0 / sqrt(fabs(*scale_sq));
+        for (int i = t; i < n; i += FX_THREADS)
+            res[i] *= sc;
+        __syncthreads();
+    }
     for (int i = t; i < n; i += FX_THREADS)
         out[i] = res[i];
 
@@ -202,13 +221,27 @@ coef_plain_kernel(const double *__restrict__ T, int k, int n, const double *__re
     }
 }
 
+__global__ void scale_plain_kernel(double *v, int n, double *norm_out, const double *scale_sq)
+{
+    // single CTA
+    __shared__ double sc;
+    if (threadIdx.x == 0)
+    {
+        if (norm_out) { *norm_out = v[n]; sc = 1.0 / sqrt(fabs(v[n])); }
+        else sc = 1.0 / sqrt(fabs(*scale_sq));
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x)
+        v[i] *= sc;
+}
+
 }
 
 namespace rails
 {
 
 int finish_reduction(const double *partial, int nblocks, int n, double *out, bool over_ranks,
-                     const double *T, int k, double *coef)
+                     const double *T, int k, double *coef, double *norm_out, const double *scale_sq)
 {
     Context &c = ctx();
     if (n <= 0) return RAILS_OK;
@@ -227,7 +260,7 @@ int finish_reduction(const double *partial, int nblocks, int n, double *out, boo
             attr = true;
         }
         RAILS_LAUNCH(finish_exchange_kernel, 1, FX_THREADS, (size_t)n * sizeof(double), partial, nblocks, n, out,
-                     mb, seq, c.d_mb_error, T, k, coef);
+                     mb, seq, c.d_mb_error, T, k, coef, norm_out, scale_sq);
         RAILS_CHECK_LAUNCH();
         return RAILS_OK;
     }
@@ -238,6 +271,12 @@ int finish_reduction(const double *partial, int nblocks, int n, double *out, boo
     }
     if (multi)
         RAILS_NCCL_TRY(ncclAllReduce(out, out, (size_t)n, ncclDouble, ncclSum, c.comm, c.stream));
+    if (norm_out || scale_sq)
+    {
+        if (norm_out) n -= 1;
+        RAILS_LAUNCH(scale_plain_kernel, 1, 256, 0, out, n, norm_out, scale_sq);
+        RAILS_CHECK_LAUNCH();
+    }
     if (coef)
     {
         const int warps = 2 * k + (n - 2 * k + 31) / 32;

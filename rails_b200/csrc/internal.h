@@ -129,8 +129,13 @@ int copy_d2h(void *dst, const void *src, size_t bytes);
 // With T != NULL (k x k, compact) it continues with the Lanczos coefficient
 // products: coef = [T out[k:2k) ; T out[0:k) ; out[2k:n)].
 // Uses the peer mailboxes when available, otherwise a second-stage kernel + NCCL.
+// Scaling options (device-resident recurrences): with norm_out != NULL the LAST of
+// the n values is a squared norm: it is stored to *norm_out and the other n - 1
+// values are multiplied by 1 / sqrt(|it|) before they are stored / used for coef;
+// with scale_sq != NULL every value is multiplied by 1 / sqrt(|*scale_sq|).
 int finish_reduction(const double *partial, int nblocks, int n, double *out, bool over_ranks,
-                     const double *T = nullptr, int k = 0, double *coef = nullptr);
+                     const double *T = nullptr, int k = 0, double *coef = nullptr,
+                     double *norm_out = nullptr, const double *scale_sq = nullptr);
 int setup_mailboxes();
 void release_mailboxes();
 

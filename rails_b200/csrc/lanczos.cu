@@ -53,14 +53,75 @@ __device__ __forceinline__ double2 ld2(const double *__restrict__ p, long long r
     return v;
 }
 
-template<bool FULL>
+// Fused update of the device-resident recurrence (rails_mv_lanczos_run): the
+// column being projected is first formed as
+//     w_i = raw - alpha (s w_{i-1}) - beta q_{i-2},   s = 1 / |w_{i-1}|, beta = |w_{i-1}|
+// (src/LyapunovSolver.hpp:411-413 and the `next /= beta` of :431 for the
+// PREVIOUS column, which is normalised in place in the same pass), and its
+// squared norm is accumulated as one more output.
+struct LanczosUpdate
+{
+    double *prev;            // w_{i-1}, un-normalised on entry, normalised on exit; NULL: no update
+    const double *prev2;     // q_{i-2} (normalised) or NULL
+    double alpha, s, beta;
+};
+
+template<bool FULL, bool UPD>
 __device__ __forceinline__ void md_tile(const Segs &S, double *__restrict__ q, double qscale,
                                         bool write_q, long long rows, long long base,
-                                        double *wacc, int lane)
+                                        double *wacc, int lane, const LanczosUpdate &up, int total)
 {
     // q tile: scaled on the fly (the pending `q /= beta` of the previous
     // step, :431) and written back once
     double2 qv[MD_RP];
+    if (UPD)
+    {
+        double nrm = 0.0;
+#pragma unroll
+        for (int v = 0; v < MD_RP; ++v)
+        {
+            const long long r = base + v * 512;
+            double2 x = make_double2(0.0, 0.0), w = make_double2(0.0, 0.0), p = make_double2(0.0, 0.0);
+            if (FULL)
+            {
+                x = *reinterpret_cast<const double2 *>(q + r);
+                w = *reinterpret_cast<const double2 *>(up.prev + r);
+                if (up.prev2) p = __ldg(reinterpret_cast<const double2 *>(up.prev2 + r));
+            }
+            else
+            {
+                if (r < rows) { x.x = q[r]; w.x = up.prev[r]; if (up.prev2) p.x = up.prev2[r]; }
+                if (r + 1 < rows) { x.y = q[r + 1]; w.y = up.prev[r + 1]; if (up.prev2) p.y = up.prev2[r + 1]; }
+            }
+            w.x = __dmul_rn(w.x, up.s);
+            w.y = __dmul_rn(w.y, up.s);
+            x.x = __dadd_rn(x.x, -__dmul_rn(up.alpha, w.x));
+            x.y = __dadd_rn(x.y, -__dmul_rn(up.alpha, w.y));
+            if (up.prev2)
+            {
+                x.x = __dadd_rn(x.x, -__dmul_rn(up.beta, p.x));
+                x.y = __dadd_rn(x.y, -__dmul_rn(up.beta, p.y));
+            }
+            if (FULL)
+            {
+                *reinterpret_cast<double2 *>(q + r) = x;
+                *reinterpret_cast<double2 *>(up.prev + r) = w;
+            }
+            else
+            {
+                if (r < rows) { q[r] = x.x; up.prev[r] = w.x; }
+                if (r + 1 < rows) { q[r + 1] = x.y; up.prev[r + 1] = w.y; }
+            }
+            qv[v] = x;
+            nrm = fma(x.x, x.x, nrm);
+            nrm = fma(x.y, x.y, nrm);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+            nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
+        if (lane == 0) wacc[total] += nrm;
+    }
+    else
 #pragma unroll
     for (int v = 0; v < MD_RP; ++v)
     {
@@ -158,10 +219,11 @@ multi_dot_kernel(Segs S, int total, double *__restrict__ q, double qscale, int w
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
     {
         const long long base = tile * MD_TILE + 2 * threadIdx.x;
+        const LanczosUpdate none = {nullptr, nullptr, 0.0, 0.0, 0.0};
         if ((tile + 1) * MD_TILE <= rows)
-            md_tile<true>(S, q, qscale, write_q != 0, rows, base, wacc, lane);
+            md_tile<true, false>(S, q, qscale, write_q != 0, rows, base, wacc, lane, none, total);
         else
-            md_tile<false>(S, q, qscale, write_q != 0, rows, base, wacc, lane);
+            md_tile<false, false>(S, q, qscale, write_q != 0, rows, base, wacc, lane, none, total);
     }
     __syncthreads();
     double *out = partial + (size_t)blockIdx.x * total;
@@ -173,6 +235,81 @@ multi_dot_kernel(Segs S, int total, double *__restrict__ q, double qscale, int w
             s += sacc[w * total + i];
         out[i] = s;
     }
+}
+
+// Step kernel A of the device-resident recurrence:
+//   partial[blockIdx.x][0 .. total)  = [X_0 X_1 ..]' w      (w NOT normalised)
+//   partial[blockIdx.x][total]       = |w|^2
+// where w = col (i = 0) or the fused update of LanczosUpdate with alpha and
+// |w_{i-1}|^2 read from device memory.
+__global__ void __launch_bounds__(MD_THREADS)
+lanczos_dot_kernel(Segs S, int total, double *__restrict__ col, double *prev, const double *prev2,
+                   const double *__restrict__ alpha_dev, const double *__restrict__ prev_sq_dev,
+                   long long rows, double *__restrict__ partial)
+{
+    extern __shared__ double sacc[];
+    const int nout = total + 1;
+    for (int i = threadIdx.x; i < nout * MD_WARPS; i += MD_THREADS)
+        sacc[i] = 0.0;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double *wacc = sacc + warp * nout;
+    LanczosUpdate up = {prev, prev2, 0.0, 0.0, 0.0};
+    if (prev)
+    {
+        const double nrm = sqrt(fabs(*prev_sq_dev));
+        up.alpha = *alpha_dev;
+        up.s = 1.0 / nrm;
+        up.beta = nrm;
+    }
+    const long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+    {
+        const long long base = tile * MD_TILE + 2 * threadIdx.x;
+        const bool full = (tile + 1) * MD_TILE <= rows;
+        if (prev)
+        {
+            if (full) md_tile<true, true>(S, col, 1.0, false, rows, base, wacc, lane, up, total);
+            else      md_tile<false, true>(S, col, 1.0, false, rows, base, wacc, lane, up, total);
+        }
+        else
+        {
+            // first column: plain projection; its squared norm from the q tile
+            if (full) md_tile<true, false>(S, col, 1.0, false, rows, base, wacc, lane, up, total);
+            else      md_tile<false, false>(S, col, 1.0, false, rows, base, wacc, lane, up, total);
+            double nrm = 0.0;
+#pragma unroll
+            for (int v = 0; v < MD_RP; ++v)
+            {
+                const long long r = base + v * 512;
+                if (r < rows) nrm = fma(col[r], col[r], nrm);
+                if (r + 1 < rows) nrm = fma(col[r + 1], col[r + 1], nrm);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
+            if (lane == 0) wacc[total] += nrm;
+        }
+    }
+    __syncthreads();
+    double *out = partial + (size_t)blockIdx.x * nout;
+    for (int i = threadIdx.x; i < nout; i += MD_THREADS)
+    {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < MD_WARPS; ++w)
+            s += sacc[w * nout + i];
+        out[i] = s;
+    }
+}
+
+// q = w / |w| for the last column of the recurrence
+__global__ void __launch_bounds__(256)
+normalize_kernel(double *__restrict__ w, const double *__restrict__ sq_dev, long long rows)
+{
+    const double s = 1.0 / sqrt(fabs(*sq_dev));
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < rows; i += (long long)gridDim.x * 256)
+        w[i] = __dmul_rn(w[i], s);
 }
 
 // out[i] = sum_b partial[b * n + i], one CTA per output, fixed order:
@@ -597,68 +734,65 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
     const bool reduce = dist && Q->flags == RAILS_MV_DISTRIBUTED && c.comm;
     *steps = 0;
 
-    // device scratch: g[total] | coef[total] | a[L] | b2[L + 1]   (b2[0] = |q_0|^2)
-    const size_t need = 2 * (size_t)std::max(total, 1) + 2 * (size_t)L + 1;
+    // device scratch: g[total + 1] | coef[total] | a[L] | b2[L + 1]   (b2[i] = |w_i|^2)
+    const int tot1 = std::max(total, 1) + 1;
+    const size_t need = 2 * (size_t)tot1 + 2 * (size_t)L + 1;
     rc = rails::ensure_small(need);
     if (rc) return rc;
-    double *g = c.d_small, *coef = g + std::max(total, 1), *a = coef + std::max(total, 1), *b2 = a + L;
+    double *g = c.d_small, *coef = g + tot1, *a = coef + tot1, *b2 = a + L;
     const double *dT = nullptr;
     if (k > 0)
     {
         rc = rails::upload_small(T, k, k, ldt, &dT);
         if (rc) return rc;
     }
+    RAILS_CUDA_TRY(cudaMemsetAsync(a, 0, (2 * (size_t)L + 1) * sizeof(double), c.stream));
 
-    if (rows == 0)
-        RAILS_CUDA_TRY(cudaMemsetAsync(c.d_small, 0, need * sizeof(double), c.stream));
     const long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
     const int nb_dot = (int)std::max<long long>(1, std::min<long long>(ntiles, (long long)c.sm_count * 4));
     const long long rows2 = (rows + 1) / 2;
     const int nb_gemv = (int)std::max<long long>(1, (rows2 + (long long)MG_THREADS * MG_RP - 1) / ((long long)MG_THREADS * MG_RP));
-    const int nb_upd = (int)std::max<long long>(1, std::min<long long>((rows / 2 + LU_THREADS - 1) / LU_THREADS,
-                                                                      (long long)c.sm_count * 8));
-    rc = rails::ensure_partial(std::max<size_t>((size_t)nb_dot * std::max(total, 1), std::max(nb_gemv, nb_upd)));
+    rc = rails::ensure_partial(std::max<size_t>((size_t)nb_dot * (total + 1), (size_t)nb_gemv));
     if (rc) return rc;
     static bool attr_set = false;
     if (!attr_set)
     {
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(multi_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            MD_MAXCOLS * MD_WARPS * (int)sizeof(double)));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (MD_MAXCOLS + 1) * MD_WARPS * (int)sizeof(double)));
         attr_set = true;
     }
     if (rows > 0)
     {
-        // |q_0|^2 -> b2[0]  (`Q.view(0) /= Q.norm()`, :375; applied by step 0's multi_dot)
-        const double *q0 = Q->data + (size_t)qc0 * Q->ld;
-        rc = rails::dot_device(q0, Q->ld, 1, q0, Q->ld, 1, rows, b2, 1, reduce);
-        if (rc) return rc;
+        // The Lanczos vectors are kept UN-normalised while the recurrence runs
+        // (w_i = |w_i| q_i): a step is two kernels and two exchanges,
+        //   A_i: w_i = raw_i - alpha_{i-1} q_{i-1} - beta_{i-2} q_{i-2} (fused update of the
+        //        previous step, which also normalises column i-1 in place),
+        //        [X_0 X_1 ..]' w_i and |w_i|^2           -> exchange -> g = ./|w_i|, coef
+        //   B_i: raw_{i+1} = sum_b X_b coef_b,  raw_{i+1}' w_i -> exchange -> alpha_i = ./|w_i|
+        // instead of three (dot, gemv, update) with three.  The update of the
+        // last step only feeds H(L, L-1), which the caller drops: it is skipped.
         for (int i = 0; i < L; ++i)
         {
-            double *q = Q->data + (size_t)(qc0 + i) * Q->ld;
-            double *next = q + Q->ld;
-            // g = [X_0 X_1 ..]' (q / |q|), q normalised in place
-            RAILS_LAUNCH(multi_dot_kernel, nb_dot, MD_THREADS, (size_t)std::max(total, 1) * MD_WARPS * sizeof(double),
-                         S, total, q, 1.0, 1, rows, c.d_partial, (const double *)(b2 + i));
-            if (total > 0)
-            {
-                // partials -> g, summed over the ranks, and coef = [T g_1; T g_0; g_rest]: one kernel
-                rc = rails::finish_reduction(c.d_partial, nb_dot, total, g, reduce, dT, k, coef);
-                if (rc) return rc;
-            }
-            // next = sum_b X_b coef_b ; a[i] = next' q
-            RAILS_LAUNCH(multi_gemv_kernel, nb_gemv, MG_THREADS, (size_t)std::max(total, 1) * sizeof(double),
-                         S, total, coef, next, q, rows, c.d_partial);
+            double *col = Q->data + (size_t)(qc0 + i) * Q->ld;
+            RAILS_LAUNCH(lanczos_dot_kernel, nb_dot, MD_THREADS, (size_t)(total + 1) * MD_WARPS * sizeof(double),
+                         S, total, col, i > 0 ? col - Q->ld : (double *)nullptr,
+                         i > 1 ? (const double *)(col - 2 * Q->ld) : (const double *)nullptr,
+                         (const double *)(a + std::max(i - 1, 0)), (const double *)(b2 + std::max(i - 1, 0)),
+                         rows, c.d_partial);
             RAILS_CHECK_LAUNCH();
-            rc = rails::finish_reduction(c.d_partial, nb_gemv, 1, a + i, reduce);
+            rc = rails::finish_reduction(c.d_partial, nb_dot, total + 1, g, reduce, dT, k, coef, b2 + i);
             if (rc) return rc;
-            // next -= a[i] q + beta_{i-1} q_prev ; b2[i + 1] = |next|^2
-            RAILS_LAUNCH(lanczos_update_kernel, nb_upd, LU_THREADS, 0, next, q,
-                         i > 0 ? (const double *)(q - Q->ld) : (const double *)nullptr, 0.0, 0.0, rows,
-                         c.d_partial, (const double *)(a + i), i > 0 ? (const double *)(b2 + i) : (const double *)nullptr);
+            RAILS_LAUNCH(multi_gemv_kernel, nb_gemv, MG_THREADS, (size_t)std::max(total, 1) * sizeof(double),
+                         S, total, coef, col + Q->ld, col, rows, c.d_partial);
             RAILS_CHECK_LAUNCH();
-            rc = rails::finish_reduction(c.d_partial, nb_upd, 1, b2 + i + 1, reduce);
+            rc = rails::finish_reduction(c.d_partial, nb_gemv, 1, a + i, reduce, nullptr, 0, nullptr, nullptr, b2 + i);
             if (rc) return rc;
         }
+        // columns 0 .. L-2 were normalised on the way; the last one here
+        double *last = Q->data + (size_t)(qc0 + L - 1) * Q->ld;
+        const int nbn = (int)std::max<long long>(1, std::min<long long>((rows + 255) / 256, (long long)c.sm_count * 8));
+        RAILS_LAUNCH(normalize_kernel, nbn, 256, 0, last, (const double *)(b2 + L - 1), rows);
+        RAILS_CHECK_LAUNCH();
     }
     // one read-back for the whole recurrence
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, a, (2 * (size_t)L + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));

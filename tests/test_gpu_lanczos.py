@@ -118,7 +118,8 @@ def test_lanczos_run_matches_the_recurrence(gpu, m, k, n, L):
     scale = max(abs(x) for x in al + be)
     for i in range(min(steps.value, 4)):
         assert abs(a_out[i] - al[i]) <= 1e-10 * scale, (i, a_out[i], al[i])
-        assert abs(b_out[i] - be[i]) <= 1e-10 * scale, (i, b_out[i], be[i])
+        if i < L - 1:          # H(L, L-1) is dropped by the caller and not computed
+            assert abs(b_out[i] - be[i]) <= 1e-10 * scale, (i, b_out[i], be[i])
     got = Qd.numpy(1, 3)
     assert np.max(np.abs(got[:, 0] - Q[:, 0])) < 1e-15
     assert np.max(np.abs(got[:, 1] - Q[:, 1])) < 1e-11

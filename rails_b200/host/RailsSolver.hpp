@@ -138,7 +138,7 @@ public:
           max_iter_(1000), tol_(1e-3), expand_size_(3), lanczos_iterations_(10),
           restart_size_(-1), reduced_size_(-1), restart_iterations_(20),
           restart_tolerance_(tol_ * 1e-3), minimize_solution_space_(true),
-          restart_from_solution_(false), use_mass_(false), verbose_(true)
+          restart_from_solution_(false), use_mass_(false), residual_method_(0), verbose_(true)
     {}
 
     virtual ~Solver() {}
@@ -156,6 +156,15 @@ public:
     int resid_lanczos(MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
                       DenseMatrix &H, MultiVector &eigenvectors, DenseMatrix &eigenvalues,
                       int max_iter);
+
+    // Exact eigenpairs of the residual through a tall-skinny QR of its factor
+    // ("Residual method" = 1; BASELINE.json north_star item (3)):
+    //     R = F S F',  F = [V, AV, B] (m x (2k+n)),  S = [[0 T 0]; [T 0 0]; [0 0 I]]
+    //     F = Q_F R_F  ->  eig(R_F S R_F') = Y Theta Y'  ->  eigenvectors Q_F Y
+    // No random start vector and no Lanczos breakdown: the result is the same
+    // to rounding on every backend and GPU count.
+    int resid_tsqr(MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
+                   MultiVector &eigenvectors, DenseMatrix &eigenvalues);
 
     // Restart basis from the dominant eigenvectors of T
     int compute_restart_vectors(DenseMatrix &X, DenseMatrix const &T, int num, double tol);
@@ -193,6 +202,7 @@ protected:
     bool minimize_solution_space_;
     bool restart_from_solution_;
     bool use_mass_;
+    int residual_method_;     // 0: the reference's Lanczos, 1: TSQR + small eigenproblem
     bool verbose_;
 
     Observer observer_;
@@ -264,6 +274,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::set_parameters(ParameterList &para
                                               restart_from_solution_);
     // extension (not a reference key): generalised equation with the stored M
     use_mass_ = lookup_parameter(params, "Use mass matrix", use_mass_);
+    // extension: 0 = Lanczos as the reference, 1 = TSQR of [V, AV, B] + small eigenproblem
+    residual_method_ = lookup_parameter(params, "Residual method", residual_method_);
 
     if (lanczos_iterations_ <= expand_size_)
     {

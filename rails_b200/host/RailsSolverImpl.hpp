@@ -253,7 +253,11 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         DenseMatrix ritz_values(L, 1);
         MultiVector ritz_vectors;
         // generalised residual AV T MV' + MV T AV' + B B' (matlab/RAILSsolver.m:391)
-        resid_lanczos(AV, use_mass_ ? MV : V, T, H, ritz_vectors, ritz_values, L);
+        bool have_ritz = false;
+        if (residual_method_ == 1 && B_.is_multivector() && 2 * V.N() + B_.multivector().N() <= n)
+            have_ritz = resid_tsqr(AV, use_mass_ ? MV : V, T, ritz_vectors, ritz_values) == 0;
+        if (!have_ritz)
+            resid_lanczos(AV, use_mass_ ? MV : V, T, H, ritz_vectors, ritz_values, L);
 
         const double res = ritz_values.norm_inf();
 
@@ -550,6 +554,75 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
     H.eigs(v, eigenvalues);
 
     eigenvectors = Q * v;
+    return 0;
+}
+
+// Non-zero eigenpairs of R = F S F' from a QR factorisation of the tall-skinny
+// factor (see the declaration).  The QR is the backend's own column-wise CGS2
+// (orthogonalize(), src/StlWrapper.cpp:305-321) applied to a copy of F, R_F is
+// recovered as Q_F' F; everything else is (2k+n) x (2k+n) host work.  Returns
+// non-zero (and leaves the outputs alone) when F is numerically rank deficient,
+// in which case the caller falls back on the Lanczos estimate.
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::resid_tsqr(
+    MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
+    MultiVector &eigenvectors, DenseMatrix &eigenvalues)
+{
+    Section s(sections_, "resid_tsqr");
+    MultiVector const &B = B_.multivector();
+    const int k = V.N(), nb = B.N(), c = 2 * k + nb;
+
+    // exact-size views on the right: assigning into a view copies the source's
+    // whole allocation when the row capacities agree (src/StlWrapper.cpp:82-83),
+    // and V / AV carry spare columns
+    MultiVector F(V, c);
+    F.view(0, k - 1) = V.view(0, k - 1);
+    F.view(k, 2 * k - 1) = AV.view(0, k - 1);
+    F.view(2 * k, c - 1) = B.view(0, nb - 1);
+
+    MultiVector Q = F.copy();
+    Q.orthogonalize();
+    DenseMatrix R = Q.dot(F);                  // c x c, upper triangular up to rounding
+
+    double rmax = 0.0, rmin = 1e300;
+    for (int i = 0; i < c; i++)
+    {
+        const double d = std::abs(R(i, i));
+        if (!(d == d)) return 1;               // NaN: a column vanished during the QR
+        rmax = std::max(rmax, d);
+        rmin = std::min(rmin, d);
+    }
+    if (!(rmin > 1e-13 * rmax))
+        return 1;
+
+    // E = R_F S R_F' with S = [[0 T 0]; [T 0 0]; [0 0 I]]
+    DenseMatrix S(c, c);
+    S = 0.0;
+    for (int j = 0; j < k; j++)
+        for (int i = 0; i < k; i++)
+        {
+            S(i, k + j) = T(i, j);
+            S(k + i, j) = T(i, j);
+        }
+    for (int i = 0; i < nb; i++)
+        S(2 * k + i, 2 * k + i) = 1.0;
+    DenseMatrix E = R * (S * R.transpose());
+    for (int j = 0; j < c; j++)
+        for (int i = 0; i < j; i++)
+        {
+            const double v = 0.5 * (E(i, j) + E(j, i));
+            E(i, j) = v;
+            E(j, i) = v;
+        }
+
+    DenseMatrix Y(c, c), theta(c, 1);
+    E.eigs(Y, theta);
+    for (int i = 0; i < c; i++)
+        if (!(theta(i, 0) == theta(i, 0)))
+            return 1;
+
+    eigenvalues = theta;
+    eigenvectors = Q * Y;
     return 0;
 }
 

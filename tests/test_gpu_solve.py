@@ -165,6 +165,45 @@ def test_generalized_solve_against_dense_solution(gpu):
     assert gpu.solve(rp, ci, v, 2, P, B=B)["ret"] == 102
 
 
+@pytest.mark.parametrize("kind,g,dim,n_b,stop,mass", [("laplacian", 12, 2, 1, 5, False), ("convdiff", 7, 3, 3, 6, False),
+                                                      ("laplacian", 10, 2, 2, 6, True)])
+def test_tsqr_residual_method_is_exact(gpu, kind, g, dim, n_b, stop, mass):
+    """a17 ("Residual method" = 1): eigenpairs of the residual from a tall-skinny
+    QR of [V, AV, B] (CGS2 kernels) + a small eigenproblem, validated against the
+    dense residual (neither reference implementation has it)."""
+    rp, ci, v = problems.build(kind, g, dim)
+    m = rp.size - 1
+    B = np.asfortranarray(np.random.RandomState(3).uniform(-1, 1, (m, n_b)))
+    M = problems.lumped_mass(m) if mass else None
+    P = {"Tolerance": 1e-14, "Expand size": 1, "Lanczos iterations": 8, "Maximum iterations": stop,
+         "Residual method": 1, "Minimize solution space": 0}
+    if mass:
+        P["Use mass matrix"] = 1
+    d = gpu.solve(rp, ci, v, n_b, P, B=B, v_cap_cols=200, M=M)
+    assert d["ret"] == -1 and d["iterations"] == stop
+    A = harness.csr_to_dense(rp, ci, v, m)
+    D = np.diag(M[2]) if mass else np.eye(m)
+    X = d["V"] @ d["T"] @ d["V"].T
+    R = A @ X @ D + D @ X @ A.T + B @ B.T
+    exact = np.max(np.abs(np.linalg.eigvalsh(0.5 * (R + R.T))))
+    assert abs(d["abs"][-1] - exact) <= 1e-9 * exact, (d["abs"][-1], exact)
+
+
+def test_tsqr_residual_method_converges_like_lanczos(gpu):
+    rp, ci, v = problems.laplacian(40, 2)
+    P = {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 10}
+    lan = gpu.solve(rp, ci, v, 1, P, v_cap_cols=300)
+    P1 = dict(P); P1["Residual method"] = 1
+    a = gpu.solve(rp, ci, v, 1, P1, v_cap_cols=300)
+    b = gpu.solve(rp, ci, v, 1, P1, v_cap_cols=300)
+    assert a["ret"] == 0 and lan["ret"] == 0
+    assert a["iterations"] <= 1.2 * lan["iterations"] + 2
+    # only the random start of V differs between two runs of the same process:
+    # same seed -> the same bits (no Lanczos start vector, no breakdown)
+    assert a["iterations"] == b["iterations"] and np.array_equal(a["rel"], b["rel"])
+    assert harness.lowrank_rel_diff(a["V"], a["T"], lan["V"], lan["T"]) < 300 * P["Tolerance"]
+
+
 def test_explicit_residual_with_given_B(gpu):
     """Reference acceptance test (test/TestHelpers.hpp:4-11): every entry of
     A X + X A' + B B' below 1e-3 after a converged solve."""

@@ -40,3 +40,33 @@ def test_parameter_rejection_matches():
     r = harness.ref_stl_solve(rp, ci, v, 1, P)
     p = harness.ref_stl_solve(rp, ci, v, 1, P, entry="b200loop_stl_solve")
     assert r["ret"] == p["ret"] == 101
+
+
+@pytest.mark.parametrize("kind,g,dim,n_b,stop", [("laplacian", 10, 2, 1, 4), ("laplacian", 10, 2, 2, 7),
+                                                 ("convdiff", 6, 3, 3, 5)])
+def test_tsqr_residual_estimate_is_the_exact_residual_norm(kind, g, dim, n_b, stop):
+    """a17 ("Residual method" = 1): the residual's eigenpairs from a tall-skinny
+    QR of [V, AV, B] and a small eigenproblem.  Neither reference implementation
+    has this, so it is validated against the dense residual: after
+    `stop` iterations the reported estimate must be the spectral norm of
+    A X + X A' + B B' with X = V T V' (product loop over the reference's own
+    StlWrapper, CPU)."""
+    rp, ci, v = problems.build(kind, g, dim)
+    m = rp.size - 1
+    B = np.asfortranarray(np.random.RandomState(3).uniform(-1, 1, (m, n_b)))
+    P = {"Tolerance": 1e-14, "Expand size": 1, "Lanczos iterations": 8, "Maximum iterations": stop,
+         "Residual method": 1, "Minimize solution space": 0}
+    p = harness.ref_stl_solve(rp, ci, v, n_b, P, B=B, v_cap_cols=200, entry="b200loop_stl_solve")
+    assert p["ret"] == -1 and p["iterations"] == stop
+    A = harness.csr_to_dense(rp, ci, v, m)
+    X = p["V"] @ p["T"] @ p["V"].T
+    R = A @ X + X @ A.T + B @ B.T
+    exact = np.max(np.abs(np.linalg.eigvalsh(0.5 * (R + R.T))))
+    assert abs(p["abs"][-1] - exact) <= 1e-9 * exact, (p["abs"][-1], exact)
+    # the estimates decrease towards convergence and the method converges
+    P2 = dict(P); P2["Tolerance"] = 1e-8; P2["Maximum iterations"] = 200
+    q = harness.ref_stl_solve(rp, ci, v, n_b, P2, B=B, v_cap_cols=200, entry="b200loop_stl_solve")
+    assert q["ret"] == 0
+    X = q["V"] @ q["T"] @ q["V"].T
+    R = A @ X + X @ A.T + B @ B.T
+    assert np.max(np.abs(np.linalg.eigvalsh(0.5 * (R + R.T)))) <= 1e-8 * np.linalg.norm(B.T @ B, 2) * 1.01

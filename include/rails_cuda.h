@@ -60,6 +60,10 @@ int rails_cuda_finalize(void);
 int rails_cuda_is_initialized(void);
 int rails_cuda_sync(void);
 const char *rails_cuda_last_error(void);
+/* number of failed calls so far: lets a caller that drives the wrappers in the
+ * reference's "print and carry on" style (src/StlWrapper.cpp:173-179) stop a
+ * solve cleanly after, e.g., an out-of-memory allocation */
+long long rails_cuda_error_count(void);
 /* number of this library's kernels launched since init (bench.py's
  * gpu_launches) */
 long long rails_cuda_kernel_launches(void);

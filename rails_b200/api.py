@@ -64,6 +64,7 @@ CUDA_SYMBOLS = [
     ("rails_cuda_is_initialized", I, []),
     ("rails_cuda_sync", I, []),
     ("rails_cuda_last_error", ctypes.c_char_p, []),
+    ("rails_cuda_error_count", LL, []),
     ("rails_cuda_kernel_launches", LL, []),
     ("rails_cuda_bytes_in_use", LL, []),
     ("rails_cuda_event_record", I, [I]),

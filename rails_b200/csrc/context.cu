@@ -25,6 +25,7 @@ int fail(int code, const char *fmt, ...)
     vsnprintf(buf, sizeof(buf), fmt, ap);
     va_end(ap);
     ctx().last_error = buf;
+    ctx().errors.fetch_add(1);
     fprintf(stderr, "rails_cuda error: %s\n", buf);
     return code;
 }
@@ -283,6 +284,7 @@ extern "C" int rails_cuda_sync(void)
 }
 
 extern "C" const char *rails_cuda_last_error(void) { return ctx().last_error.c_str(); }
+extern "C" long long rails_cuda_error_count(void) { return ctx().errors.load(); }
 extern "C" long long rails_cuda_kernel_launches(void) { return ctx().launches.load(); }
 extern "C" long long rails_cuda_bytes_in_use(void) { return ctx().bytes_in_use.load(); }
 
@@ -391,6 +393,18 @@ extern "C" int rails_mv_alloc(long long rows, int cols, int flags, rails_mv_t *o
     mv->flags = flags;
     mv->bytes = (size_t)mv->ld * (size_t)(cols > 0 ? cols : 1) * sizeof(double);
     cudaError_t e = cudaMallocAsync(&mv->data, mv->bytes, ctx().stream);
+    if (e == cudaErrorMemoryAllocation)
+    {
+        // The pool keeps every freed block (release threshold = max), and blocks
+        // freed by a capacity growth (V, AV: +100 columns at a time) are too small
+        // for the next, larger request: give the cached memory back and retry.
+        cudaGetLastError();
+        cudaStreamSynchronize(ctx().stream);
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, ctx().device) == cudaSuccess)
+            cudaMemPoolTrimTo(pool, 0);
+        e = cudaMallocAsync(&mv->data, mv->bytes, ctx().stream);
+    }
     if (e != cudaSuccess)
     {
         delete mv;

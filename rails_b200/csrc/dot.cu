@@ -364,12 +364,21 @@ extern "C" int rails_mv_dot_dev(rails_mv_t X, int xc0, int a, rails_mv_t Y, int 
     return RAILS_OK;
 }
 
-// Column-wise CGS2 (StlWrapper::orthogonalize, src/StlWrapper.cpp:305-321):
+// CGS2 (StlWrapper::orthogonalize, src/StlWrapper.cpp:305-321):
 //   for i in [first, last]:  v = V(:, i);  v /= |v|;
 //       twice:  v -= V(:, 0:i-1) * (V(:, 0:i-1)' v);      v /= |v|
 // Every scalar (the squared norms, the k x 1 coefficient vectors) stays in
-// device memory between kernels; with a communicator the sums are all-reduced
-// on the same stream.  Nothing returns to the host.
+// device memory between kernels; with a communicator the sums are reduced over
+// the ranks on the same stream.  Nothing returns to the host.
+//
+// Several new columns are processed in panels of 8: a panel is first projected,
+// twice, against ALL columns before it as one block (two k x 8 products instead
+// of 8 x two k x 1: V is streamed twice per panel, not twice per column), then
+// its columns are orthogonalised among themselves column by column.  In exact
+// arithmetic this is the column-wise recurrence; in floating point it differs
+// from it by rounding only (after the two block passes the panel is orthogonal
+// to the old columns to working precision).  RAILS_BLOCK_CGS2=0 forces the
+// column-by-column sequence.
 extern "C" int rails_mv_orthogonalize(rails_mv_t V, int col0, int first, int last)
 {
     RAILS_REQUIRE_READY();
@@ -380,27 +389,95 @@ extern "C" int rails_mv_orthogonalize(rails_mv_t V, int col0, int first, int las
     if (rc) return rc;
     const bool dist = V->flags == RAILS_MV_DISTRIBUTED;
     double *base = V->data + (size_t)col0 * V->ld;
-    for (int i = first; i <= last; ++i)
+    static int block_mode = -1;
+    if (block_mode < 0)
     {
-        double *v = base + (size_t)i * V->ld;
-        rc = rails::dot_device(v, V->ld, 1, v, V->ld, 1, V->rows, c.d_small, 1, dist);
-        if (rc) return rc;
-        rc = rails::scal_inv_norm_device(v, V->ld, V->rows, c.d_small);
-        if (rc) return rc;
-        if (i > 0)
+        const char *e = getenv("RAILS_BLOCK_CGS2");
+        block_mode = (e && e[0] == '0') ? 0 : 1;
+    }
+    const int PANEL = 8;
+    auto normalise = [&](double *v) -> int {
+        int r = rails::dot_device(v, V->ld, 1, v, V->ld, 1, V->rows, c.d_small, 1, dist);
+        if (r) return r;
+        return rails::scal_inv_norm_device(v, V->ld, V->rows, c.d_small);
+    };
+    int p0 = first;
+    while (p0 <= last)
+    {
+        const int p1 = (block_mode && last > first) ? std::min(last, p0 + PANEL - 1) : p0;
+        const int e = p1 - p0 + 1;
+        const int old = (e > 1) ? p0 : 0;      // columns handled by the block passes
+        double *W = base + (size_t)p0 * V->ld;
+        if (e > 1)
         {
-            for (int pass = 0; pass < 2; ++pass)
+            rc = rails::ensure_small((size_t)std::max(p0, 1) * e + 2);
+            if (rc) return rc;
+            for (int i = 0; i < e; ++i)
             {
-                rc = rails::dot_device(base, V->ld, i, v, V->ld, 1, V->rows, c.d_small, i, dist);
+                rc = normalise(W + (size_t)i * V->ld);
                 if (rc) return rc;
-                rc = rails::gemm_device(base, V->ld, i, c.d_small, i, 1, -1.0, 1.0, v, V->ld, V->rows);
+            }
+            if (p0 > 0)
+                for (int pass = 0; pass < 2; ++pass)
+                {
+                    rc = rails::dot_device(base, V->ld, p0, W, V->ld, e, V->rows, c.d_small, p0, dist);
+                    if (rc) return rc;
+                    rc = rails::gemm_device(base, V->ld, p0, c.d_small, p0, e, -1.0, 1.0, W, V->ld, V->rows);
+                    if (rc) return rc;
+                }
+        }
+        for (int i = p0; i <= p1; ++i)
+        {
+            double *v = base + (size_t)i * V->ld;
+            if (e == 1)
+            {
+                rc = normalise(v);
+                if (rc) return rc;
+            }
+            const int against = i - old;        // columns [old, i)
+            if (against > 0)
+            {
+                const double *Vo = base + (size_t)old * V->ld;
+                for (int pass = 0; pass < 2; ++pass)
+                {
+                    rc = rails::dot_device(Vo, V->ld, against, v, V->ld, 1, V->rows, c.d_small, against, dist);
+                    if (rc) return rc;
+                    rc = rails::gemm_device(Vo, V->ld, against, c.d_small, against, 1, -1.0, 1.0, v, V->ld, V->rows);
+                    if (rc) return rc;
+                }
+            }
+            rc = normalise(v);
+            if (rc) return rc;
+        }
+        if (e > 1 && p0 > 0)
+        {
+            // A column that (nearly) lies in the span of the columns before it in
+            // its own panel -- two Ritz vectors that are copies of one another --
+            // collapses to rounding noise in the loop above, and normalising noise
+            // brings back O(1) components along the OLD columns.  The column-wise
+            // recurrence is immune (its second pass runs against all columns); here
+            // one more block pass against the old columns restores the same
+            // guarantee, followed by a re-normalisation and one intra-panel pass
+            // (which only see rounding-size corrections for healthy columns).
+            rc = rails::dot_device(base, V->ld, p0, W, V->ld, e, V->rows, c.d_small, p0, dist);
+            if (rc) return rc;
+            rc = rails::gemm_device(base, V->ld, p0, c.d_small, p0, e, -1.0, 1.0, W, V->ld, V->rows);
+            if (rc) return rc;
+            for (int i = p0; i <= p1; ++i)
+            {
+                double *v = base + (size_t)i * V->ld;
+                if (i > p0)
+                {
+                    rc = rails::dot_device(W, V->ld, i - p0, v, V->ld, 1, V->rows, c.d_small, i - p0, dist);
+                    if (rc) return rc;
+                    rc = rails::gemm_device(W, V->ld, i - p0, c.d_small, i - p0, 1, -1.0, 1.0, v, V->ld, V->rows);
+                    if (rc) return rc;
+                }
+                rc = normalise(v);
                 if (rc) return rc;
             }
         }
-        rc = rails::dot_device(v, V->ld, 1, v, V->ld, 1, V->rows, c.d_small, 1, dist);
-        if (rc) return rc;
-        rc = rails::scal_inv_norm_device(v, V->ld, V->rows, c.d_small);
-        if (rc) return rc;
+        p0 = p1 + 1;
     }
     return RAILS_OK;
 }

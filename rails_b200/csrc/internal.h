@@ -103,6 +103,7 @@ struct Context
     unsigned long long mb_seq = 0;           // exchanges issued so far (same on every rank)
     int *d_mb_error = nullptr;               // set by a kernel whose wait timed out
     std::atomic<long long> launches{0};
+    std::atomic<long long> errors{0};        // calls that failed since the library was loaded
     std::atomic<long long> bytes_in_use{0};
     std::vector<cudaEvent_t> events;
     std::string last_error;

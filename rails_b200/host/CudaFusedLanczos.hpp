@@ -30,6 +30,12 @@ namespace RAILS
 namespace b200
 {
 
+template<>
+struct BackendHealth<CudaMultiVectorWrapper>
+{
+    static long long errors() { return rails_cuda_error_count(); }
+};
+
 // The projection dots with one host round trip (rails_mv_dot_batch).
 template<>
 struct BatchedDots<CudaMultiVectorWrapper, HostDenseMatrix>

@@ -116,6 +116,16 @@ struct BatchedDots
     }
 };
 
+// Customisation point: failed backend calls so far.  The wrappers follow the
+// reference's style (print to std::cerr, return an unfilled result); a backend
+// that can fail at run time (device out of memory) reports it here and the loop
+// stops with return code 2 instead of iterating on garbage.
+template<class MultiVector>
+struct BackendHealth
+{
+    static long long errors() { return 0; }
+};
+
 struct IterationRecord
 {
     int iteration;        // 1-based

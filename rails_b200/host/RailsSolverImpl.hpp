@@ -236,9 +236,16 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
     bool converged_before = false;
     int last_restart = 0;
     const double r0 = B_.norm();
+    const long long errors_at_start = BackendHealth<MultiVector>::errors();
 
     for (int iter = 0; iter < max_iter_; iter++)
     {
+        if (BackendHealth<MultiVector>::errors() != errors_at_start)
+        {
+            std::cerr << "The backend reported a failure; the solve is stopped after "
+                      << iter << " iterations" << std::endl;
+            return 2;
+        }
         const int cols_before = V.N();
         if (W.N())
             project(V, W, AV, BV, MV, VAV, VBV, VMV, iter == 0, max_size);

@@ -110,8 +110,11 @@ CONFIGS = {
     # the same problem as the C++ reference solves it (M never read)
     "C3I": ("laplacian", 256, 3, 1, {"Tolerance": 1e-4, "Expand size": 1,
                                      "Lanczos iterations": 10}),
+    # 16 new columns per iteration: the space is capped so that V and AV (134 MB
+    # per column) plus the restart temporaries stay inside one GPU's 180 GB
     "C4": ("convdiff", 256, 3, 16, {"Tolerance": 1e-4, "Expand size": 16,
-                                    "Lanczos iterations": 40}),
+                                    "Lanczos iterations": 40, "Restart size": 192,
+                                    "Reduced size": 96}),
     "C5": ("laplacian", 512, 3, 1, {"Tolerance": 1e-4, "Expand size": 1,
                                     "Lanczos iterations": 10}),
 }

@@ -309,6 +309,27 @@ def test_cgs2_vs_oracle(gpu, m, k, first):
     assert np.array_equal(Q[:, :first], X[:, :first])
 
 
+@pytest.mark.parametrize("first,dups", [(20, [(22, 21)]), (9, [(10, 9), (12, 9)]), (0, [(3, 1)])])
+def test_cgs2_with_duplicated_new_columns(gpu, first, dups):
+    """Two of the new columns are copies of one another (what the expansion gets
+    when two Ritz vectors are ghosts of the same eigenvector): the second one
+    collapses to rounding noise.  Whatever direction it ends up with, the result
+    must be orthonormal, and the old columns untouched."""
+    m, k = 5000, first + 6
+    rs = np.random.RandomState(first + 1)
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, k)))
+    if first:
+        X[:, :first] = np.linalg.qr(X[:, :first])[0]
+    for dst, src in dups:
+        X[:, dst] = X[:, src] * 1.5
+    Xd = gpu.MultiVector.from_numpy(X)
+    gpu.check(gpu.cuda().rails_mv_orthogonalize(Xd.h, 0, first, k - 1), "orthogonalize")
+    Q = Xd.numpy()
+    assert np.all(np.isfinite(Q))
+    assert np.max(np.abs(Q.T @ Q - np.eye(k))) < 1e-9
+    assert np.array_equal(Q[:, :first], X[:, :first])
+
+
 def test_linearity_at_full_size(gpu):
     """Size-independent properties at the C3 row count (m = 256^3), where the
     oracle is too slow to be the checker: A(x + 2y) = Ax + 2Ay on the 3-D

@@ -27,8 +27,9 @@ entry point rails_host_solve_m with HOST buffers -- the CSR arrays of A (and M)
 and B are uploaded, V and T downloaded, inside the timed wall-clock region;
 value = iterations to tolerance / that time (also reported as
 time_to_tolerance_s).
-`roofline`: the dominant kernel (first kernel of the fused residual-Lanczos
-step, [V AV B]'q) timed alone with CUDA events at the workload's row count.
+`roofline`: the dominant kernel (first kernel of a step of the device-resident
+residual-Lanczos chain: fused update + [V AV B]'w) timed alone with CUDA events
+at the workload's row count.
 `cpu_baseline` / `--impl reference`: the CPU oracle (CSR + OpenMP restatement
 of the reference loop; the reference's own sparse path needs Trilinos, which
 is not installable here) on the same inputs with all host threads.
@@ -219,6 +220,14 @@ def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
     ms = timed(lambda: api.check(lib.rails_mv_lanczos_update(V.h, k, 1e-3, q.h, 0, 1e-3, q.h, 1,
                                                              ctypes.byref(al)), "update"))
     rec("lanczos_update", ms, 32.0 * m, 2)
+    # first kernel of a step of the device-resident chain: fused update + projection
+    # (reads raw, prev, prev2 and the 2h+1 block columns, writes w and the normalised prev)
+    g1 = np.zeros(2 * h + 2)
+    ms = timed(lambda: api.check(lib.rails_mv_lanczos_project(3, hs, c0, nn, V.h, k, k + 1, -1, 1e-3,
+                                                              api.dptr(g1)), "project"))
+    # + 8m: the squared norm of `prev` is recomputed by this entry point (in the
+    # chain it is already on the device)
+    rec("lanczos_project", ms, 8.0 * m * (2 * h + 1 + 5), 4)
     for o in out.values():
         o["k"] = k
     V.free(); q.free(); small.free()
@@ -409,15 +418,16 @@ def run_b200(args):
     if kernels:
         # the dominant kernel of an outer iteration: first kernel of the fused
         # residual-Lanczos step, g = [V AV B]' q (about half of all bytes moved)
-        dk = kernels["multi_dot_scale_q"]
+        dk = kernels["lanczos_project"]
         traffic = None
         try:
-            traffic = _json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("multi_dot")
+            traffic = _json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("lanczos_dot")
         except Exception:
             pass
         roofline = {"bound": "hbm",
-                    "kernel": "multi_dot_kernel ([V AV B]'q with q rescaled in place, %d columns, "
-                              "m=%d rows)" % (2 * (dk["k"] // 2) + 1, rows),
+                    "kernel": "lanczos_dot_kernel (fused Lanczos update + [V AV B]'w, %d columns, "
+                              "m=%d rows; timed through rails_mv_lanczos_project)"
+                              % (2 * (dk["k"] // 2) + 1, rows),
                     "achieved": dk["gbs"], "peak": peak, "unit": "GB/s", "frac": dk["gbs"] / peak,
                     "traffic": traffic, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": dk["bytes"], "ms_per_launch": dk["ms"]}

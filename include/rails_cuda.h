@@ -181,6 +181,15 @@ int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc0, const in
                          const double *T, int ldt, rails_mv_t Q, int qc0, int L,
                          double *alpha, double *beta, int *steps);
 
+/* First kernel of a step of that chain on its own (unit tests, roofline timing):
+ * with prev_col >= 0, Q[:, col] -= alpha * q_prev + |Q[:, prev_col]| * Q[:, prev2_col]
+ * (q_prev = Q[:, prev_col] normalised, written back; prev2_col < 0: no last term),
+ * i.e. the update of :411-413 and the `/= beta` of :431 fused into the
+ * projection; then out[0..total) = [X_0 X_1 ..]' Q[:, col], out[total] = |Q[:, col]|^2. */
+int rails_mv_lanczos_project(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                             rails_mv_t Q, int col, int prev_col, int prev2_col,
+                             double alpha, double *out);
+
 /* ---- Gram-Schmidt: column-wise CGS2 of columns [first, last] against all
  *      earlier columns (StlWrapper::orthogonalize :305-321), executed as one
  *      device-side chain with no host round trip. ------------------------ */

@@ -699,6 +699,66 @@ extern "C" int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, ra
     return RAILS_OK;
 }
 
+// Kernel A of the device-resident recurrence on its own (unit tests, bench.py's
+// roofline leg): with prev_col >= 0 column `col` of Q is first replaced by
+//     w = Q[:, col] - alpha * (Q[:, prev_col] / |Q[:, prev_col]|) - |Q[:, prev_col]| * Q[:, prev2_col]
+// (prev2_col < 0: no third term) and Q[:, prev_col] is normalised in place; then
+// out[0 .. total) = [X_0 X_1 ..]' w and out[total] = |w|^2 (summed over ranks).
+extern "C" int rails_mv_lanczos_project(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                                        rails_mv_t Q, int col, int prev_col, int prev2_col,
+                                        double alpha, double *out)
+{
+    RAILS_REQUIRE_READY();
+    if (!Q || !out || col < 0 || col >= Q->cols || prev_col >= Q->cols || prev2_col >= Q->cols ||
+        (prev_col < 0 && prev2_col >= 0) || prev_col == col || prev2_col == col)
+        return rails::fail(RAILS_ERR_ARG, "lanczos_project: bad columns");
+    Segs S;
+    int total = 0;
+    bool dist = false;
+    int rc = collect_segs(nblk, X, xc0, xn, Q->rows, &S, &total, &dist, "lanczos_project");
+    if (rc) return rc;
+    if (total > MD_MAXCOLS)
+        return rails::fail(RAILS_ERR_ARG, "lanczos_project: %d columns, at most %d", total, MD_MAXCOLS);
+    rails::Context &c = ctx();
+    const long long rows = Q->rows;
+    const bool reduce = dist && Q->flags == RAILS_MV_DISTRIBUTED && c.comm;
+    rc = rails::ensure_small((size_t)total + 4);
+    if (rc) return rc;
+    double *g = c.d_small, *sc = g + total + 1;        // sc[0] = alpha, sc[1] = |prev|^2
+    double *colp = Q->data + (size_t)col * Q->ld;
+    double *prev = prev_col >= 0 ? Q->data + (size_t)prev_col * Q->ld : nullptr;
+    const double *prev2 = prev2_col >= 0 ? Q->data + (size_t)prev2_col * Q->ld : nullptr;
+    if (prev)
+    {
+        const double *ap = nullptr;
+        rc = rails::upload_small(&alpha, 1, 1, 1, &ap);
+        if (rc) return rc;
+        RAILS_CUDA_TRY(cudaMemcpyAsync(sc, ap, sizeof(double), cudaMemcpyDeviceToDevice, c.stream));
+        rc = rails::dot_device(prev, Q->ld, 1, prev, Q->ld, 1, rows, sc + 1, 1, reduce);
+        if (rc) return rc;
+    }
+    const long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
+    const int nb = (int)std::max<long long>(1, std::min<long long>(ntiles, (long long)c.sm_count * 4));
+    rc = rails::ensure_partial((size_t)nb * (total + 1));
+    if (rc) return rc;
+    static bool attr_set = false;
+    if (!attr_set)
+    {
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (MD_MAXCOLS + 1) * MD_WARPS * (int)sizeof(double)));
+        attr_set = true;
+    }
+    RAILS_LAUNCH(lanczos_dot_kernel, nb, MD_THREADS, (size_t)(total + 1) * MD_WARPS * sizeof(double), S, total,
+                 colp, prev, prev2, (const double *)sc, (const double *)(sc + 1), rows, c.d_partial);
+    RAILS_CHECK_LAUNCH();
+    rc = rails::finish_reduction(c.d_partial, nb, total + 1, g, reduce);
+    if (rc) return rc;
+    RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, g, (size_t)(total + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    memcpy(out, c.h_small, (size_t)(total + 1) * sizeof(double));
+    return RAILS_OK;
+}
+
 // The whole L-step recurrence of Solver::resid_lanczos
 // (src/LyapunovSolver.hpp:375-434) as ONE asynchronous chain on the library
 // stream: no value returns to the host until the last step has been enqueued.

@@ -131,6 +131,49 @@ def test_lanczos_run_matches_the_recurrence(gpu, m, k, n, L):
     assert abs(top(a_out[:n_ok], b_out[:n_ok]) - top(np.array(al), np.array(be))) <= 1e-8 * scale
 
 
+@pytest.mark.parametrize("m", [1, 3, 2047, 2048, 2049, 100003])
+def test_lanczos_project_fused_update(gpu, m):
+    """Kernel A of the chain: the update `next -= alpha q; next -= beta q_prev`
+    (:411-413) and the pending `q /= beta` (:431) fused into the projection."""
+    lib = gpu.cuda()
+    rs = np.random.RandomState(m)
+    ks = (3, 3, 2)
+    mats = [np.asfortranarray(rs.uniform(-1, 1, (m, k))) for k in ks]
+    F = np.hstack(mats)
+    Q0 = np.asfortranarray(rs.uniform(-1, 1, (m, 3)))
+    Q0[:, 0] /= np.linalg.norm(Q0[:, 0])                 # q_{i-2}: already normalised
+    mvs, hs, c0, nn = _blocks(gpu, mats)
+    tot = F.shape[1]
+    # no update: plain projection + squared norm
+    Q = gpu.MultiVector.from_numpy(Q0)
+    out = np.zeros(tot + 1)
+    gpu.check(lib.rails_mv_lanczos_project(3, hs, c0, nn, Q.h, 2, -1, -1, 0.0, gpu.dptr(out)), "project")
+    assert np.array_equal(Q.numpy(), Q0)
+    assert np.all(np.abs(out[:tot] - F.T @ Q0[:, 2]) <= 1e-13 * (np.abs(F).T @ np.abs(Q0[:, 2]) + 1))
+    assert abs(out[tot] - Q0[:, 2] @ Q0[:, 2]) <= 1e-13 * out[tot]
+    # fused update against columns 1 (un-normalised) and 0
+    alpha = 0.37
+    for third in (False, True):
+        Q = gpu.MultiVector.from_numpy(Q0)
+        gpu.check(lib.rails_mv_lanczos_project(3, hs, c0, nn, Q.h, 2, 1, 0 if third else -1, alpha,
+                                               gpu.dptr(out)), "project")
+        got = Q.numpy()
+        nrm = np.sqrt(abs(got[:, 1] @ got[:, 1])) if False else None
+        # |prev| as the device computed it is not observable bit for bit; recover the
+        # scale from the normalised column it wrote back
+        beta = np.linalg.norm(Q0[:, 1])
+        q1 = got[:, 1]
+        assert abs(np.linalg.norm(q1) - 1.0) < 1e-14
+        assert np.max(np.abs(q1 - Q0[:, 1] / beta)) <= 4e-16 * np.max(np.abs(q1)) + 1e-300
+        w = Q0[:, 2] - alpha * q1
+        if third:
+            w = w - beta * Q0[:, 0]
+        assert np.max(np.abs(got[:, 2] - w)) <= 1e-15 * (np.abs(Q0[:, 2]) + abs(alpha) + beta).max()
+        assert np.array_equal(got[:, 0], Q0[:, 0])
+        assert np.all(np.abs(out[:tot] - F.T @ got[:, 2]) <= 1e-13 * (np.abs(F).T @ np.abs(got[:, 2]) + 1))
+        assert abs(out[tot] - got[:, 2] @ got[:, 2]) <= 1e-13 * out[tot]
+
+
 def test_block_errors(gpu):
     lib = gpu.cuda()
     A = gpu.MultiVector(10, 3)

@@ -181,6 +181,12 @@ int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc0, const in
                          const double *T, int ldt, rails_mv_t Q, int qc0, int L,
                          double *alpha, double *beta, int *steps);
 
+/* Optional head start: the first projection of the chain does not depend on T, so
+ * it can be enqueued before the host solves the projected problem
+ * (src/LyapunovSolver.hpp:209); the next rails_mv_lanczos_run with the same Q,
+ * qc0 and blocks continues from it. */
+int rails_mv_lanczos_begin(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                           rails_mv_t Q, int qc0);
 /* First kernel of a step of that chain on its own (unit tests, roofline timing):
  * with prev_col >= 0, Q[:, col] -= alpha * q_prev + |Q[:, prev_col]| * Q[:, prev2_col]
  * (q_prev = Q[:, prev_col] normalised, written back; prev2_col < 0: no last term),

@@ -104,6 +104,7 @@ CUDA_SYMBOLS = [
     ("rails_mv_lanczos_update", I, [P, I, D, P, I, D, P, I, c_double_p]),
     ("rails_mv_lanczos_run", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, c_double_p, I, P, I, I,
                                  c_double_p, c_double_p, c_int_p]),
+    ("rails_mv_lanczos_begin", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, P, I]),
     ("rails_mv_lanczos_project", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, P, I, I, I, D, c_double_p]),
     ("rails_mv_orthogonalize", I, [P, I, I, I]),
     ("rails_mv_random", I, [P, I, I, LL, ctypes.c_uint]),

@@ -257,6 +257,8 @@ extern "C" int rails_cuda_finalize(void)
     if (c.h_small) cudaFreeHost(c.h_small);
     if (c.d_coef) cudaFree(c.d_coef);
     if (c.h_ring) cudaFreeHost(c.h_ring);
+    if (c.d_lz) cudaFree(c.d_lz);
+    c.d_lz = nullptr; c.lz_cap = 0; c.lz_pending = false;
     for (int i = 0; i < 2; ++i)
     {
         if (c.h_stage[i]) cudaFreeHost(c.h_stage[i]);

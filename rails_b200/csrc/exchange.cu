@@ -286,6 +286,14 @@ int finish_reduction(const double *partial, int nblocks, int n, double *out, boo
     return RAILS_OK;
 }
 
+int lanczos_coef(const double *T, int k, int n, const double *g, double *coef)
+{
+    const int warps = 2 * k + (n - 2 * k + 31) / 32;
+    RAILS_LAUNCH(coef_plain_kernel, (warps * 32 + 255) / 256, 256, 0, T, k, n, g, coef);
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
+}
+
 // Called from rails_cuda_comm_init after the NCCL communicator exists: allocates
 // this rank's mailbox, exchanges CUDA IPC handles through NCCL and maps the
 // peers'.  Any failure leaves p2p = false (NCCL all-reduce is used instead).

@@ -102,6 +102,13 @@ struct Context
     void *mb_mapped[MB_MAX_RANKS] = {nullptr};
     unsigned long long mb_seq = 0;           // exchanges issued so far (same on every rank)
     int *d_mb_error = nullptr;               // set by a kernel whose wait timed out
+    // rails_mv_lanczos_begin -> rails_mv_lanczos_run hand-over: scratch that
+    // survives other library calls, and what the pending first projection was for
+    double *d_lz = nullptr;
+    size_t lz_cap = 0;
+    bool lz_pending = false;
+    const double *lz_q = nullptr;
+    int lz_total = 0;
     std::atomic<long long> launches{0};
     std::atomic<long long> errors{0};        // calls that failed since the library was loaded
     std::atomic<long long> bytes_in_use{0};
@@ -137,6 +144,8 @@ int copy_d2h(void *dst, const void *src, size_t bytes);
 int finish_reduction(const double *partial, int nblocks, int n, double *out, bool over_ranks,
                      const double *T = nullptr, int k = 0, double *coef = nullptr,
                      double *norm_out = nullptr, const double *scale_sq = nullptr);
+// coef = [T g[k:2k) ; T g[0:k) ; g[2k:n)] on the device (T compact k x k)
+int lanczos_coef(const double *T, int k, int n, const double *g, double *coef);
 int setup_mailboxes();
 void release_mailboxes();
 

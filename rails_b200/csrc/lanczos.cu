@@ -759,6 +759,39 @@ extern "C" int rails_mv_lanczos_project(int nblk, const rails_mv_t *X, const int
     return RAILS_OK;
 }
 
+namespace
+{
+
+constexpr int LZ_MAXL = 256;           // Lanczos steps per call
+
+int lz_attr()
+{
+    static bool attr_set = false;
+    if (!attr_set)
+    {
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (MD_MAXCOLS + 1) * MD_WARPS * (int)sizeof(double)));
+        attr_set = true;
+    }
+    return RAILS_OK;
+}
+
+int lz_scratch(int total)
+{
+    rails::Context &c = ctx();
+    const size_t need = 2 * (size_t)LZ_MAXL + 1 + 2 * ((size_t)MD_MAXCOLS + 2);
+    (void)total;
+    if (c.lz_cap >= need) return RAILS_OK;
+    RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    if (c.d_lz) RAILS_CUDA_TRY(cudaFree(c.d_lz));
+    RAILS_CUDA_TRY(cudaMalloc(&c.d_lz, need * sizeof(double)));
+    RAILS_CUDA_TRY(cudaMemset(c.d_lz, 0, need * sizeof(double)));
+    c.lz_cap = need;
+    return RAILS_OK;
+}
+
+}
+
 // The whole L-step recurrence of Solver::resid_lanczos
 // (src/LyapunovSolver.hpp:375-434) as ONE asynchronous chain on the library
 // stream: no value returns to the host until the last step has been enqueued.
@@ -794,19 +827,27 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
     const bool reduce = dist && Q->flags == RAILS_MV_DISTRIBUTED && c.comm;
     *steps = 0;
 
-    // device scratch: g[total + 1] | coef[total] | a[L] | b2[L + 1]   (b2[i] = |w_i|^2)
-    const int tot1 = std::max(total, 1) + 1;
-    const size_t need = 2 * (size_t)tot1 + 2 * (size_t)L + 1;
-    rc = rails::ensure_small(need);
+    // device scratch (own buffer: it must survive the calls between
+    // rails_mv_lanczos_begin and this one):
+    //   b2[LZ_MAXL + 1] | a[LZ_MAXL] | g[total + 1] | coef[total + 1]      (b2[i] = |w_i|^2)
+    if (L > LZ_MAXL)
+        return rails::fail(RAILS_ERR_ARG, "lanczos_run: at most %d steps", LZ_MAXL);
+    const bool started = c.lz_pending && c.lz_q == Q->data + (size_t)qc0 * Q->ld && c.lz_total == total;
+    c.lz_pending = false;
+    rc = lz_scratch(total);
     if (rc) return rc;
-    double *g = c.d_small, *coef = g + tot1, *a = coef + tot1, *b2 = a + L;
+    const int tot1 = std::max(total, 1) + 1;
+    double *b2 = c.d_lz, *a = b2 + LZ_MAXL + 1, *g = a + LZ_MAXL, *coef = g + tot1;
     const double *dT = nullptr;
     if (k > 0)
     {
         rc = rails::upload_small(T, k, k, ldt, &dT);
         if (rc) return rc;
     }
-    RAILS_CUDA_TRY(cudaMemsetAsync(a, 0, (2 * (size_t)L + 1) * sizeof(double), c.stream));
+    // b2[0] (and g) are already there when the first projection was started early
+    RAILS_CUDA_TRY(cudaMemsetAsync(b2 + 1, 0, (2 * (size_t)LZ_MAXL) * sizeof(double), c.stream));
+    if (!started)
+        RAILS_CUDA_TRY(cudaMemsetAsync(b2, 0, sizeof(double), c.stream));
 
     const long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
     const int nb_dot = (int)std::max<long long>(1, std::min<long long>(ntiles, (long long)c.sm_count * 4));
@@ -814,13 +855,8 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
     const int nb_gemv = (int)std::max<long long>(1, (rows2 + (long long)MG_THREADS * MG_RP - 1) / ((long long)MG_THREADS * MG_RP));
     rc = rails::ensure_partial(std::max<size_t>((size_t)nb_dot * (total + 1), (size_t)nb_gemv));
     if (rc) return rc;
-    static bool attr_set = false;
-    if (!attr_set)
-    {
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (MD_MAXCOLS + 1) * MD_WARPS * (int)sizeof(double)));
-        attr_set = true;
-    }
+    rc = lz_attr();
+    if (rc) return rc;
     if (rows > 0)
     {
         // The Lanczos vectors are kept UN-normalised while the recurrence runs
@@ -834,14 +870,24 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
         for (int i = 0; i < L; ++i)
         {
             double *col = Q->data + (size_t)(qc0 + i) * Q->ld;
-            RAILS_LAUNCH(lanczos_dot_kernel, nb_dot, MD_THREADS, (size_t)(total + 1) * MD_WARPS * sizeof(double),
-                         S, total, col, i > 0 ? col - Q->ld : (double *)nullptr,
-                         i > 1 ? (const double *)(col - 2 * Q->ld) : (const double *)nullptr,
-                         (const double *)(a + std::max(i - 1, 0)), (const double *)(b2 + std::max(i - 1, 0)),
-                         rows, c.d_partial);
-            RAILS_CHECK_LAUNCH();
-            rc = rails::finish_reduction(c.d_partial, nb_dot, total + 1, g, reduce, dT, k, coef, b2 + i);
-            if (rc) return rc;
+            if (i == 0 && started)
+            {
+                // A_0 and its exchange ran while the host solved the projected
+                // problem (rails_mv_lanczos_begin); only the k x k products remain
+                rc = rails::lanczos_coef(dT, k, total, g, coef);
+                if (rc) return rc;
+            }
+            else
+            {
+                RAILS_LAUNCH(lanczos_dot_kernel, nb_dot, MD_THREADS, (size_t)(total + 1) * MD_WARPS * sizeof(double),
+                             S, total, col, i > 0 ? col - Q->ld : (double *)nullptr,
+                             i > 1 ? (const double *)(col - 2 * Q->ld) : (const double *)nullptr,
+                             (const double *)(a + std::max(i - 1, 0)), (const double *)(b2 + std::max(i - 1, 0)),
+                             rows, c.d_partial);
+                RAILS_CHECK_LAUNCH();
+                rc = rails::finish_reduction(c.d_partial, nb_dot, total + 1, g, reduce, dT, k, coef, b2 + i);
+                if (rc) return rc;
+            }
             RAILS_LAUNCH(multi_gemv_kernel, nb_gemv, MG_THREADS, (size_t)std::max(total, 1) * sizeof(double),
                          S, total, coef, col + Q->ld, col, rows, c.d_partial);
             RAILS_CHECK_LAUNCH();
@@ -855,7 +901,9 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
         RAILS_CHECK_LAUNCH();
     }
     // one read-back for the whole recurrence
-    RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, a, (2 * (size_t)L + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    rc = rails::ensure_small(2 * (size_t)LZ_MAXL + 1);
+    if (rc) return rc;
+    RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, b2, (2 * (size_t)LZ_MAXL + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
     int xerr = 0;
     if (c.d_mb_error)
         RAILS_CUDA_TRY(cudaMemcpyAsync(&xerr, c.d_mb_error, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
@@ -865,12 +913,57 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
     int done = 0;
     for (int i = 0; i < L; ++i)
     {
-        alpha[i] = c.h_small[i];
-        beta[i] = std::sqrt(std::fabs(c.h_small[L + 1 + i]));
+        alpha[i] = c.h_small[LZ_MAXL + 1 + i];
+        beta[i] = std::sqrt(std::fabs(c.h_small[i + 1]));
         done = i + 1;
         if (beta[i] < 1e-14)
             break;
     }
     *steps = done;
+    return RAILS_OK;
+}
+
+// Starts the recurrence early: the first projection [X_0 X_1 ..]' w_0 and |w_0|^2
+// do not depend on T, so they can run on the GPU while the host solves the
+// projected problem (src/LyapunovSolver.hpp:209 -> :215).  The matching
+// rails_mv_lanczos_run (same Q, qc0 and blocks) picks the result up.
+extern "C" int rails_mv_lanczos_begin(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
+                                      rails_mv_t Q, int qc0)
+{
+    RAILS_REQUIRE_READY();
+    rails::Context &c = ctx();
+    c.lz_pending = false;
+    if (!Q || qc0 < 0 || qc0 >= Q->cols)
+        return rails::fail(RAILS_ERR_ARG, "lanczos_begin: bad start column");
+    Segs S;
+    int total = 0;
+    bool dist = false;
+    int rc = collect_segs(nblk, X, xc0, xn, Q->rows, &S, &total, &dist, "lanczos_begin");
+    if (rc) return rc;
+    if (total > MD_MAXCOLS || Q->rows == 0)
+        return RAILS_OK;                 // nothing started; lanczos_run does everything
+    const bool reduce = dist && Q->flags == RAILS_MV_DISTRIBUTED && c.comm;
+    rc = lz_scratch(total);
+    if (rc) return rc;
+    const int tot1 = std::max(total, 1) + 1;
+    double *b2 = c.d_lz, *g = b2 + 2 * LZ_MAXL + 1;
+    (void)tot1;
+    const long long rows = Q->rows;
+    const long long ntiles = (rows + MD_TILE - 1) / MD_TILE;
+    const int nb_dot = (int)std::max<long long>(1, std::min<long long>(ntiles, (long long)c.sm_count * 4));
+    rc = rails::ensure_partial((size_t)nb_dot * (total + 1));
+    if (rc) return rc;
+    rc = lz_attr();
+    if (rc) return rc;
+    double *col = Q->data + (size_t)qc0 * Q->ld;
+    RAILS_LAUNCH(lanczos_dot_kernel, nb_dot, MD_THREADS, (size_t)(total + 1) * MD_WARPS * sizeof(double),
+                 S, total, col, (double *)nullptr, (const double *)nullptr, (const double *)b2, (const double *)b2,
+                 rows, c.d_partial);
+    RAILS_CHECK_LAUNCH();
+    rc = rails::finish_reduction(c.d_partial, nb_dot, total + 1, g, reduce, nullptr, 0, nullptr, b2);
+    if (rc) return rc;
+    c.lz_pending = true;
+    c.lz_q = col;
+    c.lz_total = total;
     return RAILS_OK;
 }

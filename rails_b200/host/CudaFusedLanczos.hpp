@@ -108,6 +108,21 @@ struct FusedLanczos<CudaMultiVectorWrapper, HostDenseMatrix>
                       << rails_cuda_last_error() << std::endl;
     }
 
+    // First projection of the chain, enqueued before T exists (rails_mv_lanczos_begin)
+    static void begin(CudaMultiVectorWrapper const &AV, CudaMultiVectorWrapper const &V,
+                      CudaMultiVectorWrapper const &B, CudaMultiVectorWrapper &Q, int max_iter)
+    {
+        if (per_step() || AV.N() != V.N())
+            return;
+        Q.resize(max_iter + 1);
+        rails_mv_t blocks[3] = {V.device_handle(), AV.device_handle(), B.device_handle()};
+        int col0[3] = {V.device_col0(), AV.device_col0(), B.device_col0()};
+        int ncols[3] = {V.N(), AV.N(), B.N()};
+        report(rails_mv_lanczos_begin(3, blocks, col0, ncols, Q.device_handle(), Q.device_col0()),
+               "lanczos_begin");
+        Q.resize(1);
+    }
+
     // Q holds the un-normalised random start vector in column 0 and has room
     // for max_iter + 1 columns.  Returns the number of Lanczos steps.
     static int run(CudaMultiVectorWrapper const &AV, CudaMultiVectorWrapper const &V,

@@ -100,6 +100,8 @@ struct FusedLanczos
     static bool active() { return false; }
     static int run(MultiVector const &, MultiVector const &, DenseMatrix const &,
                    MultiVector const &, DenseMatrix &, MultiVector &, int) { return -1; }
+    // optional head start before T is known (Q holds the random start vector)
+    static void begin(MultiVector const &, MultiVector const &, MultiVector const &, MultiVector &, int) {}
 };
 
 // Customisation point: several independent inner products X_i' Y_i returned
@@ -166,6 +168,15 @@ public:
     int resid_lanczos(MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
                       DenseMatrix &H, MultiVector &eigenvectors, DenseMatrix &eigenvalues,
                       int max_iter);
+    // same, continuing from a start vector that lanczos_start() already drew
+    // (and, on a backend with fused kernels, already projected)
+    int resid_lanczos(MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
+                      DenseMatrix &H, MultiVector &eigenvectors, DenseMatrix &eigenvalues,
+                      int max_iter, MultiVector *started);
+    // Q = random start vector (:372-374), drawn BEFORE the projected solve so
+    // that a backend can overlap the first projection with it; returns false
+    // when the backend has no use for that
+    bool lanczos_start(MultiVector const &AV, MultiVector const &V, MultiVector &Q, int max_iter);
 
     // Exact eigenpairs of the residual through a tall-skinny QR of its factor
     // ("Residual method" = 1; BASELINE.json north_star item (3)):

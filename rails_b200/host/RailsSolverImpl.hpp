@@ -250,6 +250,13 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         if (W.N())
             project(V, W, AV, BV, MV, VAV, VBV, VMV, iter == 0, max_size);
 
+        // the Lanczos start vector is drawn here rather than after the projected
+        // solve (neither draws from std::rand() in between, so the random stream
+        // is the reference's): the GPU projects it while the host works on T
+        MultiVector Qstart;
+        const bool started = residual_method_ == 0 &&
+                             lanczos_start(AV, use_mass_ ? MV : V, Qstart, lanczos_iterations_);
+
         if (use_mass_)
             dense_solve_generalized(VAV, VMV, VBV, T);
         else
@@ -264,7 +271,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         if (residual_method_ == 1 && B_.is_multivector() && 2 * V.N() + B_.multivector().N() <= n)
             have_ritz = resid_tsqr(AV, use_mass_ ? MV : V, T, ritz_vectors, ritz_values) == 0;
         if (!have_ritz)
-            resid_lanczos(AV, use_mass_ ? MV : V, T, H, ritz_vectors, ritz_values, L);
+            resid_lanczos(AV, use_mass_ ? MV : V, T, H, ritz_vectors, ritz_values, L,
+                          started ? &Qstart : (MultiVector *) nullptr);
 
         const double res = ritz_values.norm_inf();
 
@@ -484,15 +492,44 @@ int Solver<Matrix, MultiVector, DenseMatrix>::dense_solve_generalized(
 // operator applied through its low-rank factors (:367-447):
 //     R q = B (B' q) + AV (T (V' q)) + V (T (AV' q))
 template<class Matrix, class MultiVector, class DenseMatrix>
+bool Solver<Matrix, MultiVector, DenseMatrix>::lanczos_start(
+    MultiVector const &AV, MultiVector const &V, MultiVector &Q, int max_iter)
+{
+    if (!(FusedLanczos<MultiVector, DenseMatrix>::enabled && B_.is_multivector() &&
+          FusedLanczos<MultiVector, DenseMatrix>::active()))
+        return false;
+    Section s(sections_, "resid_lanczos");
+    Q = MultiVector(V, max_iter + 1);
+    Q.resize(1);
+    Q.random();
+    FusedLanczos<MultiVector, DenseMatrix>::begin(AV, V, B_.multivector(), Q, max_iter);
+    return true;
+}
+
+template<class Matrix, class MultiVector, class DenseMatrix>
 int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
     MultiVector const &AV, MultiVector const &V, DenseMatrix const &T, DenseMatrix &H,
     MultiVector &eigenvectors, DenseMatrix &eigenvalues, int max_iter)
 {
+    return resid_lanczos(AV, V, T, H, eigenvectors, eigenvalues, max_iter, (MultiVector *) nullptr);
+}
+
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
+    MultiVector const &AV, MultiVector const &V, DenseMatrix const &T, DenseMatrix &H,
+    MultiVector &eigenvectors, DenseMatrix &eigenvalues, int max_iter, MultiVector *started)
+{
     Section s(sections_, "resid_lanczos");
 
-    MultiVector Q(V, max_iter + 1);
-    Q.resize(1);
-    Q.random();
+    MultiVector Q;
+    if (started)
+        Q = *started;              // shallow: shares the buffer the backend is working on
+    else
+    {
+        Q = MultiVector(V, max_iter + 1);
+        Q.resize(1);
+        Q.random();
+    }
 
     H = 0.0;
 

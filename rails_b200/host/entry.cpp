@@ -60,7 +60,9 @@ void limit_blas_threads()
     setter f = (setter)dlsym(RTLD_DEFAULT, "openblas_set_num_threads");
     if (!f) return;
     const char *e = std::getenv("RAILS_BLAS_THREADS");
-    int n = e ? std::atoi(e) : 4;
+    // one thread: the projected solve (real Schur form of a k x k matrix) is
+    // level-1/2 bound; measured 195 us (1 thread) vs 330 us (4 threads) at k = 25
+    int n = e ? std::atoi(e) : 1;
     if (n > 0) f(n);
 }
 long long g_timed_launches = 0;

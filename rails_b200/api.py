@@ -219,3 +219,95 @@ def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, r
         out["V"] = V[:, :k.value]
         out["T"] = T[:k.value, :k.value]
     return out
+
+
+# ---- MatrixMarket / parameter files / post-processing (host library) ---------
+def _host_message():
+    f = host().rails_host_last_message
+    f.restype = ctypes.c_char_p
+    return f().decode()
+
+
+def mm_read_crs(path, row_begin=0, row_end=-1):
+    """Rows [row_begin, row_end) of a coordinate file as (rowptr, colidx, vals,
+    global_rows, cols); the reader the command-line driver uses for A, B, M."""
+    lib = host()
+    dims = (ctypes.c_longlong * 4)()
+    if lib.rails_host_mm_read_crs(path.encode(), ctypes.c_longlong(row_begin),
+                                  ctypes.c_longlong(row_end), dims):
+        raise RailsError(_host_message())
+    rows, global_rows, cols, nnz = (int(x) for x in dims)
+    rp = np.zeros(rows + 1, dtype=np.int32)
+    ci = np.zeros(nnz, dtype=np.int32)
+    v = np.zeros(nnz)
+    lib.rails_host_mm_fetch_crs(iptr(rp), iptr(ci), dptr(v))
+    return rp, ci, v, global_rows, cols
+
+
+def mm_read_dense(path):
+    lib = host()
+    r, c = ctypes.c_int(0), ctypes.c_int(0)
+    if lib.rails_host_mm_read_dense(path.encode(), ctypes.byref(r), ctypes.byref(c)):
+        raise RailsError(_host_message())
+    out = np.zeros((r.value, c.value), order="F")
+    if out.size:
+        lib.rails_host_mm_fetch_dense(dptr(out))
+    return out
+
+
+def mm_write_dense(path, a, comment=""):
+    a = np.asfortranarray(a, dtype=np.float64)
+    if a.ndim == 1:
+        a = a.reshape(-1, 1, order="F")
+    if host().rails_host_mm_write_dense(path.encode(), ctypes.c_int(a.shape[0]), ctypes.c_int(a.shape[1]),
+                                        dptr(a), ctypes.c_longlong(max(a.shape[0], 1)), comment.encode()):
+        raise RailsError(_host_message())
+
+
+def mm_write_crs(path, rowptr, colidx, vals, cols, global_rows=None, row_begin=0):
+    rows = rowptr.size - 1
+    global_rows = rows if global_rows is None else global_rows
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int32)
+    colidx = np.ascontiguousarray(colidx, dtype=np.int32)
+    vals = np.ascontiguousarray(vals, dtype=np.float64)
+    if host().rails_host_mm_write_crs(path.encode(), ctypes.c_int(rows), ctypes.c_int(global_rows),
+                                      ctypes.c_int(cols), ctypes.c_int(row_begin), iptr(rowptr),
+                                      iptr(colidx), dptr(vals)):
+        raise RailsError(_host_message())
+
+
+def params_get(path, sublist, key, default=None):
+    """Value of `key` in `sublist` of an XML/INI parameter file as a float, or
+    `default` when it is absent."""
+    val, found = ctypes.c_double(0.0), ctypes.c_int(0)
+    if host().rails_host_params_get(path.encode(), (sublist or "").encode(), key.encode(),
+                                    ctypes.byref(val), ctypes.byref(found)):
+        raise RailsError(_host_message())
+    return val.value if found.value else default
+
+
+def params_to_xml(path):
+    buf = ctypes.create_string_buffer(1 << 16)
+    if host().rails_host_params_to_xml(path.encode(), buf, ctypes.c_int(len(buf))):
+        raise RailsError(_host_message())
+    return buf.value.decode()
+
+
+def solution_eigs(V, T, num=10, tol=1e-6, global_rows=None):
+    """Dominant eigenpairs and trace of X = V T V' on the GPU
+    (rails_host_solution_eigs).  Returns (eigenvalues, eigenvectors, trace)."""
+    V = np.asfortranarray(V, dtype=np.float64)
+    T = np.asfortranarray(T, dtype=np.float64)
+    rows, k = V.shape
+    global_rows = rows if global_rows is None else global_rows
+    lam = np.zeros(max(k, 1))
+    Q = np.zeros((rows, max(k, 1)), order="F")
+    found, trace = ctypes.c_int(0), ctypes.c_double(0.0)
+    rc = host().rails_host_solution_eigs(
+        ctypes.c_int(rows), ctypes.c_int(global_rows), ctypes.c_int(k), dptr(V),
+        ctypes.c_longlong(max(rows, 1)), dptr(T), ctypes.c_int(max(k, 1)), ctypes.c_int(num),
+        ctypes.c_double(tol), ctypes.byref(found), dptr(lam), dptr(Q), ctypes.c_longlong(max(rows, 1)),
+        ctypes.byref(trace))
+    if rc:
+        raise RailsError("rails_host_solution_eigs failed (%d): %s" % (rc, _host_message()))
+    return lam[:found.value].copy(), Q[:, :found.value].copy(), trace.value

@@ -3,6 +3,8 @@
     rails_b200/librails_cuda.so   CUDA kernels + the C ABI of include/rails_cuda.h
     rails_b200/librails_host.so   C++ host side: wrapper classes, solver loop,
                                   sb03md stand-in, C entry points for Python
+    rails_b200/rails_cuda_main    the command-line driver (A.mtx B.mtx M.mtx ->
+                                  V.mtx T.mtx, counterpart of the reference's main.cpp)
 
 nvcc cross-compiles without a GPU; the .so files travel to the GPU box with the
 gpurun snapshot (they are git-ignored, not gpurun-ignored).
@@ -96,9 +98,22 @@ def build_host(force=False):
     return lib
 
 
+def build_cli(force=False):
+    libdir, blas = openblas_path()
+    src = os.path.join(HERE, "cli", "rails_main.cpp")
+    hdrs = [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith((".hpp", ".h"))]
+    exe = os.path.join(HERE, "rails_cuda_main")
+    if force or _stale(exe, [src] + hdrs + [os.path.join(HERE, "librails_host.so")]):
+        _run(["g++", "-std=c++17", "-O2", "-I" + INC, "-I" + HOST, "-o", exe, src,
+              "-L" + HERE, "-lrails_host", "-lrails_cuda", blas, "-lpthread",
+              "-Wl,--disable-new-dtags,-rpath," + libdir + ":$ORIGIN"])
+    return exe
+
+
 def build_all(force=False, verbose=False):
     build_cuda(force, verbose)
     build_host(force)
+    build_cli(force)
 
 
 if __name__ == "__main__":

@@ -196,3 +196,80 @@ extern "C" int b200loop_stl_solve(
     }
     return ret;
 }
+
+// The product loop over StlWrapper with everything the MATLAB-feature options
+// need (tests/test_matlab_features.py): a dense mass matrix, a warm-start
+// basis V0 and a null space.  M_in / V0 / N_in may be NULL.
+extern "C" int b200loop_stl_solve_ext(
+    int m, const int *rowptr, const int *colidx, const double *vals,
+    const double *M_in, int n_b, const double *B_in, unsigned seed,
+    int nparams, const char *const *keys, const double *pvals,
+    int k0, const double *V0, int n_null, const double *N_in,
+    int hist_cap, double *hist_abs, double *hist_rel, int *hist_k, int *hist_restarted,
+    int *hist_len, int *k_out, int v_cap_cols, double *V_out, double *T_out)
+{
+    std::srand(seed);
+
+    StlWrapper A(m, m);
+    A = 0.0;
+    for (int i = 0; i < m; ++i)
+        for (int p = rowptr[i]; p < rowptr[i + 1]; ++p)
+            A(i, colidx[p]) = vals[p];
+
+    StlWrapper M(m, m);
+    M = 0.0;
+    for (int j = 0; j < m; ++j)
+        for (int i = 0; i < m; ++i)
+            M(i, j) = M_in ? M_in[i + (size_t)j * m] : (i == j ? 1.0 : 0.0);
+
+    StlWrapper B(m, n_b);
+    for (int j = 0; j < n_b; ++j)
+        for (int i = 0; i < m; ++i)
+            B(i, j) = B_in[i + (size_t)j * m];
+
+    RAILS::b200::Solver<StlWrapper, StlWrapper, StlWrapper> solver(A, B, M);
+    rails_oracle::ParameterList params(nparams, keys, pvals);
+    int ret = solver.set_parameters(params);
+    if (ret)
+        return 100 + ret;
+    solver.set_verbose(false);
+    if (n_null > 0 && N_in)
+    {
+        StlWrapper N(m, n_null);
+        for (int j = 0; j < n_null; ++j)
+            for (int i = 0; i < m; ++i)
+                N(i, j) = N_in[i + (size_t)j * m];
+        solver.set_nullspace(N);
+    }
+
+    StlWrapper V(m, std::max(k0, 1));
+    for (int j = 0; j < k0; ++j)
+        for (int i = 0; i < m; ++i)
+            V(i, j) = V0[i + (size_t)j * m];
+    StlWrapper T;
+    ret = solver.solve(V, T);
+
+    auto const &h = solver.history();
+    if (hist_len)
+        *hist_len = (int)h.size();
+    for (int i = 0; i < std::min((int)h.size(), hist_cap); ++i)
+    {
+        if (hist_abs) hist_abs[i] = h[i].residual;
+        if (hist_rel) hist_rel[i] = h[i].relative;
+        if (hist_k) hist_k[i] = h[i].space_size;
+        if (hist_restarted) hist_restarted[i] = h[i].restarted ? 1 : 0;
+    }
+    int k = V.N();
+    if (k_out)
+        *k_out = k;
+    if (V_out && T_out && k <= v_cap_cols)
+    {
+        for (int j = 0; j < k; ++j)
+            for (int i = 0; i < m; ++i)
+                V_out[i + (size_t)j * m] = V(i, j);
+        for (int j = 0; j < k; ++j)
+            for (int i = 0; i < k; ++i)
+                T_out[i + (size_t)j * v_cap_cols] = T(i, j);
+    }
+    return ret;
+}

@@ -178,9 +178,10 @@ class MultiVector:
 
 
 def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, row_offset=0,
-          v_cap_cols=0, V0=None, time_from=0, time_to=0, hist_cap=4096, M=None):
-    """rails_host_solve_m through ctypes.  M = (rowptr, colidx, vals) of the mass
-    matrix rows of this rank (used with params["Use mass matrix"] = 1).  Returns a dict."""
+          v_cap_cols=0, V0=None, time_from=0, time_to=0, hist_cap=4096, M=None, nullspace=None):
+    """rails_host_solve_x through ctypes.  M = (rowptr, colidx, vals) of the mass
+    matrix rows of this rank (used with params["Use mass matrix"] = 1); nullspace =
+    this rank's rows of a space to project out of V.  Returns a dict."""
     lib = host()
     rows = rowptr.size - 1
     global_rows = rows if global_rows is None else global_rows
@@ -201,14 +202,16 @@ def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, r
     ss, su, sd = ctypes.c_double(0), ctypes.c_double(0), ctypes.c_double(0)
     Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
     mrp, mci, mv = M if M is not None else (None, None, None)
-    ret = lib.rails_host_solve_m(
+    Nc = None if nullspace is None else np.asfortranarray(nullspace, dtype=np.float64).reshape(rows, -1, order="F")
+    ret = lib.rails_host_solve_x(
         ctypes.c_int(rows), ctypes.c_int(global_rows), ctypes.c_int(row_offset),
         iptr(rowptr), iptr(colidx), dptr(vals), iptr(mrp), iptr(mci), dptr(mv),
         ctypes.c_int(n_b), dptr(Bc), ctypes.c_uint(seed),
         ctypes.c_int(len(keys)), karr, dptr(pv), ctypes.c_int(hist_cap), dptr(ha), dptr(hr),
         iptr(hk), dptr(hs), ctypes.byref(hl), ctypes.byref(k), ctypes.c_int(v_cap_cols),
         dptr(V), dptr(T), ctypes.c_int(time_from), ctypes.c_int(time_to), ctypes.byref(tm),
-        ctypes.byref(ss), ctypes.byref(su), ctypes.byref(sd))
+        ctypes.byref(ss), ctypes.byref(su), ctypes.byref(sd),
+        ctypes.c_int(0 if Nc is None else Nc.shape[1]), dptr(Nc))
     n = min(hl.value, hist_cap)
     out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
                space=hk[:n].copy(), seconds=hs[:n].copy(), timed_ms=tm.value,

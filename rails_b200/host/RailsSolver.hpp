@@ -150,7 +150,10 @@ public:
           max_iter_(1000), tol_(1e-3), expand_size_(3), lanczos_iterations_(10),
           restart_size_(-1), reduced_size_(-1), restart_iterations_(20),
           restart_tolerance_(tol_ * 1e-3), minimize_solution_space_(true),
-          restart_from_solution_(false), use_mass_(false), residual_method_(0), verbose_(true)
+          restart_from_solution_(false), use_mass_(false), residual_method_(0),
+          m_orthogonalization_(false), relative_restart_tolerance_(false), restart_upon_start_(false),
+          orthogonalize_candidates_(false), lanczos_vectors_(-1), has_nullspace_(false),
+          verbose_(true)
     {}
 
     virtual ~Solver() {}
@@ -184,8 +187,21 @@ public:
     //     F = Q_F R_F  ->  eig(R_F S R_F') = Y Theta Y'  ->  eigenvectors Q_F Y
     // No random start vector and no Lanczos breakdown: the result is the same
     // to rounding on every backend and GPU count.
-    int resid_tsqr(MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
-                   MultiVector &eigenvectors, DenseMatrix &eigenvalues);
+    // The factorisation is kept in `state` across outer iterations and only the
+    // columns that are new since the last call are orthogonalised.
+    struct TsqrState
+    {
+        MultiVector Q;            // orthonormal basis of span F, r columns
+        DenseMatrix RV, RA, RB;   // r x k, r x k, r x n:  [V, AV, B] = Q [RV, RA, RB]
+        int columns;              // columns of V / AV already factorised
+        int capacity;             // column capacity of Q
+        bool valid;
+        TsqrState() : columns(0), capacity(0), valid(false) {}
+    };
+    int resid_tsqr(TsqrState &state, MultiVector const &AV, MultiVector const &V,
+                   DenseMatrix const &T, MultiVector &eigenvectors, DenseMatrix &eigenvalues,
+                   int want);
+    void tsqr_append(TsqrState &state, MultiVector const &block, DenseMatrix &R);
 
     // Restart basis from the dominant eigenvectors of T
     int compute_restart_vectors(DenseMatrix &X, DenseMatrix const &T, int num, double tol);
@@ -194,6 +210,20 @@ public:
     // MATLAB lyap(VAV, VBV, [], VMV), matlab/RAILSsolver.m:381)
     int dense_solve_generalized(DenseMatrix const &A, DenseMatrix const &E, DenseMatrix const &B,
                                 DenseMatrix &X);
+
+    // ---- options of the MATLAB implementation (matlab/RAILSsolver.m), all off
+    // by default so that the loop above stays the C++ reference's ---------------
+    // opts.nullspace (:28-29,218-220): a space projected out of every vector
+    // that enters V.  Orthonormalised here (Morth(opts.nullspace, [])).
+    void set_nullspace(MultiVector const &N);
+    // Morth (:538-617): orthonormalise the columns of W against `against` and
+    // V -- Euclidean inner product, or the M inner product with
+    // "M-orthogonalization" -- and append the survivors (norm >= 1e-8 after the
+    // projection) to V.  Two classical Gram-Schmidt passes per column in place
+    // of MATLAB's single modified pass: same result to rounding, and each pass
+    // is one V'w + one V*c kernel instead of k dependent axpys.  Returns the
+    // number of columns appended.
+    int morth(MultiVector const &W, MultiVector const *against, MultiVector &V);
 
     // ---- additions ------------------------------------------------------
     void set_observer(Observer obs) { observer_ = obs; }
@@ -224,6 +254,14 @@ protected:
     bool restart_from_solution_;
     bool use_mass_;
     int residual_method_;     // 0: the reference's Lanczos, 1: TSQR + small eigenproblem
+    // MATLAB-only behaviour, each with the option it restates
+    bool m_orthogonalization_;        // opts.ortho = 'M'        (:31-34,303-304,406,527-528)
+    bool relative_restart_tolerance_; // d / max(d) > tol        (:476-477)
+    bool restart_upon_start_;         // opts.restart_upon_start (:48-51,456)
+    bool orthogonalize_candidates_;   // Morth(V2, .., V) before the selection (:403-409,517-531)
+    int lanczos_vectors_;             // opts.lanczos_vectors: candidates kept (:72-77,309-311)
+    bool has_nullspace_;
+    MultiVector nullspace_;
     bool verbose_;
 
     Observer observer_;
@@ -247,7 +285,8 @@ protected:
                  MultiVector &MV, DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, bool first,
                  int max_size);
     void compress(MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV, MultiVector &MV,
-                  DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, DenseMatrix const &T);
+                  DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, DenseMatrix const &T,
+                  TsqrState *tsqr = nullptr);
 };
 
 // A key is looked up as given, then UPPER, lower and Title Case; the last
@@ -297,6 +336,17 @@ int Solver<Matrix, MultiVector, DenseMatrix>::set_parameters(ParameterList &para
     use_mass_ = lookup_parameter(params, "Use mass matrix", use_mass_);
     // extension: 0 = Lanczos as the reference, 1 = TSQR of [V, AV, B] + small eigenproblem
     residual_method_ = lookup_parameter(params, "Residual method", residual_method_);
+
+    // extensions: options of matlab/RAILSsolver.m (see the member declarations)
+    m_orthogonalization_ = lookup_parameter(params, "M-orthogonalization", m_orthogonalization_);
+    relative_restart_tolerance_ = lookup_parameter(params, "Relative restart tolerance",
+                                                   relative_restart_tolerance_);
+    restart_upon_start_ = lookup_parameter(params, "Restart upon start", restart_upon_start_);
+    orthogonalize_candidates_ = lookup_parameter(params, "Orthogonalize candidates",
+                                                 orthogonalize_candidates_);
+    lanczos_vectors_ = lookup_parameter(params, "Lanczos vectors", lanczos_vectors_);
+    if (m_orthogonalization_)
+        use_mass_ = true;          // V'MV = I: the residual still needs MV (:391)
 
     if (lanczos_iterations_ <= expand_size_)
     {

@@ -139,11 +139,26 @@ void Solver<Matrix, MultiVector, DenseMatrix>::project(
 template<class Matrix, class MultiVector, class DenseMatrix>
 void Solver<Matrix, MultiVector, DenseMatrix>::compress(
     MultiVector &V, MultiVector &W, MultiVector &AV, MultiVector &BV, MultiVector &MV,
-    DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, DenseMatrix const &T)
+    DenseMatrix &VAV, DenseMatrix &VBV, DenseMatrix &VMV, DenseMatrix const &T, TsqrState *tsqr)
 {
     DenseMatrix X;
     compute_restart_vectors(X, T, std::min(reduced_size_, V.N()), restart_tolerance_);
     const int kept = X.N();
+
+    if (tsqr)
+    {
+        // V X and AV X are combinations of columns the basis already spans:
+        // the factorisation follows with two small products, Q is untouched
+        DenseMatrix RV = tsqr->RV * X, RA = tsqr->RA * X;
+        tsqr->RV = RV;
+        tsqr->RA = RA;
+        tsqr->columns = kept;
+        // ... unless the basis has grown well beyond what the compressed factor
+        // needs: then it is rebuilt from [B, V, AV] at the next estimate
+        const int needed = 2 * kept + (B_.is_multivector() ? B_.multivector().N() : 0);
+        if (tsqr->Q.N() > 2 * needed + 8)
+            tsqr->valid = false;
+    }
 
     V.view(0, kept - 1) = V * X;
     V.resize(kept);
@@ -199,6 +214,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
 
     const int n = V.M();
     int max_size = std::max(V.N(), std::min(restart_size_ > 0 ? restart_size_ : 100, n));
+    const bool custom_ortho = m_orthogonalization_ || has_nullspace_;
 
     if (!restart_from_solution_)
     {
@@ -206,7 +222,15 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         V.resize(max_size);
         V.resize(1);
         V.random();
-        V.orthogonalize();
+        if (custom_ortho)
+        {
+            // V = Morth(V, M, nullspace) (matlab/RAILSsolver.m:303-307)
+            MultiVector start = V.copy();
+            V.resize(0);
+            morth(start, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
+        }
+        else
+            V.orthogonalize();
     }
     else if (max_size != V.N())
     {
@@ -233,6 +257,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         VMV = DenseMatrix(max_size, max_size);
     }
 
+    TsqrState tsqr;                  // "Residual method" = 1: QR of [V, AV, B] kept across iterations
     bool converged_before = false;
     int last_restart = 0;
     const double r0 = B_.norm();
@@ -257,7 +282,9 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         const bool started = residual_method_ == 0 &&
                              lanczos_start(AV, use_mass_ ? MV : V, Qstart, lanczos_iterations_);
 
-        if (use_mass_)
+        // an M-orthonormal basis has V'MV = I: the standard projected equation
+        // (matlab/RAILSsolver.m:375-385, `hasM && ~mortho`)
+        if (use_mass_ && !m_orthogonalization_)
             dense_solve_generalized(VAV, VMV, VBV, T);
         else
             dense_solve(VAV, VBV, T);
@@ -268,8 +295,11 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         MultiVector ritz_vectors;
         // generalised residual AV T MV' + MV T AV' + B B' (matlab/RAILSsolver.m:391)
         bool have_ritz = false;
-        if (residual_method_ == 1 && B_.is_multivector() && 2 * V.N() + B_.multivector().N() <= n)
-            have_ritz = resid_tsqr(AV, use_mass_ ? MV : V, T, ritz_vectors, ritz_values) == 0;
+        if (residual_method_ == 1 && B_.is_multivector())
+        {
+            const int want = std::max(expand_size_, orthogonalize_candidates_ ? lanczos_vectors_ : 0);
+            have_ritz = resid_tsqr(tsqr, AV, use_mass_ ? MV : V, T, ritz_vectors, ritz_values, want) == 0;
+        }
         if (!have_ritz)
             resid_lanczos(AV, use_mass_ ? MV : V, T, H, ritz_vectors, ritz_values, L,
                           started ? &Qstart : (MultiVector *) nullptr);
@@ -319,7 +349,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
 
         const bool space_full = restart_size_ > 0 && V.N() >= restart_size_;
         const bool period_over = restart_iterations_ > 0 && iter - last_restart >= restart_iterations_;
-        if (space_full || period_over || converged)
+        const bool at_start = restart_upon_start_ && iter == 0;    // matlab/RAILSsolver.m:456
+        if (space_full || period_over || converged || at_start)
         {
             if (verbose_)
             {
@@ -328,6 +359,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
                               << "space size";
                 else if (restart_size_ > 0)
                     std::cout << "Reached the maximum space size of " << restart_size_;
+                else if (at_start)
+                    std::cout << "Restart upon start";
                 else if (restart_iterations_ > 0)
                     std::cout << restart_iterations_ << " iterations have passed";
                 else
@@ -337,7 +370,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
                           << " vectors" << std::endl;
             }
 
-            compress(V, W, AV, BV, MV, VAV, VBV, VMV, T);
+            compress(V, W, AV, BV, MV, VAV, VBV, VMV, T, tsqr.valid ? &tsqr : (TsqrState *) nullptr);
             last_restart = iter;
 
             rec.restarted = true;
@@ -385,15 +418,49 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         }
 
         // expand with the Ritz vectors of the largest residual Ritz values
-        std::vector<int> picked = detail::largest_by_magnitude(ritz_values, grow_by);
-        for (int i = 0; i < grow_by; i++)
-            V.push_back(ritz_vectors.view(picked[i]));
+        int appended = grow_by;
+        if (orthogonalize_candidates_)
         {
+            // matlab/RAILSsolver.m:403-409,517-531: the nev leading candidates are
+            // orthonormalised against V first (those already inside the space
+            // drop out), the first `grow_by` survivors are then appended
+            Section s(sections_, "orthogonalize");
+            const int nev = std::min(lanczos_vectors_ > 0 ? lanczos_vectors_ : expand_size_,
+                                     ritz_values.M());
+            std::vector<int> picked = detail::largest_by_magnitude(ritz_values, nev);
+            MultiVector candidates(V, std::max(nev, 1));
+            candidates.resize(0);
+            for (int i = 0; i < nev; i++)
+                candidates.push_back(ritz_vectors.view(picked[i]));
+            MultiVector survivors(V, std::max(nev, 1));
+            survivors.resize(0);
+            morth(candidates, &V, survivors);
+            survivors.resize(std::min(grow_by, survivors.N()));
+            appended = morth(survivors, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
+        }
+        else if (custom_ortho)
+        {
+            Section s(sections_, "orthogonalize");
+            std::vector<int> picked = detail::largest_by_magnitude(ritz_values, grow_by);
+            MultiVector block(V, std::max(grow_by, 1));
+            block.resize(0);
+            for (int i = 0; i < grow_by; i++)
+                block.push_back(ritz_vectors.view(picked[i]));
+            appended = morth(block, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
+        }
+        else
+        {
+            std::vector<int> picked = detail::largest_by_magnitude(ritz_values, grow_by);
+            for (int i = 0; i < grow_by; i++)
+                V.push_back(ritz_vectors.view(picked[i]));
             Section s(sections_, "orthogonalize");
             V.orthogonalize();
         }
 
-        W = V.view(cols_before, cols_before + grow_by - 1);
+        if (appended > 0)
+            W = V.view(cols_before, cols_before + appended - 1);
+        else
+            W.resize(0);      // every candidate was already in the space
 
         rec.seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
         trace_iteration(iter + 1);
@@ -601,73 +668,195 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
     return 0;
 }
 
-// Non-zero eigenpairs of R = F S F' from a QR factorisation of the tall-skinny
-// factor (see the declaration).  The QR is the backend's own column-wise CGS2
-// (orthogonalize(), src/StlWrapper.cpp:305-321) applied to a copy of F, R_F is
-// recovered as Q_F' F; everything else is (2k+n) x (2k+n) host work.  Returns
-// non-zero (and leaves the outputs alone) when F is numerically rank deficient,
-// in which case the caller falls back on the Lanczos estimate.
+// Orthogonalises the columns of `block` against the basis kept in `state` (two
+// classical Gram-Schmidt passes), appends the independent ones to the basis and
+// the coefficient columns to R: afterwards block = Q * R[:, new columns] to
+// rounding.  A column whose remainder is below 1e-10 of its norm is dependent --
+// from the second iteration on that is every expansion vector, an eigenvector of
+// the previous residual and therefore a combination of the columns already in
+// F -- and only contributes its coefficients.  Dropping it is what makes two
+// passes enough: normalising such a remainder would bring back O(1) components
+// along the old columns.
+template<class Matrix, class MultiVector, class DenseMatrix>
+void Solver<Matrix, MultiVector, DenseMatrix>::tsqr_append(
+    TsqrState &state, MultiVector const &block, DenseMatrix &R)
+{
+    const int e = block.N();
+    for (int j = 0; j < e; j++)
+    {
+        MultiVector w = block.view(j).copy();
+        const double full = w.norm();
+        const int r = state.Q.N();
+        DenseMatrix coef(std::max(r, 1), 1);
+        coef.resize(r, 1);
+        coef = 0.0;
+        for (int pass = 0; pass < 2 && r > 0; pass++)
+        {
+            DenseMatrix c = state.Q.dot(w);
+            w -= state.Q * c;
+            for (int i = 0; i < r; i++)
+                coef(i, 0) += c(i, 0);
+        }
+        const double rest = w.norm();
+        const bool independent = full > 0.0 && rest > 1e-10 * full;
+        if (independent)
+        {
+            w /= rest;
+            if (state.Q.N() + 1 > state.capacity)
+            {
+                state.capacity += 100;
+                const int have = state.Q.N();
+                state.Q.resize(state.capacity);
+                state.Q.resize(have);
+            }
+            state.Q.push_back(w);
+        }
+        // every R block carries one row per basis vector
+        const int rows = state.Q.N();
+        DenseMatrix *blocks[3] = {&state.RV, &state.RA, &state.RB};
+        for (int b = 0; b < 3; b++)
+        {
+            DenseMatrix &X = *blocks[b];
+            const int have_rows = X.M(), have_cols = X.N();
+            if (have_rows == rows)
+                continue;
+            X.resize(rows, have_cols);
+            for (int c2 = 0; c2 < have_cols; c2++)
+                for (int i = have_rows; i < rows; i++)
+                    X(i, c2) = 0.0;
+        }
+        const int col = R.N();
+        R.resize(rows, col + 1);
+        for (int i = 0; i < rows; i++)
+            R(i, col) = i < r ? coef(i, 0) : (independent ? rest : 0.0);
+    }
+}
+
+// Non-zero eigenpairs of the residual R = F S F' from a QR factorisation of its
+// tall-skinny factor (see the declaration), kept up to date incrementally:
+//     F = [V, AV, B] = Q [R_V, R_AV, R_B]
+//     E = R_V T R_AV' + R_AV T R_V' + R_B R_B'          (r x r, r = rank F)
+//     E = Y Theta Y'   ->   eigenvectors Q Y
+// Each outer iteration only orthogonalises the columns that are new since the
+// last call (e columns of V and of AV): 4 e passes over Q instead of the 2 L
+// passes over [V, AV, B] of the Lanczos estimate, and one Q * Y product for the
+// `want` leading eigenvectors only.  eigenvalues come back sorted by decreasing
+// magnitude (all r of them), eigenvectors holds the first `want`.
 template<class Matrix, class MultiVector, class DenseMatrix>
 int Solver<Matrix, MultiVector, DenseMatrix>::resid_tsqr(
-    MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
-    MultiVector &eigenvectors, DenseMatrix &eigenvalues)
+    TsqrState &state, MultiVector const &AV, MultiVector const &V, DenseMatrix const &T,
+    MultiVector &eigenvectors, DenseMatrix &eigenvalues, int want)
 {
     Section s(sections_, "resid_tsqr");
     MultiVector const &B = B_.multivector();
-    const int k = V.N(), nb = B.N(), c = 2 * k + nb;
+    const int k = V.N(), nb = B.N();
 
-    // exact-size views on the right: assigning into a view copies the source's
-    // whole allocation when the row capacities agree (src/StlWrapper.cpp:82-83),
-    // and V / AV carry spare columns
-    MultiVector F(V, c);
-    F.view(0, k - 1) = V.view(0, k - 1);
-    F.view(k, 2 * k - 1) = AV.view(0, k - 1);
-    F.view(2 * k, c - 1) = B.view(0, nb - 1);
-
-    MultiVector Q = F.copy();
-    Q.orthogonalize();
-    DenseMatrix R = Q.dot(F);                  // c x c, upper triangular up to rounding
-
-    double rmax = 0.0, rmin = 1e300;
-    for (int i = 0; i < c; i++)
+    if (!state.valid)
     {
-        const double d = std::abs(R(i, i));
-        if (!(d == d)) return 1;               // NaN: a column vanished during the QR
-        rmax = std::max(rmax, d);
-        rmin = std::min(rmin, d);
+        state.capacity = std::min(V.M(), std::max(100, 2 * k + nb + 2));
+        state.Q = MultiVector(V, state.capacity);
+        state.Q.resize(0);
+        // capacity up front: resize() keeps entries in place within it
+        const int kcap = std::max(V.N(), std::min(restart_size_ > 0 ? restart_size_ : 100, V.M())) + 1;
+        state.RV = DenseMatrix(state.capacity, kcap); state.RV.resize(0, 0);
+        state.RA = DenseMatrix(state.capacity, kcap); state.RA.resize(0, 0);
+        state.RB = DenseMatrix(state.capacity, std::max(nb, 1)); state.RB.resize(0, 0);
+        state.columns = 0;
+        tsqr_append(state, B.view(0, nb - 1), state.RB);
+        state.valid = true;
     }
-    if (!(rmin > 1e-13 * rmax))
-        return 1;
+    if (state.columns < k)
+    {
+        // bound to the view temporaries (a copy-constructed view would be a deep copy)
+        MultiVector const &Vnew = V.view(state.columns, k - 1);
+        tsqr_append(state, Vnew, state.RV);
+        MultiVector const &AVnew = AV.view(state.columns, k - 1);
+        tsqr_append(state, AVnew, state.RA);
+        state.columns = k;
+    }
 
-    // E = R_F S R_F' with S = [[0 T 0]; [T 0 0]; [0 0 I]]
-    DenseMatrix S(c, c);
-    S = 0.0;
-    for (int j = 0; j < k; j++)
-        for (int i = 0; i < k; i++)
+    const int r = state.Q.N();
+    DenseMatrix E = state.RV * (T * state.RA.transpose());
+    DenseMatrix E2 = state.RB * state.RB.transpose();
+    for (int j = 0; j < r; j++)
+        for (int i = 0; i <= j; i++)
         {
-            S(i, k + j) = T(i, j);
-            S(k + i, j) = T(i, j);
-        }
-    for (int i = 0; i < nb; i++)
-        S(2 * k + i, 2 * k + i) = 1.0;
-    DenseMatrix E = R * (S * R.transpose());
-    for (int j = 0; j < c; j++)
-        for (int i = 0; i < j; i++)
-        {
-            const double v = 0.5 * (E(i, j) + E(j, i));
+            const double v = E(i, j) + E(j, i) + E2(i, j);
             E(i, j) = v;
-            E(j, i) = v;
+            if (i != j)
+                E(j, i) = v;
         }
-
-    DenseMatrix Y(c, c), theta(c, 1);
+    DenseMatrix Y(r, r), theta(r, 1);
     E.eigs(Y, theta);
-    for (int i = 0; i < c; i++)
+    for (int i = 0; i < theta.M(); i++)
         if (!(theta(i, 0) == theta(i, 0)))
             return 1;
 
-    eigenvalues = theta;
-    eigenvectors = Q * Y;
+    const int found = theta.M();
+    std::vector<int> order = detail::largest_by_magnitude(theta, found);
+    want = std::max(1, std::min(want, found));
+    eigenvalues = DenseMatrix(found, 1);
+    DenseMatrix C(r, want);
+    for (int c = 0; c < found; c++)
+    {
+        eigenvalues(c, 0) = theta(order[c], 0);
+        if (c < want)
+            for (int i = 0; i < r; i++)
+                C(i, c) = Y(i, order[c]);
+    }
+    eigenvectors = state.Q * C;
     return 0;
+}
+
+template<class Matrix, class MultiVector, class DenseMatrix>
+void Solver<Matrix, MultiVector, DenseMatrix>::set_nullspace(MultiVector const &N)
+{
+    nullspace_ = N.copy();
+    nullspace_.orthogonalize();       // Morth(opts.nullspace, []) (matlab/RAILSsolver.m:218-220)
+    has_nullspace_ = nullspace_.N() > 0;
+}
+
+// Morth (matlab/RAILSsolver.m:538-617), see the declaration
+template<class Matrix, class MultiVector, class DenseMatrix>
+int Solver<Matrix, MultiVector, DenseMatrix>::morth(
+    MultiVector const &W, MultiVector const *against, MultiVector &V)
+{
+    const bool m_inner = m_orthogonalization_;
+    // w <- w - Q (Q' w), or w - Q (Q' M w) in the M inner product (:584-592,606-613)
+    auto remove = [&](MultiVector &w, MultiVector const &Q) {
+        if (Q.N() < 1)
+            return;
+        DenseMatrix c = m_inner ? Q.dot(M_ * w) : Q.dot(w);
+        w -= Q * c;
+    };
+    int appended = 0;
+    for (int i = 0; i < W.N(); i++)
+    {
+        MultiVector w = W.view(i).copy();
+        double nrm = w.norm();                  // v1 = W(:,i) / norm(W(:,i))
+        if (!(nrm > 0.0))
+            continue;
+        w /= nrm;
+        for (int pass = 0; pass < 2; pass++)
+        {
+            if (against)
+                remove(w, *against);
+            remove(w, V);
+        }
+        if (m_inner)
+        {
+            DenseMatrix g = w.dot(M_ * w);      // nrm = sqrt(v1' M v1)
+            nrm = g(0, 0) > 0.0 ? std::sqrt(g(0, 0)) : 0.0;
+        }
+        else
+            nrm = w.norm();
+        if (!(nrm >= 1e-8))                     // tol = 1e-8 (:554,578-580)
+            continue;
+        w /= nrm;
+        V.push_back(w);
+        appended++;
+    }
+    return appended;
 }
 
 template<class Matrix, class MultiVector, class DenseMatrix>
@@ -699,9 +888,14 @@ int Solver<Matrix, MultiVector, DenseMatrix>::compute_restart_vectors(
 
     // candidates are sorted by magnitude, so the rejected ones are a suffix
     // and column i can be written in place (:468-479)
+    // MATLAB cuts relative to the largest eigenvalue (matlab/RAILSsolver.m:476-477),
+    // the C++ reference on the absolute value (:468-479)
+    double scale = 1.0;
+    if (relative_restart_tolerance_ && num > 0)
+        scale = std::max(std::abs(vals(picked[0], 0)), 1e-300);
     int kept = 0;
     for (int i = 0; i < num; ++i)
-        if (std::abs(vals(picked[i], 0)) > tol)
+        if (std::abs(vals(picked[i], 0)) / scale > tol)
         {
             for (int j = 0; j < T.N(); ++j)
                 X(j, i) = vecs(j, picked[i]);

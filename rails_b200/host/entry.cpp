@@ -90,7 +90,10 @@ extern "C" {
 //            "Use mass matrix" = 1 (generalised equation A X M' + M X A' + B B' = 0,
 //            matlab/RAILSsolver.m:368-392); otherwise M is stored and never read,
 //            like the reference C++ loop.
-int rails_host_solve_m(int rows, int global_rows, int row_offset,
+//   n_null/N_in : this rank's rows of a null space to project out of every
+//            vector that enters V (rows x n_null, ld = rows; opts.nullspace of
+//            matlab/RAILSsolver.m:28-29), or 0/NULL
+int rails_host_solve_x(int rows, int global_rows, int row_offset,
                      const int *rowptr, const int *colidx, const double *vals,
                      const int *m_rowptr, const int *m_colidx, const double *m_vals,
                      int n_b, const double *B_in, unsigned seed,
@@ -99,7 +102,8 @@ int rails_host_solve_m(int rows, int global_rows, int row_offset,
                      double *hist_sec, int *hist_len,
                      int *k_io, int v_cap_cols, double *V_io, double *T_out,
                      int time_from, int time_to, float *timed_ms,
-                     double *solve_seconds, double *setup_seconds, double *dense_solve_seconds)
+                     double *solve_seconds, double *setup_seconds, double *dense_solve_seconds,
+                     int n_null, const double *N_in)
 {
     if (!rails_cuda_is_initialized())
     {
@@ -124,7 +128,8 @@ int rails_host_solve_m(int rows, int global_rows, int row_offset,
         B.random();
 
     KeyValueParameters params(nparams, keys, pvals);
-    const bool use_mass = params.get("Use mass matrix", false);
+    const bool use_mass = params.get("Use mass matrix", false) ||
+                          params.get("M-orthogonalization", false);
     CudaOperatorWrapper M = A;
     if (m_rowptr)
     {
@@ -143,6 +148,13 @@ int rails_host_solve_m(int rows, int global_rows, int row_offset,
     if (ret)
         return 100 + ret;
     solver.set_verbose(std::getenv("RAILS_VERBOSE") != nullptr);
+    if (n_null > 0 && N_in)
+    {
+        CudaMultiVectorWrapper N(global_rows, n_null);
+        if (rails_mv_upload(N.device_handle(), 0, n_null, N_in, rows))
+            return 200;
+        solver.set_nullspace(N);
+    }
 
     bool warm = params.get("Restart from solution", false);
     CudaMultiVectorWrapper V(global_rows, warm && k_io ? std::max(*k_io, 1) : 1);
@@ -222,6 +234,24 @@ int rails_host_solve_m(int rows, int global_rows, int row_offset,
                 T_out[i + (size_t)j * v_cap_cols] = T(i, j);
     }
     return ret;
+}
+
+int rails_host_solve_m(int rows, int global_rows, int row_offset,
+                     const int *rowptr, const int *colidx, const double *vals,
+                     const int *m_rowptr, const int *m_colidx, const double *m_vals,
+                     int n_b, const double *B_in, unsigned seed,
+                     int nparams, const char *const *keys, const double *pvals,
+                     int hist_cap, double *hist_abs, double *hist_rel, int *hist_k,
+                     double *hist_sec, int *hist_len,
+                     int *k_io, int v_cap_cols, double *V_io, double *T_out,
+                     int time_from, int time_to, float *timed_ms,
+                     double *solve_seconds, double *setup_seconds, double *dense_solve_seconds)
+{
+    return rails_host_solve_x(rows, global_rows, row_offset, rowptr, colidx, vals, m_rowptr, m_colidx,
+                              m_vals, n_b, B_in, seed, nparams, keys, pvals, hist_cap, hist_abs,
+                              hist_rel, hist_k, hist_sec, hist_len, k_io, v_cap_cols, V_io, T_out,
+                              time_from, time_to, timed_ms, solve_seconds, setup_seconds,
+                              dense_solve_seconds, 0, nullptr);
 }
 
 int rails_host_solve(int rows, int global_rows, int row_offset,

@@ -168,3 +168,35 @@ def assert_same_solve(d, o, tol, early=8, early_tol=1e-8, late_tol=1e-4, x_tol=1
     dx = lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"])
     assert dx < 300 * tol, dx
     return False
+
+
+def stl_solve_ext(rowptr, colidx, vals, B, params, M=None, V0=None, nullspace=None, seed=1,
+                  v_cap_cols=300, hist_cap=4096):
+    """The PRODUCT's solver loop over the reference's StlWrapper (CPU, dense),
+    with a dense mass matrix, a warm-start basis and a null space."""
+    lib = ref()
+    m = rowptr.size - 1
+    nk, karr, pv = _params(params)
+    B = np.asfortranarray(B, dtype=np.float64).reshape(m, -1, order="F")
+    Mc = None if M is None else np.asfortranarray(M, dtype=np.float64)
+    Vc = None if V0 is None else np.asfortranarray(V0, dtype=np.float64).reshape(m, -1, order="F")
+    Nc = None if nullspace is None else np.asfortranarray(nullspace, dtype=np.float64).reshape(m, -1, order="F")
+    ha, hr = np.zeros(hist_cap), np.zeros(hist_cap)
+    hk, hres = np.zeros(hist_cap, dtype=np.int32), np.zeros(hist_cap, dtype=np.int32)
+    hl, k = ctypes.c_int(0), ctypes.c_int(0)
+    V = np.zeros((m, v_cap_cols), order="F")
+    T = np.zeros((v_cap_cols, v_cap_cols), order="F")
+    ret = lib.b200loop_stl_solve_ext(
+        ctypes.c_int(m), iptr(rowptr), iptr(colidx), dptr(vals), dptr(Mc), ctypes.c_int(B.shape[1]),
+        dptr(B), ctypes.c_uint(seed), ctypes.c_int(nk), karr, dptr(pv),
+        ctypes.c_int(0 if Vc is None else Vc.shape[1]), dptr(Vc),
+        ctypes.c_int(0 if Nc is None else Nc.shape[1]), dptr(Nc),
+        ctypes.c_int(hist_cap), dptr(ha), dptr(hr), iptr(hk), iptr(hres), ctypes.byref(hl),
+        ctypes.byref(k), ctypes.c_int(v_cap_cols), dptr(V), dptr(T))
+    n = min(hl.value, hist_cap)
+    out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
+               space=hk[:n].copy(), restarted=hres[:n].copy())
+    if k.value <= v_cap_cols:
+        out["V"] = V[:, :k.value]
+        out["T"] = T[:k.value, :k.value]
+    return out

@@ -201,7 +201,8 @@ public:
     int resid_tsqr(TsqrState &state, MultiVector const &AV, MultiVector const &V,
                    DenseMatrix const &T, MultiVector &eigenvectors, DenseMatrix &eigenvalues,
                    int want);
-    void tsqr_append(TsqrState &state, MultiVector const &block, DenseMatrix &R);
+    void tsqr_append(TsqrState &state, std::vector<MultiVector const *> const &blocks,
+                     std::vector<DenseMatrix *> const &Rs);
 
     // Restart basis from the dominant eigenvectors of T
     int compute_restart_vectors(DenseMatrix &X, DenseMatrix const &T, int num, double tol);

@@ -304,6 +304,18 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
             resid_lanczos(AV, use_mass_ ? MV : V, T, H, ritz_vectors, ritz_values, L,
                           started ? &Qstart : (MultiVector *) nullptr);
 
+        // the QR path returns its eigenvalues sorted and only the leading
+        // eigenvectors: pick those in order (a tie must not send the unstable
+        // sort of the reference's selection to a column that was not computed)
+        auto pick_ritz = [&](int count) {
+            if (!have_ritz)
+                return detail::largest_by_magnitude(ritz_values, count);
+            std::vector<int> first(count);
+            for (int i = 0; i < count; i++)
+                first[i] = i;
+            return first;
+        };
+
         const double res = ritz_values.norm_inf();
 
         if (verbose_)
@@ -427,7 +439,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
             Section s(sections_, "orthogonalize");
             const int nev = std::min(lanczos_vectors_ > 0 ? lanczos_vectors_ : expand_size_,
                                      ritz_values.M());
-            std::vector<int> picked = detail::largest_by_magnitude(ritz_values, nev);
+            std::vector<int> picked = pick_ritz(nev);
             MultiVector candidates(V, std::max(nev, 1));
             candidates.resize(0);
             for (int i = 0; i < nev; i++)
@@ -441,7 +453,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         else if (custom_ortho)
         {
             Section s(sections_, "orthogonalize");
-            std::vector<int> picked = detail::largest_by_magnitude(ritz_values, grow_by);
+            std::vector<int> picked = pick_ritz(grow_by);
             MultiVector block(V, std::max(grow_by, 1));
             block.resize(0);
             for (int i = 0; i < grow_by; i++)
@@ -450,7 +462,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         }
         else
         {
-            std::vector<int> picked = detail::largest_by_magnitude(ritz_values, grow_by);
+            std::vector<int> picked = pick_ritz(grow_by);
             for (int i = 0; i < grow_by; i++)
                 V.push_back(ritz_vectors.view(picked[i]));
             Section s(sections_, "orthogonalize");
@@ -668,68 +680,107 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
     return 0;
 }
 
-// Orthogonalises the columns of `block` against the basis kept in `state` (two
-// classical Gram-Schmidt passes), appends the independent ones to the basis and
-// the coefficient columns to R: afterwards block = Q * R[:, new columns] to
-// rounding.  A column whose remainder is below 1e-10 of its norm is dependent --
-// from the second iteration on that is every expansion vector, an eigenvector of
-// the previous residual and therefore a combination of the columns already in
-// F -- and only contributes its coefficients.  Dropping it is what makes two
-// passes enough: normalising such a remainder would bring back O(1) components
-// along the old columns.
+// Orthogonalises the columns of the given blocks against the basis kept in
+// `state`, appends the independent ones to the basis and the coefficient
+// columns to the R factor of each block: afterwards blocks[i] = Q * Rs[i][:, new
+// columns] to rounding.  All columns are projected against the OLD basis
+// together (two classical Gram-Schmidt passes = two Q'W and two W -= Q C
+// products, whatever the number of columns: Q is streamed four times per call),
+// then one by one against the few columns this call has added.  A column whose
+// remainder is below 1e-10 of its norm is dependent -- from the second iteration
+// on that is every expansion vector, an eigenvector of the previous residual and
+// therefore a combination of the columns already in F -- and only contributes
+// its coefficients.  Dropping it is what makes two passes enough: normalising
+// such a remainder would bring back O(1) components along the old columns.
 template<class Matrix, class MultiVector, class DenseMatrix>
 void Solver<Matrix, MultiVector, DenseMatrix>::tsqr_append(
-    TsqrState &state, MultiVector const &block, DenseMatrix &R)
+    TsqrState &state, std::vector<MultiVector const *> const &blocks,
+    std::vector<DenseMatrix *> const &Rs)
 {
-    const int e = block.N();
-    for (int j = 0; j < e; j++)
+    int total = 0;
+    for (size_t b = 0; b < blocks.size(); b++)
+        total += blocks[b]->N();
+    if (total < 1)
+        return;
+
+    MultiVector W(*blocks[0], total);
+    W.resize(0);
+    for (size_t b = 0; b < blocks.size(); b++)
+        W.push_back(*blocks[b]);
+
+    std::vector<double> full(total);
+    for (int j = 0; j < total; j++)
     {
-        MultiVector w = block.view(j).copy();
-        const double full = w.norm();
-        const int r = state.Q.N();
-        DenseMatrix coef(std::max(r, 1), 1);
-        coef.resize(r, 1);
-        coef = 0.0;
-        for (int pass = 0; pass < 2 && r > 0; pass++)
-        {
-            DenseMatrix c = state.Q.dot(w);
-            w -= state.Q * c;
-            for (int i = 0; i < r; i++)
-                coef(i, 0) += c(i, 0);
-        }
-        const double rest = w.norm();
-        const bool independent = full > 0.0 && rest > 1e-10 * full;
-        if (independent)
-        {
-            w /= rest;
-            if (state.Q.N() + 1 > state.capacity)
-            {
-                state.capacity += 100;
-                const int have = state.Q.N();
-                state.Q.resize(state.capacity);
-                state.Q.resize(have);
-            }
-            state.Q.push_back(w);
-        }
-        // every R block carries one row per basis vector
-        const int rows = state.Q.N();
-        DenseMatrix *blocks[3] = {&state.RV, &state.RA, &state.RB};
-        for (int b = 0; b < 3; b++)
-        {
-            DenseMatrix &X = *blocks[b];
-            const int have_rows = X.M(), have_cols = X.N();
-            if (have_rows == rows)
-                continue;
-            X.resize(rows, have_cols);
-            for (int c2 = 0; c2 < have_cols; c2++)
-                for (int i = have_rows; i < rows; i++)
-                    X(i, c2) = 0.0;
-        }
-        const int col = R.N();
-        R.resize(rows, col + 1);
-        for (int i = 0; i < rows; i++)
-            R(i, col) = i < r ? coef(i, 0) : (independent ? rest : 0.0);
+        MultiVector const &w = static_cast<MultiVector const &>(W).view(j);
+        full[j] = w.norm();
     }
+
+    const int r0 = state.Q.N();
+    DenseMatrix coef(std::max(r0, 1), total);
+    coef.resize(r0, total);
+    coef = 0.0;
+    for (int pass = 0; pass < 2 && r0 > 0; pass++)
+    {
+        DenseMatrix C = state.Q.dot(W);
+        W -= state.Q * C;
+        for (int j = 0; j < total; j++)
+            for (int i = 0; i < r0; i++)
+                coef(i, j) += C(i, j);
+    }
+
+    if (r0 + total > state.capacity)
+    {
+        state.capacity = std::min(W.M(), std::max(state.capacity + 100, r0 + total));
+        state.Q.resize(state.capacity);
+        state.Q.resize(r0);
+    }
+
+    int col = 0;
+    for (size_t b = 0; b < blocks.size(); b++)
+        for (int jb = 0; jb < blocks[b]->N(); jb++, col++)
+        {
+            MultiVector &&w = W.view(col);
+            const int r = state.Q.N();                 // r0 + columns added by this call
+            std::vector<double> extra(r - r0, 0.0);
+            if (r > r0)
+            {
+                MultiVector const &added = static_cast<MultiVector const &>(state.Q).view(r0, r - 1);
+                for (int pass = 0; pass < 2; pass++)
+                {
+                    DenseMatrix c = added.dot(w);
+                    w -= added * c;
+                    for (int i = 0; i < r - r0; i++)
+                        extra[i] += c(i, 0);
+                }
+            }
+            const double rest = w.norm();
+            const bool independent = full[col] > 0.0 && rest > 1e-10 * full[col] &&
+                                     state.Q.N() < state.capacity;
+            if (independent)
+            {
+                w /= rest;
+                state.Q.push_back(w);
+            }
+            // every R block carries one row per basis vector
+            const int rows = state.Q.N();
+            DenseMatrix *all[3] = {&state.RV, &state.RA, &state.RB};
+            for (int q = 0; q < 3; q++)
+            {
+                DenseMatrix &X = *all[q];
+                const int have_rows = X.M(), have_cols = X.N();
+                if (have_rows == rows)
+                    continue;
+                X.resize(rows, have_cols);
+                for (int c2 = 0; c2 < have_cols; c2++)
+                    for (int i = have_rows; i < rows; i++)
+                        X(i, c2) = 0.0;
+            }
+            DenseMatrix &R = *Rs[b];
+            const int at = R.N();
+            R.resize(rows, at + 1);
+            for (int i = 0; i < rows; i++)
+                R(i, at) = i < r0 ? coef(i, col) : (i < r ? extra[i - r0] : (independent ? rest : 0.0));
+        }
 }
 
 // Non-zero eigenpairs of the residual R = F S F' from a QR factorisation of its
@@ -738,8 +789,8 @@ void Solver<Matrix, MultiVector, DenseMatrix>::tsqr_append(
 //     E = R_V T R_AV' + R_AV T R_V' + R_B R_B'          (r x r, r = rank F)
 //     E = Y Theta Y'   ->   eigenvectors Q Y
 // Each outer iteration only orthogonalises the columns that are new since the
-// last call (e columns of V and of AV): 4 e passes over Q instead of the 2 L
-// passes over [V, AV, B] of the Lanczos estimate, and one Q * Y product for the
+// last call (e columns of V and of AV, as one block): 4 passes over Q instead of
+// the 2 L passes over [V, AV, B] of the Lanczos estimate, and one Q * Y product for the
 // `want` leading eigenvectors only.  eigenvalues come back sorted by decreasing
 // magnitude (all r of them), eigenvectors holds the first `want`.
 template<class Matrix, class MultiVector, class DenseMatrix>
@@ -762,16 +813,21 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_tsqr(
         state.RA = DenseMatrix(state.capacity, kcap); state.RA.resize(0, 0);
         state.RB = DenseMatrix(state.capacity, std::max(nb, 1)); state.RB.resize(0, 0);
         state.columns = 0;
-        tsqr_append(state, B.view(0, nb - 1), state.RB);
+        MultiVector const &Ball = B.view(0, nb - 1);
+        tsqr_append(state, std::vector<MultiVector const *>(1, &Ball),
+                    std::vector<DenseMatrix *>(1, &state.RB));
         state.valid = true;
     }
     if (state.columns < k)
     {
         // bound to the view temporaries (a copy-constructed view would be a deep copy)
         MultiVector const &Vnew = V.view(state.columns, k - 1);
-        tsqr_append(state, Vnew, state.RV);
         MultiVector const &AVnew = AV.view(state.columns, k - 1);
-        tsqr_append(state, AVnew, state.RA);
+        std::vector<MultiVector const *> blocks;
+        std::vector<DenseMatrix *> factors;
+        blocks.push_back(&Vnew); factors.push_back(&state.RV);
+        blocks.push_back(&AVnew); factors.push_back(&state.RA);
+        tsqr_append(state, blocks, factors);
         state.columns = k;
     }
 

@@ -193,6 +193,7 @@ public:
     {
         MultiVector Q;            // orthonormal basis of span F, r columns
         DenseMatrix RV, RA, RB;   // r x k, r x k, r x n:  [V, AV, B] = Q [RV, RA, RB]
+        DenseMatrix RM;           // r x k: MV = Q RM ("Residual method" = 2 with a mass matrix)
         int columns;              // columns of V / AV already factorised
         int capacity;             // column capacity of Q
         bool valid;
@@ -203,6 +204,10 @@ public:
                    int want);
     void tsqr_append(TsqrState &state, std::vector<MultiVector const *> const &blocks,
                      std::vector<DenseMatrix *> const &Rs);
+    // "Residual method" = 2: the whole iteration in the coordinates of that basis
+    // (RailsCoefficientSpace.hpp)
+    int solve_coefficient_space(MultiVector &V, DenseMatrix &T);
+    void tsqr_shrink(TsqrState &state);
 
     // Restart basis from the dominant eigenvectors of T
     int compute_restart_vectors(DenseMatrix &X, DenseMatrix const &T, int num, double tol);
@@ -254,7 +259,8 @@ protected:
     bool minimize_solution_space_;
     bool restart_from_solution_;
     bool use_mass_;
-    int residual_method_;     // 0: the reference's Lanczos, 1: TSQR + small eigenproblem
+    int residual_method_;     // 0: the reference's Lanczos, 1: TSQR + small eigenproblem,
+                              // 2: the whole iteration in the coordinates of the TSQR basis
     // MATLAB-only behaviour, each with the option it restates
     bool m_orthogonalization_;        // opts.ortho = 'M'        (:31-34,303-304,406,527-528)
     bool relative_restart_tolerance_; // d / max(d) > tol        (:476-477)
@@ -335,7 +341,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::set_parameters(ParameterList &para
                                               restart_from_solution_);
     // extension (not a reference key): generalised equation with the stored M
     use_mass_ = lookup_parameter(params, "Use mass matrix", use_mass_);
-    // extension: 0 = Lanczos as the reference, 1 = TSQR of [V, AV, B] + small eigenproblem
+    // extension: 0 = Lanczos as the reference, 1 = TSQR of [V, AV, B] + small eigenproblem,
+    // 2 = projection, residual and orthogonalisation all in the coordinates of that basis
     residual_method_ = lookup_parameter(params, "Residual method", residual_method_);
 
     // extensions: options of matlab/RAILSsolver.m (see the member declarations)
@@ -363,5 +370,6 @@ int Solver<Matrix, MultiVector, DenseMatrix>::set_parameters(ParameterList &para
 }
 
 #include "RailsSolverImpl.hpp"
+#include "RailsCoefficientSpace.hpp"
 
 #endif

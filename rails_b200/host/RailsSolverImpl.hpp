@@ -209,6 +209,9 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         }
         std::cerr << std::endl;
     };
+    if (residual_method_ == 2 && B_.is_multivector() && !m_orthogonalization_ && !has_nullspace_)
+        return solve_coefficient_space(V, T);
+
     history_.clear();
     sections_.clear();
 
@@ -295,7 +298,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         MultiVector ritz_vectors;
         // generalised residual AV T MV' + MV T AV' + B B' (matlab/RAILSsolver.m:391)
         bool have_ritz = false;
-        if (residual_method_ == 1 && B_.is_multivector())
+        if (residual_method_ >= 1 && B_.is_multivector())
         {
             const int want = std::max(expand_size_, orthogonalize_candidates_ ? lanczos_vectors_ : 0);
             have_ritz = resid_tsqr(tsqr, AV, use_mass_ ? MV : V, T, ritz_vectors, ritz_values, want) == 0;
@@ -763,8 +766,8 @@ void Solver<Matrix, MultiVector, DenseMatrix>::tsqr_append(
             }
             // every R block carries one row per basis vector
             const int rows = state.Q.N();
-            DenseMatrix *all[3] = {&state.RV, &state.RA, &state.RB};
-            for (int q = 0; q < 3; q++)
+            DenseMatrix *all[4] = {&state.RV, &state.RA, &state.RB, &state.RM};
+            for (int q = 0; q < 4; q++)
             {
                 DenseMatrix &X = *all[q];
                 const int have_rows = X.M(), have_cols = X.N();
@@ -812,6 +815,7 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_tsqr(
         state.RV = DenseMatrix(state.capacity, kcap); state.RV.resize(0, 0);
         state.RA = DenseMatrix(state.capacity, kcap); state.RA.resize(0, 0);
         state.RB = DenseMatrix(state.capacity, std::max(nb, 1)); state.RB.resize(0, 0);
+        state.RM = DenseMatrix(1, 1); state.RM.resize(0, 0);
         state.columns = 0;
         MultiVector const &Ball = B.view(0, nb - 1);
         tsqr_append(state, std::vector<MultiVector const *>(1, &Ball),

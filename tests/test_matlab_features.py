@@ -118,8 +118,15 @@ def project_out(p, N):
     p["csr"] = (S.indptr.astype(np.int32), S.indices.astype(np.int32), S.data.copy())
 
 
-@pytest.mark.parametrize("name", CASE_NAMES)
-def test_product_loop_follows_matlab_restatement(name):
+# "Residual method" = 2 (the iteration in the coordinates of the TSQR basis,
+# rails_b200/host/RailsCoefficientSpace.hpp) is the same algorithm in exact
+# arithmetic: it must follow the restatement too.  It does not take a null space
+# or M-orthogonalisation.
+METHOD2_CASES = ["expand1", "expand2_nev4", "mass", "relative_cut", "restart_upon_start"]
+
+
+@pytest.mark.parametrize("name,method", [(c, 1) for c in CASE_NAMES] + [(c, 2) for c in METHOD2_CASES])
+def test_product_loop_follows_matlab_restatement(name, method):
     p = setup()
     mopts, popts, uses_m, V0, N = cases(p)[name]
     if N is not None:
@@ -127,6 +134,7 @@ def test_product_loop_follows_matlab_restatement(name):
     o = run_oracle(p, mopts, uses_m, V0, N)
     P = dict(BASE)
     P.update(popts)
+    P["Residual method"] = method
     q = harness.stl_solve_ext(*p["csr"], p["B"], P, M=p["M"] if uses_m else None, V0=V0, nullspace=N)
     assert q["ret"] == (0 if o["res"] < TOL else -1)
     compare(o, q, p["n"])
@@ -143,16 +151,18 @@ def test_product_loop_follows_matlab_restatement(name):
         assert np.linalg.norm(R, 2) < TOL * np.linalg.norm(B.T @ B, 2) * 1.001
 
 
-def test_exact_residual_eigenpairs_at_every_iteration():
-    """The residual estimate of "Residual method" = 1 is the spectral norm of the
-    explicit residual at every iteration, including those where [V, AV, B] is
+@pytest.mark.parametrize("method", [1, 2])
+def test_exact_residual_eigenpairs_at_every_iteration(method):
+    """The residual estimate of "Residual method" = 1 / 2 is the spectral norm of
+    the explicit residual at every iteration, including those where [V, AV, B] is
     rank deficient (from the second one on) and where 2k + n exceeds what L
     Lanczos steps could resolve."""
     p = setup(g=12, n_b=2)
     A, B = p["A"], p["B"]
     for stop in (2, 9, 23, 36, 40):
         P = dict(BASE, **{"Tolerance": 1e-14, "Maximum iterations": stop, "Expand size": 1,
-                          "Lanczos iterations": 3, "Minimize solution space": 0})
+                          "Lanczos iterations": 3, "Minimize solution space": 0,
+                          "Residual method": method})
         q = harness.stl_solve_ext(*p["csr"], B, P, V0=p["V0"])
         assert q["iterations"] == stop and q["k"] == stop
         X = q["V"] @ q["T"] @ q["V"].T
@@ -171,3 +181,47 @@ def test_default_options_leave_the_reference_loop_untouched():
     q = harness.stl_solve_ext(rp, ci, v, B, P, v_cap_cols=100)
     assert q["iterations"] == r["iterations"] and np.array_equal(q["rel"], r["rel"])
     assert np.array_equal(q["V"], r["V"]) and np.array_equal(q["T"], r["T"])
+
+
+@pytest.mark.parametrize("kind,g,dim,n_b,extra", [
+    ("laplacian", 16, 2, 1, {}),
+    ("convdiff", 6, 3, 3, {"Expand size": 3}),
+    ("laplacian", 14, 2, 2, {"Expand size": 2, "Restart size": 24, "Reduced size": 10}),
+    ("laplacian", 12, 2, 1, {"Restart iterations": 7, "Minimize solution space": 0}),
+])
+def test_coefficient_space_solve_from_a_random_start(kind, g, dim, n_b, extra):
+    """"Residual method" = 2 as a user runs it (random start vector, default
+    options, restarts that shrink the basis): converges, the reported estimate is
+    the true residual norm, V is orthonormal, and methods 1 and 2 -- the same
+    algorithm, organised differently -- take the same number of iterations."""
+    rp, ci, v = problems.build(kind, g, dim)
+    m = rp.size - 1
+    B = np.asfortranarray(np.random.RandomState(8).uniform(-1, 1, (m, n_b)))
+    P = {"Tolerance": 1e-7, "Expand size": 1, "Lanczos iterations": 10, "Maximum iterations": 500,
+         "Orthogonalize candidates": 1}
+    P.update(extra)
+    out = {}
+    for method in (1, 2):
+        q = harness.stl_solve_ext(rp, ci, v, B, dict(P, **{"Residual method": method}), v_cap_cols=m)
+        assert q["ret"] == 0
+        V, T = q["V"], q["T"]
+        assert np.linalg.norm(V.T @ V - np.eye(V.shape[1])) < 1e-10
+        A = harness.csr_to_dense(rp, ci, v, m)
+        X = V @ T @ V.T
+        R = A @ X + X @ A.T + B @ B.T
+        exact = np.max(np.abs(np.linalg.eigvalsh(0.5 * (R + R.T))))
+        assert abs(q["abs"][-1] - exact) < 1e-6 * exact
+        assert exact < 1e-7 * np.linalg.norm(B.T @ B, 2)
+        out[method] = q
+    if "Restart size" in extra:
+        # some twenty compression restarts, each re-amplifying rounding
+        # differences (DESIGN.md "Reproducibility"): same path at first, same
+        # answer, iteration counts within a few
+        assert abs(out[1]["iterations"] - out[2]["iterations"]) <= 5
+        err = np.abs(out[1]["rel"][:30] - out[2]["rel"][:30]) / out[1]["rel"][:30]
+        assert np.max(err[:10]) < 1e-7 and np.max(err) < 1e-3
+        return
+    assert out[1]["iterations"] == out[2]["iterations"]
+    assert np.array_equal(out[1]["space"], out[2]["space"])
+    err = np.abs(out[1]["rel"] - out[2]["rel"]) / out[1]["rel"]
+    assert np.max(err[:8]) < 1e-9 and np.max(err) < 1e-2

@@ -27,6 +27,10 @@ entry point rails_host_solve_m with HOST buffers -- the CSR arrays of A (and M)
 and B are uploaded, V and T downloaded, inside the timed wall-clock region;
 value = iterations to tolerance / that time (also reported as
 time_to_tolerance_s).
+`e2e_tsqr`: the same end-to-end solve with "Residual method" = 2 (exact
+residual eigenpairs from the tall-skinny QR of [B, V, AV, MV]; projection,
+Gram-Schmidt and restarts on the R factors).  A different sequence of iterates
+from the reference's Lanczos estimate, so it is reported beside `e2e`, not as it.
 `roofline`: the dominant kernel (first kernel of a step of the device-resident
 residual-Lanczos chain: fused update + [V AV B]'w) timed alone with CUDA events
 at the workload's row count.
@@ -400,6 +404,31 @@ def run_b200(args):
     h2d_total = allreduce_max(dist, float(h2d)) * world
     d2h_total = allreduce_max(dist, float(d2h)) * world
 
+    # ---- leg 3: the same end-to-end solve with "Residual method" = 2 (exact
+    #      residual eigenpairs from the tall-skinny QR of [B, V, AV, MV] and the
+    #      whole iteration in the coordinates of that basis, BASELINE.json
+    #      north_star item (3)).  Reported beside `e2e`, never instead of it: the
+    #      iterates are not the reference's Lanczos iterates. --------------------
+    p2 = dict(params)
+    p2["Residual method"] = 2
+    api.solve(rp, ci, v, n_b, p2, B=B, global_rows=m, row_offset=r0, v_cap_cols=cap, M=M)   # untimed
+    lib.rails_cuda_sync()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.time()
+    e2e2 = api.solve(rp, ci, v, n_b, p2, B=B, global_rows=m, row_offset=r0, v_cap_cols=cap, M=M)
+    lib.rails_cuda_sync()
+    if dist is not None:
+        dist.barrier()
+    wall2 = allreduce_max(dist, time.time() - t0)
+    x_diff = None
+    if world == 1 and "V" in e2e and "V" in e2e2:
+        V1, T1, V2, T2 = e2e["V"], e2e["T"], e2e2["V"], e2e2["T"]
+        G11, G22, G12 = V1.T @ V1, V2.T @ V2, V1.T @ V2
+        n1 = np.trace(T1 @ G11 @ T1.T @ G11)
+        n2 = np.trace(T2 @ G22 @ T2.T @ G22)
+        x_diff = float(np.sqrt(max(n1 - 2 * np.trace(T1 @ G12 @ T2.T @ G12.T) + n2, 0.0) / n1))
+
     kernels = None
     if not args.no_kernels:
         kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps)
@@ -463,6 +492,15 @@ def run_b200(args):
                 "setup_seconds": e2e["setup_seconds"], "solve_seconds": e2e["solve_seconds"],
                 "what": "rails_host_solve to tolerance 1e-4 with host CSR/B(/M) in, V/T out; "
                         "%d iterations in %.3f s" % (e2e["iterations"], wall)},
+        "e2e_tsqr": {"value": e2e2["iterations"] / wall2, "unit": "iterations/s",
+                     "time_to_tolerance_s": wall2, "iterations_to_tolerance": int(e2e2["iterations"]),
+                     "converged": e2e2["ret"] == 0, "space_size": int(e2e2["k"]),
+                     "setup_seconds": e2e2["setup_seconds"], "solve_seconds": e2e2["solve_seconds"],
+                     "final_relative_residual": float(e2e2["rel"][-1]),
+                     "x_rel_diff_vs_e2e": x_diff,
+                     "what": "the e2e solve with \"Residual method\" = 2: exact residual eigenpairs "
+                             "from the tall-skinny QR of [B, V, AV, MV], iteration carried out on the "
+                             "R factors; same tolerance, host buffers in and out"},
         "gpu_launches": int(res["timed_launches"]),
         "clocks": clocks,
         "roofline": roofline,

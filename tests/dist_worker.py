@@ -146,6 +146,43 @@ def main():
             assert dx < 1e-6, dx
             print("%s g=%d on %d GPUs: %d iterations, history diff %.1e, |dX|/|X| %.1e"
                   % (kind, g, world, d["iterations"], np.max(rel), dx), flush=True)
+    # 4. "Residual method" = 1 / 2 and the MATLAB-only options on row blocks,
+    #    against the numpy restatement of RAILSsolver.m on the global problem
+    #    (same cases and bar as tests/test_gpu_matlab_features.py)
+    import test_matlab_features as mf
+    for name, method in [("expand1", 1), ("expand1", 2), ("mass", 2), ("relative_cut", 2),
+                         ("m_orthogonal", 1), ("nullspace", 1)]:
+        p = mf.setup()
+        mopts, popts, uses_m, V0, N = mf.cases(p)[name]
+        if N is not None:
+            mf.project_out(p, N)
+        m = p["n"]
+        r0, r1 = problems.partition_rows(m, world, rank)
+        rpg, cig, vg = p["csr"]
+        rp = (rpg[r0:r1 + 1] - rpg[r0]).astype(np.int32)
+        ci = cig[rpg[r0]:rpg[r1]].copy()
+        v = vg[rpg[r0]:rpg[r1]].copy()
+        P = dict(mf.BASE)
+        P.update(popts)
+        P["Residual method"] = method
+        Mc = None
+        if uses_m:
+            dm = np.ascontiguousarray(np.diag(p["M"])[r0:r1])
+            Mc = (np.arange(r1 - r0 + 1, dtype=np.int32), np.arange(r0, r1, dtype=np.int32), dm)
+        q = api.solve(rp, ci, v, p["B"].shape[1], P, B=np.asfortranarray(p["B"][r0:r1]), global_rows=m,
+                      row_offset=r0, v_cap_cols=m, V0=np.asfortranarray(V0[r0:r1]), M=Mc,
+                      nullspace=None if N is None else np.asfortranarray(N[r0:r1]))
+        V = gather_rows(q["V"])
+        if rank == 0:
+            o = mf.run_oracle(p, mopts, uses_m, V0, N)
+            assert q["ret"] == (0 if o["res"] < mf.TOL else -1), (name, method, q["ret"])
+            restarted = np.zeros(q["iterations"], dtype=np.int32)
+            restarted[:-1] = np.diff(q["space"]) <= 0
+            q["restarted"] = restarted
+            q["V"] = V
+            mf.compare(o, q, m)
+            print("%s method %d on %d GPUs: %d iterations, same path as the MATLAB restatement"
+                  % (name, method, world, q["iterations"]), flush=True)
     dist.barrier()
     if rank == 0:
         print("DIST_OK", flush=True)

@@ -39,6 +39,8 @@ extern "C" {
 
 typedef struct rails_mv_s *rails_mv_t;
 typedef struct rails_csr_s *rails_csr_t;
+typedef struct rails_lu_s *rails_lu_t;
+typedef struct rails_idx_s *rails_idx_t;
 
 enum {
     RAILS_OK = 0,
@@ -237,6 +239,45 @@ int rails_csr_spmm(rails_csr_t A, int trans, rails_mv_t X, int xc0, int ncols,
 /* sqrt(lambda_max(A'A)) by power iteration on the device (EpetraOp::norm
  * :115-145; reached only when B is an Operator) */
 int rails_csr_norm2(rails_csr_t A, double *out);
+
+/* ---- sparse LU solves: the `A11 \ x` inside every apply of the reference's
+ *      Schur-complement operator for a singular mass matrix
+ *      (src/SchurOperator.cpp:177-186 factorise with Amesos_Klu, :204-208,
+ *      :252-256,:262-266 solve; matlab/RAILSschur.m:31-36 lu() and the two
+ *      solve closures) and the `A \ x` behind the inverse projection methods
+ *      (matlab/RAILSschur.m:60-66, RAILSsolver.m:294-298,520-524).
+ *      The factors P A Q = L U are computed once on the host (as KLU's are):
+ *      L unit lower triangular with only its strict part stored, U upper
+ *      triangular with its diagonal, both column-compressed in pivot numbering;
+ *      pinv[i] = pivot position of row i, q[j] = column eliminated at step j.
+ *      They are kept in HBM with a level schedule per triangle; a solve is a few
+ *      launches whatever the number of levels.  Single rank only (the reference
+ *      solver is serial too). ------------------------------------------------- */
+int rails_lu_create(int n, const int *Lp, const int *Li, const double *Lx,
+                    const int *Up, const int *Ui, const double *Ux,
+                    const int *pinv, const int *q, rails_lu_t *out);
+int rails_lu_free(rails_lu_t F);
+/* X[:, xc0..xc0+nc) = op(A)^-1 B[:, bc0..bc0+nc);  trans != 0: A'.  X may be B. */
+int rails_lu_solve(rails_lu_t F, int trans, rails_mv_t B, int bc0, int nc,
+                   rails_mv_t X, int xc0);
+/* stored entries of L + U (unit diagonal of L not counted) */
+long long rails_lu_nnz(rails_lu_t F);
+/* levels of the schedule of triangle `which` (0: L, 1: U, 2: U', 3: L') and the
+ * kernels one solve launches */
+int rails_lu_levels(rails_lu_t F, int which);
+int rails_lu_launches_per_solve(rails_lu_t F, int trans);
+
+/* ---- row index lists: the idx1 / idx2 splitting of the Schur complement
+ *      (Epetra_Import between the maps of src/SchurOperator.cpp:93-94,131-132,
+ *      228-238,280-286; x(idx2, :) and Xreorder of matlab/RAILSschur.m:52-60) --- */
+int rails_idx_create(long long n, const int *host_idx, rails_idx_t *out);
+int rails_idx_free(rails_idx_t I);
+/* dst[i, :] = scale * src[idx[i], :]        (dst has n rows) */
+int rails_mv_gather_rows(rails_mv_t dst, int dc0, rails_mv_t src, int sc0, int nc,
+                         rails_idx_t I, double scale);
+/* dst[idx[i], :] = scale * src[i, :]; the other rows of dst are left alone */
+int rails_mv_scatter_rows(rails_mv_t dst, int dc0, rails_mv_t src, int sc0, int nc,
+                          rails_idx_t I, double scale);
 
 #ifdef __cplusplus
 }

@@ -21,7 +21,9 @@ Deliberate restatement choices (each marked below):
     is random, so no MATLAB run is reproducible beyond that anyway.
   * `lyap` (matlab/mex/lyap.c:95-150: SLICOT sb03md / sg03ad) is scipy's
     Bartels-Stewart solver; the generalised equation is reduced with E^-1.
-  * projection_method is 1 (no A^-1 variants: SURVEY.md §8(f) N4).
+  * A may be a matrix or a function handle (RAILSsolver.m:262-270: `A(x)`), as
+    RAILSschur returns one; opts['projection_method'] and opts['Ainv'] follow
+    :7-24,280-308,520-524.
 """
 import numpy as np
 import scipy.linalg
@@ -116,7 +118,12 @@ def rails_solver(A, M, B, maxit=100, tol=1e-4, opts=None, V0=None):
     random start vector of :277-280.  Returns a dict: V, T, res, iter, resvec,
     space (columns of V when each residual was estimated)."""
     opts = dict(opts or {})
-    m = A.shape[0]
+    m = B.shape[0]
+    if callable(A):                                            # :262-270 function handle
+        A_apply = A
+    else:
+        A_mat = A
+        A_apply = lambda x: A_mat @ x
     has_m = M is not None
     restart_size = opts.get("restart_size", -1)                # :118-131 defaults
     restart_iterations = opts.get("restart_iterations", -1)
@@ -138,10 +145,27 @@ def rails_solver(A, M, B, maxit=100, tol=1e-4, opts=None, V0=None):
     if opts.get("nullspace", None) is not None:                # :218-220
         nullspace = morth(np.asarray(opts["nullspace"], dtype=float), None)
 
+    projection_method = opts.get("projection_method", 1)       # :131,224-226
+    invA = opts.get("Ainv", opts.get("invA", None))            # :155-160
+    if invA is None:
+        invA = lambda x: np.linalg.solve(A_mat, x)             # :284-286
+    frac = projection_method - np.floor(projection_method)
+    eps = np.sqrt(np.finfo(float).eps)
+
     V = opts.get("space", V0)
     if V is None:
         V = (np.random.rand(m, 1) - 0.5) * 2                   # :277-280
     V = np.array(V, dtype=float).reshape(m, -1)
+    W = V
+    if abs(frac - 0.1) < eps:                                  # :294-296
+        W = invA(V)
+    if abs(frac - 0.2) < eps:                                  # :297-300
+        V = np.array(B, dtype=float)
+        W = invA(V)
+    if np.floor(projection_method) == 2 and abs(frac - 0.3) > eps:     # :302-307
+        V = np.hstack([V, W])
+    elif np.floor(projection_method) == 1 and abs(frac - 0.3) > eps:
+        V = W
     if mortho:                                                 # :303-307
         V = morth(V, M, nullspace, None, fast)
     elif ortho:
@@ -165,7 +189,7 @@ def rails_solver(A, M, B, maxit=100, tol=1e-4, opts=None, V0=None):
         iter_since_restart += 1
         k_old = VAV.shape[1]
         new = slice(k_old, V.shape[1])
-        AVnew = A @ V[:, new]                                  # :346-353
+        AVnew = A_apply(V[:, new])                             # :346-353
         VAV = V.T @ AVnew if k_old == 0 else np.block([[VAV], [V[:, new].T @ AV]])
         if k_old > 0:
             VAV = np.hstack([VAV, V.T @ AVnew])
@@ -235,6 +259,10 @@ def rails_solver(A, M, B, maxit=100, tol=1e-4, opts=None, V0=None):
 
         num = min(expand, V2.shape[1], m - V.shape[1])         # :517
         W = V2[:, :num]
+        if 1 < projection_method < 2:                          # :520-524
+            W = invA(W)
+        elif 2 < projection_method < 3:
+            W = np.hstack([W, invA(W)])
         V = morth(W, M if mortho else None, nullspace, V, fast)   # :527-531
 
     return dict(V=V, T=T, res=res, iter=it, resvec=np.array(resvec), space=np.array(space))

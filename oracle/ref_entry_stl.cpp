@@ -197,6 +197,14 @@ extern "C" int b200loop_stl_solve(
     return ret;
 }
 
+// Dense A^-1 handed to the NEXT b200loop_stl_solve_ext call (opts.Ainv of
+// matlab/RAILSsolver.m:19-24; "Projection method" > 1)
+static std::vector<double> g_pending_inverse;
+extern "C" void b200loop_stl_set_inverse(int m, const double *Ainv)
+{
+    g_pending_inverse.assign(Ainv, Ainv + (size_t)m * m);
+}
+
 // The product loop over StlWrapper with everything the MATLAB-feature options
 // need (tests/test_matlab_features.py): a dense mass matrix, a warm-start
 // basis V0 and a null space.  M_in / V0 / N_in may be NULL.
@@ -233,6 +241,15 @@ extern "C" int b200loop_stl_solve_ext(
     if (ret)
         return 100 + ret;
     solver.set_verbose(false);
+    if (g_pending_inverse.size() == (size_t)m * m)
+    {
+        StlWrapper Ainv(m, m);
+        for (int j = 0; j < m; ++j)
+            for (int i = 0; i < m; ++i)
+                Ainv(i, j) = g_pending_inverse[i + (size_t)j * m];
+        solver.set_inverse(Ainv);
+    }
+    g_pending_inverse.clear();
     if (n_null > 0 && N_in)
     {
         StlWrapper N(m, n_null);
@@ -262,7 +279,7 @@ extern "C" int b200loop_stl_solve_ext(
     int k = V.N();
     if (k_out)
         *k_out = k;
-    if (V_out && T_out && k <= v_cap_cols)
+    if (V_out && T_out && k <= v_cap_cols && T.M() >= k && T.N() >= k)
     {
         for (int j = 0; j < k; ++j)
             for (int i = 0; i < m; ++i)

@@ -52,6 +52,8 @@ def host():
         lib = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
         lib.rails_host_last_sections.restype = ctypes.c_char_p
         lib.rails_host_last_timed_launches.restype = ctypes.c_longlong
+        lib.rails_host_lu_factor.restype = ctypes.c_void_p
+        lib.rails_host_schur_create.restype = ctypes.c_void_p
         _host = lib
     return _host
 
@@ -116,6 +118,17 @@ CUDA_SYMBOLS = [
     ("rails_csr_nnz", LL, [P]),
     ("rails_csr_spmm", I, [P, I, P, I, I, P, I]),
     ("rails_csr_norm2", I, [P, c_double_p]),
+    ("rails_lu_create", I, [I, c_int_p, c_int_p, c_double_p, c_int_p, c_int_p, c_double_p, c_int_p, c_int_p,
+                            ctypes.POINTER(P)]),
+    ("rails_lu_free", I, [P]),
+    ("rails_lu_solve", I, [P, I, P, I, I, P, I]),
+    ("rails_lu_nnz", LL, [P]),
+    ("rails_lu_levels", I, [P, I]),
+    ("rails_lu_launches_per_solve", I, [P, I]),
+    ("rails_idx_create", I, [LL, c_int_p, ctypes.POINTER(P)]),
+    ("rails_idx_free", I, [P]),
+    ("rails_mv_gather_rows", I, [P, I, P, I, I, P, D]),
+    ("rails_mv_scatter_rows", I, [P, I, P, I, I, P, D]),
 ]
 
 
@@ -314,3 +327,166 @@ def solution_eigs(V, T, num=10, tol=1e-6, global_rows=None):
     if rc:
         raise RailsError("rails_host_solution_eigs failed (%d): %s" % (rc, _host_message()))
     return lam[:found.value].copy(), Q[:, :found.value].copy(), trace.value
+
+
+# ---- singular mass matrix: host sparse LU, Schur-complement operator -------------
+def _csr32(rowptr, colidx, vals):
+    return (np.ascontiguousarray(rowptr, dtype=np.int32), np.ascontiguousarray(colidx, dtype=np.int32),
+            np.ascontiguousarray(vals, dtype=np.float64))
+
+
+class SparseLU:
+    """Host factorisation P A Q = L U (rails_b200/host/SparseLU.cpp).  solve()
+    is host arithmetic (factorisation checks); device_solve() uploads the factors
+    and solves on the GPU (rails_lu_create / rails_lu_solve)."""
+
+    def __init__(self, rowptr, colidx, vals, pivot_threshold=0.1, order=None):
+        rp, ci, v = _csr32(rowptr, colidx, vals)
+        self.n = rp.size - 1
+        info = ctypes.c_int(0)
+        o = None if order is None else np.ascontiguousarray(order, dtype=np.int32)
+        self.h = ctypes.c_void_p(host().rails_host_lu_factor(
+            ctypes.c_int(self.n), iptr(rp), iptr(ci), dptr(v), ctypes.c_double(pivot_threshold), iptr(o),
+            ctypes.byref(info)))
+        self.info = info.value
+        out, piv = (ctypes.c_longlong * 3)(), (ctypes.c_double * 2)()
+        host().rails_host_lu_info(self.h, out, piv)
+        self.nnz_l, self.nnz_u, self.off_diagonal_pivots = int(out[0]), int(out[1]), int(out[2])
+        self.min_pivot, self.max_pivot = piv[0], piv[1]
+
+    def permutations(self):
+        pinv, q = np.zeros(self.n, dtype=np.int32), np.zeros(self.n, dtype=np.int32)
+        host().rails_host_lu_permutations(self.h, iptr(pinv), iptr(q))
+        return pinv, q
+
+    def solve(self, b, trans=False):
+        x = np.asfortranarray(np.array(b, dtype=np.float64).reshape(self.n, -1, order="F"))
+        host().rails_host_lu_solve(self.h, dptr(x), ctypes.c_int(x.shape[1]), ctypes.c_longlong(self.n),
+                                   ctypes.c_int(1 if trans else 0))
+        return x
+
+    def device_solve(self, b, trans=False, repeat=0):
+        x = np.asfortranarray(np.array(b, dtype=np.float64).reshape(self.n, -1, order="F"))
+        ms, stats = ctypes.c_float(0), (ctypes.c_longlong * 6)()
+        rc = host().rails_host_lu_device_solve(self.h, ctypes.c_int(1 if trans else 0), dptr(x),
+                                               ctypes.c_int(x.shape[1]), ctypes.c_longlong(self.n),
+                                               ctypes.c_int(repeat), ctypes.byref(ms), stats)
+        if rc:
+            raise RailsError("rails_host_lu_device_solve failed (%d): %s"
+                             % (rc, cuda().rails_cuda_last_error().decode()))
+        self.device_stats = dict(nnz=int(stats[0]), levels=[int(stats[i]) for i in range(1, 5)],
+                                 launches_per_solve=int(stats[5]), ms_per_solve=ms.value)
+        return x
+
+    def __del__(self):
+        try:
+            host().rails_host_lu_free(self.h)
+        except Exception:
+            pass
+
+
+def minimum_degree(rowptr, colidx):
+    rp = np.ascontiguousarray(rowptr, dtype=np.int32)
+    ci = np.ascontiguousarray(colidx, dtype=np.int32)
+    order = np.zeros(rp.size - 1, dtype=np.int32)
+    host().rails_host_minimum_degree(ctypes.c_int(rp.size - 1), iptr(rp), iptr(ci), iptr(order))
+    return order
+
+
+class SchurOperator:
+    """The Schur-complement operator on the GPU (rails_b200/host/CudaSchurOperator.cpp)
+    for parity tests of its pieces: S, S', S^-1, restrict, prolongate."""
+
+    S, ST, SINV, RESTRICT, PROLONGATE = 0, 1, 2, 3, 4
+
+    def __init__(self, rowptr, colidx, vals, mdiag, border=None, zero_tolerance=1e-12, scale=1.0):
+        rp, ci, v = _csr32(rowptr, colidx, vals)
+        md = np.ascontiguousarray(mdiag, dtype=np.float64)
+        bd = None if border is None else np.asfortranarray(border, dtype=np.float64)
+        info = ctypes.c_int(0)
+        self.h = ctypes.c_void_p(host().rails_host_schur_create(
+            ctypes.c_int(rp.size - 1), iptr(rp), iptr(ci), dptr(v), dptr(md),
+            ctypes.c_int(0 if bd is None else bd.shape[1]), dptr(bd), ctypes.c_double(zero_tolerance),
+            ctypes.c_double(scale), ctypes.byref(info)))
+        if info.value or not self.h:
+            raise RailsError("rails_host_schur_create failed (%d): %s"
+                             % (info.value, cuda().rails_cuda_last_error().decode()))
+        nt, n1, n2 = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+        host().rails_host_schur_sizes(self.h, ctypes.byref(nt), ctypes.byref(n1), ctypes.byref(n2))
+        self.n_total, self.n1, self.n2 = nt.value, n1.value, n2.value
+        self.idx1, self.idx2 = np.zeros(self.n1, dtype=np.int32), np.zeros(self.n2, dtype=np.int32)
+        host().rails_host_schur_indices(self.h, iptr(self.idx1), iptr(self.idx2))
+
+    def apply(self, what, X, repeat=0):
+        rows_in = self.n_total if what == self.RESTRICT else self.n2
+        rows_out = self.n_total if what == self.PROLONGATE else self.n2
+        X = np.asfortranarray(np.array(X, dtype=np.float64).reshape(rows_in, -1, order="F"))
+        Y = np.zeros((rows_out, X.shape[1]), order="F")
+        ms = ctypes.c_float(0)
+        rc = host().rails_host_schur_apply(self.h, ctypes.c_int(what), dptr(X), ctypes.c_int(X.shape[1]),
+                                           dptr(Y), ctypes.c_int(repeat), ctypes.byref(ms))
+        if rc:
+            raise RailsError("rails_host_schur_apply failed (%d): %s"
+                             % (rc, cuda().rails_cuda_last_error().decode()))
+        self.ms_per_apply = ms.value
+        return Y
+
+    def stats(self):
+        st, fs = (ctypes.c_longlong * 6)(), ctypes.c_double(0)
+        host().rails_host_schur_stats(self.h, st, ctypes.byref(fs))
+        return dict(factor_nnz=int(st[0]), levels_l=int(st[1]), levels_u=int(st[2]),
+                    launches_per_solve=int(st[3]), off_diagonal_pivots=int(st[4]), mvps=int(st[5]),
+                    factor_seconds=fs.value)
+
+    def free(self):
+        if self.h:
+            host().rails_host_schur_free(self.h)
+            self.h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def solve_schur(rowptr, colidx, vals, mdiag, B, params, border=None, seed=1, v_cap_cols=400,
+                hist_cap=4096):
+    """rails_host_solve_schur: A X M' + M X A' + B B' = 0 with a singular diagonal
+    M through the Schur complement.  Returns a dict with V (full rows, prolongated,
+    border rows included), V_reduced, T, the history and the set-up facts."""
+    lib = host()
+    rp, ci, v = _csr32(rowptr, colidx, vals)
+    n = rp.size - 1
+    md = np.ascontiguousarray(mdiag, dtype=np.float64)
+    Bc = np.asfortranarray(np.array(B, dtype=np.float64).reshape(n, -1, order="F"))
+    bd = None if border is None else np.asfortranarray(border, dtype=np.float64)
+    nb = 0 if bd is None else bd.shape[1]
+    keys = [k.encode() for k in params]
+    karr = (ctypes.c_char_p * len(keys))(*keys)
+    pv = np.array([float(x) for x in params.values()], dtype=np.float64)
+    ha, hr = np.zeros(hist_cap), np.zeros(hist_cap)
+    hk = np.zeros(hist_cap, dtype=np.int32)
+    hl, k = ctypes.c_int(0), ctypes.c_int(0)
+    n2_max = int(np.sum(np.abs(md) >= params.get("Schur zero tolerance", 1e-12)))
+    Vf = np.zeros((n + nb, v_cap_cols), order="F")
+    Vr = np.zeros((max(n2_max, 1), v_cap_cols), order="F")
+    T = np.zeros((v_cap_cols, v_cap_cols), order="F")
+    sizes, stats, secs = (ctypes.c_int * 2)(), (ctypes.c_longlong * 6)(), (ctypes.c_double * 2)()
+    ret = lib.rails_host_solve_schur(
+        ctypes.c_int(n), iptr(rp), iptr(ci), dptr(v), dptr(md), ctypes.c_int(nb), dptr(bd),
+        ctypes.c_int(Bc.shape[1]), dptr(Bc), ctypes.c_uint(seed), ctypes.c_int(len(keys)), karr, dptr(pv),
+        ctypes.c_int(hist_cap), dptr(ha), dptr(hr), iptr(hk), ctypes.byref(hl), ctypes.byref(k),
+        ctypes.c_int(v_cap_cols), dptr(Vf), dptr(Vr), dptr(T), sizes, stats, secs)
+    m = min(hl.value, hist_cap)
+    out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:m].copy(), rel=hr[:m].copy(),
+               space=hk[:m].copy(), n1=sizes[0], n2=sizes[1], setup_seconds=secs[0],
+               solve_seconds=secs[1],
+               stats=dict(factor_nnz=int(stats[0]), levels_l=int(stats[1]), levels_u=int(stats[2]),
+                          launches_per_solve=int(stats[3]), off_diagonal_pivots=int(stats[4]),
+                          mvps=int(stats[5])))
+    if 0 < k.value <= v_cap_cols:
+        out["V"] = Vf[:, :k.value]
+        out["V_reduced"] = Vr[:sizes[1], :k.value]
+        out["T"] = T[:k.value, :k.value]
+    return out

@@ -36,6 +36,11 @@ CudaOperatorWrapper::CudaOperatorWrapper(int m, int n, const int *rowptr, const 
     : CudaOperatorWrapper(m, m, n, 0, rowptr, colidx, vals)
 {}
 
+CudaOperatorWrapper::CudaOperatorWrapper(std::shared_ptr<const Action> const &action)
+    : action_(action), m_(action ? action->rows() : -1), n_(action ? action->cols() : -1),
+      transpose_(false)
+{}
+
 CudaOperatorWrapper CudaOperatorWrapper::transpose() const
 {
     // flag on a shallow copy (src/Epetra_OperatorWrapper.cpp:50-55)
@@ -48,6 +53,16 @@ CudaMultiVectorWrapper CudaOperatorWrapper::operator*(CudaMultiVectorWrapper con
 {
     // result lives on the operator's range map with other.N() columns
     // (src/Epetra_OperatorWrapper.cpp:75-91)
+    if (action_)
+    {
+        if (other.M() != N() || other.transpose_)
+        {
+            std::cerr << "Incomplatible sizes: operator " << M() << "x" << N() << " times "
+                      << other.M() << "x" << other.N() << std::endl;
+            return CudaMultiVectorWrapper(M(), other.N());
+        }
+        return action_->apply(other, transpose_);
+    }
     other.materialize();
     CudaMultiVectorWrapper out;
     out.allocate(M(), other.N(), other.replicated_ && rails_cuda_comm_size() == 1);
@@ -68,6 +83,8 @@ double CudaOperatorWrapper::norm() const
     double out = 0.0;
     if (ptr_)
         check(rails_csr_norm2(ptr_->h, &out), "norm");
+    else if (action_)
+        std::cerr << "CudaOperatorWrapper::norm is not available for a composite operator" << std::endl;
     return out;
 }
 

@@ -19,6 +19,20 @@ namespace RAILS
 
 class CudaOperatorWrapper
 {
+public:
+    // An operator that is not one CSR matrix: the Schur complement
+    // A22 - A21 A11^-1 A12 and its inverse (CudaSchurOperator.hpp).  The
+    // reference wraps any Epetra_Operator the same way -- its SchurOperator is
+    // handed to the solver through Epetra_OperatorWrapper (src/main.cpp:90-98).
+    struct Action
+    {
+        virtual ~Action() {}
+        virtual CudaMultiVectorWrapper apply(CudaMultiVectorWrapper const &x, bool transpose) const = 0;
+        virtual int rows() const = 0;
+        virtual int cols() const = 0;
+    };
+
+private:
     struct Handle
     {
         rails_csr_t h;
@@ -28,6 +42,7 @@ class CudaOperatorWrapper
         Handle &operator=(Handle const &) = delete;
     };
     std::shared_ptr<Handle> ptr_;
+    std::shared_ptr<const Action> action_;
     int m_, n_;          // GLOBAL sizes
     bool transpose_;
 
@@ -40,6 +55,10 @@ public:
                         const int *rowptr, const int *colidx, const double *vals);
     // convenience: whole matrix on one rank
     CudaOperatorWrapper(int m, int n, const int *rowptr, const int *colidx, const double *vals);
+    // composite operator (implicit, like the reference's conversion from
+    // Teuchos::RCP<Epetra_Operator>, src/Epetra_OperatorWrapper.hpp)
+    CudaOperatorWrapper(std::shared_ptr<const Action> const &action);
+    bool valid() const { return ptr_ || action_; }
 
     virtual ~CudaOperatorWrapper() {}
 

@@ -153,6 +153,7 @@ public:
           restart_from_solution_(false), use_mass_(false), residual_method_(0),
           m_orthogonalization_(false), relative_restart_tolerance_(false), restart_upon_start_(false),
           orthogonalize_candidates_(false), lanczos_vectors_(-1), has_nullspace_(false),
+          projection_method_(1.0), has_inverse_(false),
           verbose_(true)
     {}
 
@@ -230,6 +231,15 @@ public:
     // is one V'w + one V*c kernel instead of k dependent axpys.  Returns the
     // number of columns appended.
     int morth(MultiVector const &W, MultiVector const *against, MultiVector &V);
+    // opts.Ainv / opts.invA (:19-24,155-160): an operator that applies A^-1,
+    // possibly approximately.  Only read when "Projection method" > 1 (:7-17):
+    //   1.x  the space is expanded with A^-1 r instead of the residual vectors r,
+    //   2.x  with [r, A^-1 r] (the extended Krylov flavour);
+    //   x.1  start from A^-1 V0, x.2 from B (and A^-1 B), x.3 from V0 alone
+    // (:294-308,520-524).  For a singular mass matrix the reference pairs this
+    // with the Schur-complement operator and its Sinv (matlab/RAILSschur.m:60-66,
+    // matlab/test/test_MOC.m:45-49).
+    void set_inverse(Matrix const &Ainv) { Ainv_ = Ainv; has_inverse_ = true; }
 
     // ---- additions ------------------------------------------------------
     void set_observer(Observer obs) { observer_ = obs; }
@@ -269,6 +279,9 @@ protected:
     int lanczos_vectors_;             // opts.lanczos_vectors: candidates kept (:72-77,309-311)
     bool has_nullspace_;
     MultiVector nullspace_;
+    double projection_method_;        // opts.projection_method  (:7-17,294-308,520-524)
+    bool has_inverse_;
+    Matrix Ainv_;
     bool verbose_;
 
     Observer observer_;
@@ -353,6 +366,13 @@ int Solver<Matrix, MultiVector, DenseMatrix>::set_parameters(ParameterList &para
     orthogonalize_candidates_ = lookup_parameter(params, "Orthogonalize candidates",
                                                  orthogonalize_candidates_);
     lanczos_vectors_ = lookup_parameter(params, "Lanczos vectors", lanczos_vectors_);
+    projection_method_ = lookup_parameter(params, "Projection method", projection_method_);
+    if (projection_method_ < 1.0 || projection_method_ >= 3.0)
+    {
+        std::cerr << "Projection method " << projection_method_ << " does not exist "
+                  << "(1, 1.1, 1.2, 1.3, 2.1, 2.2, 2.3)" << std::endl;
+        return 1;
+    }
     if (m_orthogonalization_)
         use_mass_ = true;          // V'MV = I: the residual still needs MV (:391)
 

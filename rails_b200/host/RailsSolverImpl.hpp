@@ -209,7 +209,31 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         }
         std::cerr << std::endl;
     };
-    if (residual_method_ == 2 && B_.is_multivector() && !m_orthogonalization_ && !has_nullspace_)
+    // opts.projection_method (matlab/RAILSsolver.m:7-17): which of the A^-1 variants
+    const double pm_fraction = projection_method_ - std::floor(projection_method_);
+    const bool pm_inverse = projection_method_ > 1.0 + 1e-8;
+    const bool pm_extended = pm_inverse && std::floor(projection_method_) == 2.0;   // [r, A^-1 r]
+    const bool pm_start_1 = std::abs(pm_fraction - 0.1) < 1e-8;
+    const bool pm_start_2 = std::abs(pm_fraction - 0.2) < 1e-8;
+    const bool pm_start_3 = std::abs(pm_fraction - 0.3) < 1e-8;
+    if (pm_inverse && !has_inverse_)
+    {
+        std::cerr << "Projection method " << projection_method_
+                  << " needs an inverse operator (set_inverse)" << std::endl;
+        return 1;
+    }
+    if (!pm_inverse && has_inverse_ && verbose_)
+        std::cout << "An inverse application method is provided, but the current "
+                  << "projection method does not make use of this" << std::endl;   // :280-283
+    if (pm_start_2 && !B_.is_multivector())
+    {
+        std::cerr << "Projection method " << projection_method_
+                  << " starts from B, which must be a MultiVector" << std::endl;
+        return 1;
+    }
+
+    if (residual_method_ == 2 && B_.is_multivector() && !m_orthogonalization_ && !has_nullspace_ &&
+        !pm_inverse)
         return solve_coefficient_space(V, T);
 
     history_.clear();
@@ -217,7 +241,22 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
 
     const int n = V.M();
     int max_size = std::max(V.N(), std::min(restart_size_ > 0 ? restart_size_ : 100, n));
-    const bool custom_ortho = m_orthogonalization_ || has_nullspace_;
+    const bool custom_ortho = m_orthogonalization_ || has_nullspace_ || pm_inverse;
+
+    // W -> A^-1 W (1.x) or [W, A^-1 W] (2.x)  (matlab/RAILSsolver.m:520-524)
+    auto with_inverse = [&](MultiVector const &block) {
+        if (!pm_inverse || block.N() < 1)
+            return block.copy();
+        Section s(sections_, "Apply inverse");
+        MultiVector inv = Ainv_ * block;
+        if (!pm_extended)
+            return inv;
+        MultiVector both(block, 2 * block.N());
+        both.resize(0);
+        both.push_back(block);
+        both.push_back(inv);
+        return both;
+    };
 
     if (!restart_from_solution_)
     {
@@ -225,14 +264,16 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         V.resize(max_size);
         V.resize(1);
         V.random();
-        if (custom_ortho)
+        // with an inverse projection method the start space is orthonormalised
+        // further down, after A^-1 has been applied
+        if (custom_ortho && !pm_inverse)
         {
             // V = Morth(V, M, nullspace) (matlab/RAILSsolver.m:303-307)
             MultiVector start = V.copy();
             V.resize(0);
             morth(start, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
         }
-        else
+        else if (!pm_inverse)
             V.orthogonalize();
     }
     else if (max_size != V.N())
@@ -240,6 +281,25 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         const int have = V.N();
         V.resize(max_size);
         V.resize(have);
+    }
+
+    if (pm_inverse && (pm_start_1 || pm_start_2 || !restart_from_solution_))
+    {
+        // matlab/RAILSsolver.m:290-307: V0 = the given or random space (x.1, x.3) or
+        // B (x.2); W = A^-1 V0 (x.1, x.2); V = [V0, W] (2.1, 2.2), W (1.1, 1.2), V0 (x.3)
+        MultiVector start = pm_start_2 ? B_.multivector().copy() : V.copy();
+        if (pm_start_1 || pm_start_2)
+            start = with_inverse(start);
+        else if (!pm_start_3)
+            std::cerr << "Projection method " << projection_method_
+                      << ": unknown start variant, starting from V_0" << std::endl;
+        if (start.N() > max_size)
+        {
+            max_size = start.N();
+            V.resize(max_size);
+        }
+        V.resize(0);
+        morth(start, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
     }
 
     MultiVector W(V);                 // deep copy, as `MultiVector W = V` (:123)
@@ -401,10 +461,11 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         const int grow_by = std::min(std::min(expand_size_, ritz_values.M()), room);
 
         // capacity grows 100 columns at a time (:311-332)
-        if (V.N() + grow_by > max_size)
+        const int add_cols = pm_extended ? 2 * grow_by : grow_by;
+        if (V.N() + add_cols > max_size)
         {
             Section s(sections_, "Resize spaces");
-            max_size += 100;
+            max_size += std::max(100, add_cols);
             const int have = V.N();
 
             V.resize(max_size);
@@ -451,7 +512,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
             survivors.resize(0);
             morth(candidates, &V, survivors);
             survivors.resize(std::min(grow_by, survivors.N()));
-            appended = morth(survivors, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
+            MultiVector block = with_inverse(survivors);
+            appended = morth(block, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
         }
         else if (custom_ortho)
         {
@@ -461,7 +523,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
             block.resize(0);
             for (int i = 0; i < grow_by; i++)
                 block.push_back(ritz_vectors.view(picked[i]));
-            appended = morth(block, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
+            MultiVector expansion = with_inverse(block);
+            appended = morth(expansion, has_nullspace_ ? &nullspace_ : (MultiVector const *) nullptr, V);
         }
         else
         {

@@ -171,11 +171,15 @@ def assert_same_solve(d, o, tol, early=8, early_tol=1e-8, late_tol=1e-4, x_tol=1
 
 
 def stl_solve_ext(rowptr, colidx, vals, B, params, M=None, V0=None, nullspace=None, seed=1,
-                  v_cap_cols=300, hist_cap=4096):
+                  v_cap_cols=300, hist_cap=4096, inverse=None):
     """The PRODUCT's solver loop over the reference's StlWrapper (CPU, dense),
-    with a dense mass matrix, a warm-start basis and a null space."""
+    with a dense mass matrix, a warm-start basis, a null space and a dense A^-1
+    (for "Projection method" > 1)."""
     lib = ref()
     m = rowptr.size - 1
+    if inverse is not None:
+        inv = np.asfortranarray(inverse, dtype=np.float64)
+        lib.b200loop_stl_set_inverse(ctypes.c_int(m), dptr(inv))
     nk, karr, pv = _params(params)
     B = np.asfortranarray(B, dtype=np.float64).reshape(m, -1, order="F")
     Mc = None if M is None else np.asfortranarray(M, dtype=np.float64)

@@ -236,6 +236,34 @@ def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
     # + 8m: the squared norm of `prev` is recomputed by this entry point (in the
     # chain it is already on the device)
     rec("lanczos_project", ms, 8.0 * m * (2 * h + 1 + 5), 4)
+    # The two calls of the path that are bound by FP64 arithmetic rather than by HBM
+    # once k, r >~ 50: the restart compression V <- V X (k x r,
+    # src/LyapunovSolver.hpp:265-297) and the warm-start projection V'(AV) (k x k,
+    # :173-195).  Reported against both ceilings; the FP64 one is the nominal
+    # 37 TFLOP/s of an HGX B200 GPU (no measured FP64 peak exists on this pool).
+    FP64_NOMINAL_TFLOPS = 37.0
+    r = max(k // 2, 1)
+    Out = api.MultiVector(rows, r)
+    Xc = np.asfortranarray(np.random.RandomState(3).uniform(-1, 1, (k, r)) * 1e-2)
+    G = np.zeros((k, k), order="F")
+
+    def rec_flops(name, fn, nbytes, flops):
+        l0 = lib.rails_cuda_kernel_launches()
+        fn()
+        launches = int(lib.rails_cuda_kernel_launches() - l0)
+        ms = timed(fn, reps=4, warm=1)
+        rec(name, ms, nbytes, launches)
+        out[name].update({"flops": flops, "tflops": flops / ms / 1e9,
+                          "frac_of_fp64_nominal": flops / ms / 1e9 / FP64_NOMINAL_TFLOPS,
+                          "fp64_nominal_tflops": FP64_NOMINAL_TFLOPS})
+
+    rec_flops("gemm_kxr_restart",
+              lambda: api.check(lib.rails_mv_gemm(V.h, 0, k, api.dptr(Xc), k, r, 1.0, 0.0, Out.h, 0), "gemm"),
+              8.0 * m * (k + r), 2.0 * m * k * r)
+    rec_flops("dot_kxk_projection",
+              lambda: api.check(lib.rails_mv_dot(V.h, 0, k, V.h, 0, k, api.dptr(G), k), "dot"),
+              8.0 * m * k, 2.0 * m * k * k)
+    Out.free()
     for o in out.values():
         o["k"] = k
     V.free(); q.free(); small.free()

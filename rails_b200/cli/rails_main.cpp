@@ -8,11 +8,16 @@
 // write V.mtx and T.mtx, print the dominant eigenvalues of X next to their
 // share of trace(X), and dump the timing profile.  Differences, all forced by
 // what is in scope:
-//   * the operator is A itself, not the Schur complement of a singular-M
-//     system (SchurOperator, N4): an M with zero diagonal rows is refused with
-//     a message instead of being reduced;
-//   * a non-identity M selects the generalised branch ("Use mass matrix",
-//     matlab/RAILSsolver.m:368-392), an identity or absent M the standard one;
+//   * the reference always solves on the Schur complement of the rows where M is
+//     zero (src/main.cpp:75-98).  Here that reduction (CudaSchurOperator, one
+//     GPU) is used when M has zero diagonal rows and A itself otherwise; V.mtx
+//     then holds the PROLONGATED basis (all m rows), so that X = V T V' is the
+//     solution of the original equation and the eigenvalues printed are those
+//     the reference gets from SchurOperator::Apply with SetSolution;
+//   * a non-identity (reduced) M selects the generalised branch ("Use mass
+//     matrix", matlab/RAILSsolver.m:368-392), an identity or absent M the
+//     standard one; "Projection method" > 1 uses S^-1 x = (A^-1 [0; x])(idx2)
+//     as opts.Ainv (matlab/RAILSschur.m:60-66);
 //   * the eigenpairs of X come from the k x k matrix T and one V*C product
 //     (SolutionTools.hpp) instead of Anasazi;
 //   * one process drives one GPU.  Started N times with RANK / WORLD_SIZE /
@@ -26,6 +31,7 @@
 #include "CudaFusedLanczos.hpp"
 #include "CudaMultiVectorWrapper.hpp"
 #include "CudaOperatorWrapper.hpp"
+#include "CudaSchurOperator.hpp"
 #include "HostDenseMatrix.hpp"
 #include "MatrixMarket.hpp"
 #include "ParameterFile.hpp"
@@ -314,22 +320,51 @@ int main(int argc, char *argv[])
 
     ParameterTree &solver_params = params.sublist("Lyapunov Solver");
     bool mass = false;
+    bool singular = false;
     if (have_M)
     {
-        if (any_rank(io::zero_diagonal_rows(M) > 0, (int)m))
+        singular = any_rank(io::zero_diagonal_rows(M) > 0, (int)m);
+        if (singular && (nranks > 1 || opt.b_operator))
         {
             if (root)
-                std::cerr << "M has rows with a zero diagonal: a singular mass matrix needs the Schur\n"
-                             "complement reduction of the reference (SchurOperator), which this backend\n"
-                             "does not provide.  Reduce the system first and pass the reduced A, B, M."
-                          << std::endl;
+                std::cerr << "M has rows with a zero diagonal: the Schur complement reduction runs on one\n"
+                             "GPU with a dense B (no --b-operator)." << std::endl;
             return 4;
         }
-        mass = any_rank(!io::is_identity(M), (int)m);
+        mass = !singular && any_rank(!io::is_identity(M), (int)m);
+    }
+    CudaSchurOperator schur;
+    if (singular)
+    {
+        if (root)
+            std::cout << "Computing Schur complement" << std::endl;
+        auto t_schur = tick();
+        std::vector<double> mdiag((size_t)m, 0.0);
+        for (int r = 0; r < M.rows; ++r)
+            for (int e = M.rowptr[r]; e < M.rowptr[r + 1]; ++e)
+                if (M.colidx[e] == r)
+                    mdiag[r] += M.vals[e];
+        schur = CudaSchurOperator((int)m, A.rowptr.data(), A.colidx.data(), A.vals.data(), mdiag.data(),
+                                  solver_params.get("Schur zero tolerance", 1e-12),
+                                  solver_params.get("Schur scale", 1.0));
+        int src = schur.Compute();
+        if (src)
+        {
+            std::cerr << "Schur complement set-up failed (" << src << ")" << std::endl;
+            return 4;
+        }
+        mass = !schur.mass_is_identity();
+        profile["Compute Schur complement"] = since(t_schur);
+        std::cout << "Singular part: " << schur.n1() << " rows, Schur complement: " << schur.n2()
+                  << " rows, nnz(L+U) of A11: " << schur.factor_nnz() << ", levels "
+                  << schur.factor_levels(0) << "/" << schur.factor_levels(1) << ", "
+                  << schur.launches_per_solve() << " launches per solve" << std::endl;
     }
     if (mass && !solver_params.isParameter("Use mass matrix"))
         solver_params.set("Use mass matrix", true);
     mass = solver_params.get("Use mass matrix", false);
+    if (singular && !mass)
+        solver_params.set("Use mass matrix", false);
     if (mass && !have_M)
     {
         std::cerr << "\"Use mass matrix\" is set but " << opt.M << " does not exist" << std::endl;
@@ -339,12 +374,18 @@ int main(int argc, char *argv[])
     if (root)
         std::cout << "Creating solver" << std::endl;
     auto t_setup = tick();
-    CudaOperatorWrapper Aop(A.rows, (int)m, (int)m, (int)r0, A.rowptr.data(), A.colidx.data(),
-                            A.vals.data());
-    if (!Aop.device_handle())
+    CudaOperatorWrapper Aop;
+    if (singular)
+        Aop = schur.schur_operator();
+    else
+        Aop = CudaOperatorWrapper(A.rows, (int)m, (int)m, (int)r0, A.rowptr.data(), A.colidx.data(),
+                                  A.vals.data());
+    if (!Aop.valid())
         return 3;
     CudaOperatorWrapper Mop = Aop;
-    if (have_M)
+    if (singular)
+        Mop = schur.mass_operator();
+    else if (have_M)
     {
         Mop = CudaOperatorWrapper(M.rows, (int)m, (int)m, (int)r0, M.rowptr.data(), M.colidx.data(),
                                   M.vals.data());
@@ -378,6 +419,8 @@ int main(int argc, char *argv[])
             return 3;
         }
     }
+    if (singular)
+        Bmv = schur.restrict(Bmv);          // BS (matlab/RAILSschur.m:43-49)
     profile["Create operators"] = since(t_setup);
 
     CudaMultiVectorWrapper V;
@@ -401,6 +444,8 @@ int main(int argc, char *argv[])
             return 2;
         }
         V = CudaMultiVectorWrapper::from_host((int)m, vc, data.data(), m);
+        if (singular && !opt.only_eigenvalues)
+            V = schur.select_regular(V);    // the reduced basis sits in the rows idx2
         if (opt.only_eigenvalues)
         {
             int tr = 0, tc = 0;
@@ -423,7 +468,7 @@ int main(int argc, char *argv[])
         }
     }
     else
-        V = CudaMultiVectorWrapper((int)m, 1);
+        V = CudaMultiVectorWrapper(singular ? schur.n2() : (int)m, 1);
 
     if (!opt.only_eigenvalues)
     {
@@ -436,8 +481,13 @@ int main(int argc, char *argv[])
             if (prc)
                 return;
             solver.set_verbose(root && solver_params.get("Verbose", true));
+            if (singular && solver_params.get("Projection method", 1.0) > 1.0 + 1e-8)
+                solver.set_inverse(schur.inverse_operator());
             if (root)
                 std::cout << "Performing solve" << std::endl;
+            if (root && singular)
+                std::cout << "Amount of matrix-vector products before the solve: " << schur.GetMVPs()
+                          << std::endl;
             auto t_solve = tick();
             ret = solver.solve(V, T);
             rails_cuda_sync();
@@ -462,6 +512,14 @@ int main(int argc, char *argv[])
         if (root && !history.empty())
             std::cout << "Iterations: " << history.size() << ", final relative residual estimate: "
                       << history.back().relative << ", space size: " << V.N() << std::endl;
+        if (singular)
+        {
+            std::cout << "Amount of matrix-vector products after the solve: " << schur.GetMVPs() << std::endl;
+            auto t_pro = tick();
+            V = schur.prolongate(V);        // Vtrans (matlab/RAILSschur.m:68): X = V T V' on all m rows
+            rails_cuda_sync();
+            profile["Prolongate solution"] = since(t_pro);
+        }
 
         auto t_write = tick();
         if (write_distributed(join(opt.dir, opt.V), V, rank, nranks, "RAILS solution factor V", err))
@@ -551,6 +609,7 @@ int main(int argc, char *argv[])
     Bop = CudaOperatorWrapper();
     Aop = CudaOperatorWrapper();
     Mop = CudaOperatorWrapper();
+    schur = CudaSchurOperator();
     rails_cuda_finalize();
 
     // the solver's own code: 0 converged, -1 stopped unconverged, 1 fell through

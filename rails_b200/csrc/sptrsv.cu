@@ -22,6 +22,8 @@
 // algorithmic bytes per solve = 12 nnz(L + U) + 16 n c (c right-hand sides).
 #include "internal.h"
 
+#include <cuda_pipeline.h>
+
 #include <algorithm>
 
 using rails::ctx;
@@ -30,37 +32,45 @@ namespace
 {
 
 constexpr int LEVEL_THREADS = 256;         // multi-CTA level kernel: 8 warps
-constexpr int CHAIN_THREADS = 1024;        // single-CTA chain kernel: 32 warps
+constexpr int CHAIN_THREADS = 512;         // single-CTA chain kernel: 16 warps, 128 registers each
 constexpr int SMALL_LEVEL_ROWS = 128;      // levels up to this size go into a chain
+// a chain is cut into windows whose matrix data fit one shared-memory stage
+constexpr int WIN_ENTRIES = 8192;          // col (4 B) + val (8 B) per entry: 96 KB per stage
+constexpr int WIN_ROWS = 256;              // int4 descriptors: 4 KB
+constexpr int WIN_LEVELS = 64;
 
 struct Triangle
 {
     int n = 0;
     long long nnz = 0;
-    int *rowptr = nullptr;
+    // rows in level order: rowinfo[r] = {row, first entry, end, 0}; col / val
+    // hold the strict part of the rows in that same order, so a sweep streams
+    // through them front to back
+    int4 *rowinfo = nullptr;
     int *col = nullptr;
     double *val = nullptr;
-    double *diag = nullptr;                // nullptr: unit diagonal
-    int *order = nullptr;                  // rows sorted by level
+    double *diag = nullptr;                // by row; nullptr: unit diagonal
     int *lvlptr = nullptr;                 // device copy of the level offsets
+    int *winptr = nullptr;                 // chain windows: first level of window w; bit 30 set when
+                                           // the window is one level too large to stage
     int nlevels = 0;
-    struct Segment { int lvl0, lvl1, row0, row1; bool chain; };
+    struct Segment { int lvl0, lvl1, row0, row1; bool chain; int win0, win1; };
     std::vector<Segment> segments;
     size_t bytes = 0;
 };
 
 template<int CT>
-__device__ __forceinline__ void solve_row(const int *__restrict__ rowptr, const int *__restrict__ col,
+__device__ __forceinline__ void solve_row(const int4 info, const int *__restrict__ col,
                                           const double *__restrict__ val,
-                                          const double *__restrict__ diag, int row, double *X,
+                                          const double *__restrict__ diag, double *X,
                                           long long ld, int c0, int lane)
 {
     double acc[CT];
 #pragma unroll
     for (int c = 0; c < CT; ++c)
         acc[c] = 0.0;
-    const int pend = rowptr[row + 1];
-    for (int p = rowptr[row] + lane; p < pend; p += 32)
+    const int row = info.x;
+    for (int p = info.y + lane; p < info.z; p += 32)
     {
         const int j = col[p];
         const double v = val[p];
@@ -86,51 +96,253 @@ __device__ __forceinline__ void solve_row(const int *__restrict__ rowptr, const 
     }
 }
 
-__device__ __forceinline__ void solve_row_all(const int *rowptr, const int *col, const double *val,
-                                              const double *diag, int row, double *X, long long ld,
-                                              int nc, int lane)
+__device__ __forceinline__ void solve_row_all(const int4 info, const int *col, const double *val,
+                                              const double *diag, double *X, long long ld, int nc,
+                                              int lane)
 {
     int c0 = 0;
     for (; c0 + 4 <= nc; c0 += 4)
-        solve_row<4>(rowptr, col, val, diag, row, X, ld, c0, lane);
+        solve_row<4>(info, col, val, diag, X, ld, c0, lane);
     if (c0 + 2 <= nc)
     {
-        solve_row<2>(rowptr, col, val, diag, row, X, ld, c0, lane);
+        solve_row<2>(info, col, val, diag, X, ld, c0, lane);
         c0 += 2;
     }
     if (c0 < nc)
-        solve_row<1>(rowptr, col, val, diag, row, X, ld, c0, lane);
+        solve_row<1>(info, col, val, diag, X, ld, c0, lane);
 }
 
-// one level, rows order[r0 .. r1): a warp per row, grid-strided
+// one level, rows r0 .. r1 (level order): a warp per row, grid-strided
 __global__ void __launch_bounds__(LEVEL_THREADS)
-sptrsv_level_kernel(const int *__restrict__ rowptr, const int *__restrict__ col,
-                    const double *__restrict__ val, const double *__restrict__ diag,
-                    const int *__restrict__ order, int r0, int r1, double *X, long long ld, int nc)
+sptrsv_level_kernel(const int4 *__restrict__ rowinfo, const int *__restrict__ col,
+                    const double *__restrict__ val, const double *__restrict__ diag, int r0, int r1,
+                    double *X, long long ld, int nc)
 {
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * LEVEL_THREADS + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * LEVEL_THREADS) >> 5;
     for (int r = r0 + warp; r < r1; r += nwarps)
-        solve_row_all(rowptr, col, val, diag, order[r], X, ld, nc, lane);
+        solve_row_all(rowinfo[r], col, val, diag, X, ld, nc, lane);
 }
 
-// levels [l0, l1) walked by one CTA, a block barrier between levels
-__global__ void __launch_bounds__(CHAIN_THREADS)
-sptrsv_chain_kernel(const int *__restrict__ rowptr, const int *__restrict__ col,
+// A run of consecutive small levels walked by one CTA, a block barrier between
+// levels.
+//
+// These are the levels near the root of the elimination tree: few rows (often
+// one), each with hundreds of entries, every level waiting for the one before.
+// What such a level costs is a chain of memory latencies, so everything that
+// does not depend on the previous level is taken off that chain:
+//   * the run is cut (on the host) into windows of up to WIN_LEVELS levels whose
+//     row descriptors and matrix entries fit one shared-memory stage; they are
+//     contiguous in memory because the factor is stored in level order.  While
+//     the CTA works on one window, cp.async copies the next into the other
+//     stage.  Inside a window only the gather of X, a warp reduction and two
+//     barriers stand between consecutive levels;
+//   * a level with fewer than 8 rows is worked on by the whole CTA: each row
+//     gets a team of 16 / pow2(rows) warps that split its entries, the per-warp
+//     partial sums are combined in fixed order through shared memory;
+//   * a level too large for a stage is a window of its own and is read from
+//     global memory, a warp per row.
+struct WindowStage
+{
+    int lvl[WIN_LEVELS + 1];     // row offsets of the window's levels
+    int4 info[WIN_ROWS];
+    int col[WIN_ENTRIES];
+    double val[WIN_ENTRIES];
+};
+
+struct WindowShape
+{
+    int la, lb;        // levels
+    int ra, rb;        // rows (level order)
+    int ea, eb;        // entries
+    bool direct;
+};
+
+constexpr int WIN_DIRECT = 1 << 30;
+
+__device__ __forceinline__ WindowShape window_shape(const int4 *__restrict__ rowinfo,
+                                                    const int *__restrict__ lvlptr,
+                                                    const int *__restrict__ winptr, int w)
+{
+    WindowShape s;
+    const int a = winptr[w];
+    s.direct = (a & WIN_DIRECT) != 0;
+    s.la = a & ~WIN_DIRECT;
+    s.lb = winptr[w + 1] & ~WIN_DIRECT;
+    s.ra = lvlptr[s.la];
+    s.rb = lvlptr[s.lb];
+    s.ea = rowinfo[s.ra].y;
+    s.eb = rowinfo[s.rb - 1].z;
+    return s;
+}
+
+__device__ __forceinline__ void window_fetch(WindowStage &st, const WindowShape &s,
+                                             const int4 *__restrict__ rowinfo,
+                                             const int *__restrict__ col,
+                                             const double *__restrict__ val,
+                                             const int *__restrict__ lvlptr)
+{
+    if (s.direct)
+        return;
+    for (int i = threadIdx.x; i <= s.lb - s.la; i += CHAIN_THREADS)
+        __pipeline_memcpy_async(&st.lvl[i], lvlptr + s.la + i, 4);
+    for (int i = threadIdx.x; i < s.rb - s.ra; i += CHAIN_THREADS)
+        __pipeline_memcpy_async(&st.info[i], rowinfo + s.ra + i, 16);
+    for (int i = threadIdx.x; i < s.eb - s.ea; i += CHAIN_THREADS)
+    {
+        __pipeline_memcpy_async(&st.col[i], col + s.ea + i, 4);
+        __pipeline_memcpy_async(&st.val[i], val + s.ea + i, 8);
+    }
+}
+
+__global__ void __launch_bounds__(CHAIN_THREADS, 1)
+sptrsv_chain_kernel(const int4 *__restrict__ rowinfo, const int *__restrict__ col,
                     const double *__restrict__ val, const double *__restrict__ diag,
-                    const int *__restrict__ order, const int *__restrict__ lvlptr, int l0, int l1,
+                    const int *__restrict__ lvlptr, const int *__restrict__ winptr, int w0, int w1,
                     double *X, long long ld, int nc)
 {
+    extern __shared__ __align__(16) unsigned char chain_smem[];
+    WindowStage *stages = reinterpret_cast<WindowStage *>(chain_smem);
+    __shared__ double partial[CHAIN_THREADS / 32][4];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     constexpr int nwarps = CHAIN_THREADS / 32;
-    for (int l = l0; l < l1; ++l)
+
+    WindowShape shape = window_shape(rowinfo, lvlptr, winptr, w0);
+    window_fetch(stages[0], shape, rowinfo, col, val, lvlptr);
+    __pipeline_commit();
+
+    for (int w = w0; w < w1; ++w)
     {
-        const int r1 = lvlptr[l + 1];
-        for (int r = lvlptr[l] + warp; r < r1; r += nwarps)
-            solve_row_all(rowptr, col, val, diag, order[r], X, ld, nc, lane);
+        const WindowStage &st = stages[(w - w0) & 1];
+        // this window's copies have landed; everybody is done with the other stage
+        __pipeline_wait_prior(0);
         __syncthreads();
+        WindowShape ahead = shape;
+        if (w + 1 < w1)
+        {
+            ahead = window_shape(rowinfo, lvlptr, winptr, w + 1);
+            window_fetch(stages[(w + 1 - w0) & 1], ahead, rowinfo, col, val, lvlptr);
+        }
+        __pipeline_commit();
+
+        if (shape.direct)
+        {
+            for (int r = shape.ra + warp; r < shape.rb; r += nwarps)
+                solve_row_all(rowinfo[r], col, val, diag, X, ld, nc, lane);
+            __syncthreads();
+            shape = ahead;
+            continue;
+        }
+
+        for (int l = 0; l < shape.lb - shape.la; ++l)
+        {
+            const int r0 = st.lvl[l] - shape.ra;
+            const int rows = st.lvl[l + 1] - shape.ra - r0;
+            if (rows >= nwarps / 2)
+            {
+                // a warp per row, matrix data from the stage
+                for (int r = r0 + warp; r < r0 + rows; r += nwarps)
+                {
+                    const int4 info = st.info[r];
+                    for (int c0 = 0; c0 < nc; c0 += 4)
+                    {
+                        const int ct = min(4, nc - c0);
+                        double acc[4] = {0.0, 0.0, 0.0, 0.0};
+                        for (int p = info.y - shape.ea + lane; p < info.z - shape.ea; p += 32)
+                        {
+                            const int j = st.col[p];
+                            const double v = st.val[p];
+#pragma unroll
+                            for (int c = 0; c < 4; ++c)
+                                if (c < ct)
+                                    acc[c] = fma(v, __ldcg(X + j + (size_t)(c0 + c) * ld), acc[c]);
+                        }
+#pragma unroll
+                        for (int c = 0; c < 4; ++c)
+                            if (c < ct)
+                            {
+#pragma unroll
+                                for (int off = 16; off > 0; off >>= 1)
+                                    acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
+                            }
+                        if (lane < ct)
+                        {
+                            double mine = acc[0];
+                            if (lane == 1) mine = acc[1];
+                            if (lane == 2) mine = acc[2];
+                            if (lane == 3) mine = acc[3];
+                            double *x = X + info.x + (size_t)(c0 + lane) * ld;
+                            const double r = __ldcg(x) - mine;
+                            *x = diag ? r / diag[info.x] : r;
+                        }
+                    }
+                }
+                __syncthreads();
+                continue;
+            }
+
+            // team mode: 16 / pow2(rows) warps per row
+            const int shift = 4 - (rows <= 1 ? 0 : 32 - __clz(rows - 1));      // log2(warps per row)
+            const int team_warps = 1 << shift;
+            const int team = warp >> shift;
+            const int part = warp & (team_warps - 1);
+            const bool has = team < rows;
+            int4 info = make_int4(-1, 0, 0, 0);
+            if (has)
+                info = st.info[r0 + team];
+            const bool leader = has && part == 0;
+            const int stride = team_warps * 32;
+            for (int c0 = 0; c0 < nc; c0 += 4)
+            {
+                const int ct = min(4, nc - c0);
+                // right-hand side and pivot of this row: do not depend on the sweep
+                double rhs = 0.0, d = 1.0;
+                if (leader && lane < ct)
+                {
+                    rhs = __ldcg(X + info.x + (size_t)(c0 + lane) * ld);
+                    if (diag)
+                        d = diag[info.x];
+                }
+                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+                if (has)
+                    for (int p = info.y - shape.ea + part * 32 + lane; p < info.z - shape.ea; p += stride)
+                    {
+                        const int j = st.col[p];
+                        const double v = st.val[p];
+#pragma unroll
+                        for (int c = 0; c < 4; ++c)
+                            if (c < ct)
+                                acc[c] = fma(v, __ldcg(X + j + (size_t)(c0 + c) * ld), acc[c]);
+                    }
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (c < ct)
+                    {
+#pragma unroll
+                        for (int off = 16; off > 0; off >>= 1)
+                            acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
+                    }
+                if (lane == 0)
+                {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+                        partial[warp][c] = acc[c];
+                }
+                __syncthreads();
+                if (leader && lane < ct)
+                {
+                    double sum = 0.0;
+                    for (int t = 0; t < team_warps; ++t)
+                        sum += partial[warp + t][lane];
+                    const double r = rhs - sum;
+                    X[info.x + (size_t)(c0 + lane) * ld] = diag ? r / d : r;
+                }
+                __syncthreads();
+            }
+        }
+        shape = ahead;
     }
 }
 
@@ -210,46 +422,104 @@ int build_triangle(int n, const std::vector<int> &ptr, const std::vector<int> &i
         }
         seg.row0 = lvlptr[seg.lvl0];
         seg.row1 = lvlptr[seg.lvl1];
+        seg.win0 = seg.win1 = 0;
         T.segments.push_back(seg);
         l = seg.lvl1;
     }
+    // entries per level (strict part), for the windows of the chains
+    std::vector<long long> lvl_entries(nlevels, 0);
+    for (int i = 0; i < n; ++i)
+        lvl_entries[level[i]] += ptr[i + 1] - ptr[i];
+    std::vector<int> winptr;
+    for (size_t si = 0; si < T.segments.size(); ++si)
+    {
+        Triangle::Segment &seg = T.segments[si];
+        if (!seg.chain)
+            continue;
+        seg.win0 = (int)winptr.size();
+        for (int lv = seg.lvl0; lv < seg.lvl1;)
+        {
+            const int rows0 = lvlptr[lv + 1] - lvlptr[lv];
+            if (lvl_entries[lv] > WIN_ENTRIES || rows0 > WIN_ROWS)
+            {
+                winptr.push_back(lv | WIN_DIRECT);
+                ++lv;
+                continue;
+            }
+            long long entries = 0;
+            int rows = 0, e = lv;
+            while (e < seg.lvl1 && e - lv < WIN_LEVELS && entries + lvl_entries[e] <= WIN_ENTRIES &&
+                   rows + (lvlptr[e + 1] - lvlptr[e]) <= WIN_ROWS)
+            {
+                entries += lvl_entries[e];
+                rows += lvlptr[e + 1] - lvlptr[e];
+                ++e;
+            }
+            winptr.push_back(lv);
+            lv = e;
+        }
+        seg.win1 = (int)winptr.size();
+        winptr.push_back(seg.lvl1);          // end marker, shared with nothing
+    }
+
+    // entries stored in level order
+    std::vector<int4> rowinfo(n);
+    std::vector<int> col2(idx.size());
+    std::vector<double> val2(val.size());
+    int pos = 0;
+    for (int r = 0; r < n; ++r)
+    {
+        const int i = order[r];
+        rowinfo[r] = make_int4(i, pos, pos + (ptr[i + 1] - ptr[i]), 0);
+        for (int p = ptr[i]; p < ptr[i + 1]; ++p, ++pos)
+        {
+            col2[pos] = idx[p];
+            val2[pos] = val[p];
+        }
+    }
 
     int rc;
-    if ((rc = upload(ptr.data(), (size_t)(n + 1) * sizeof(int), (void **)&T.rowptr))) return rc;
-    if ((rc = upload(idx.data(), idx.size() * sizeof(int), (void **)&T.col))) return rc;
-    if ((rc = upload(val.data(), val.size() * sizeof(double), (void **)&T.val))) return rc;
+    if ((rc = upload(rowinfo.data(), (size_t)n * sizeof(int4), (void **)&T.rowinfo))) return rc;
+    if ((rc = upload(col2.data(), col2.size() * sizeof(int), (void **)&T.col))) return rc;
+    if ((rc = upload(val2.data(), val2.size() * sizeof(double), (void **)&T.val))) return rc;
     if (diag && (rc = upload(diag->data(), (size_t)n * sizeof(double), (void **)&T.diag))) return rc;
-    if ((rc = upload(order.data(), (size_t)n * sizeof(int), (void **)&T.order))) return rc;
     if ((rc = upload(lvlptr.data(), lvlptr.size() * sizeof(int), (void **)&T.lvlptr))) return rc;
+    if ((rc = upload(winptr.data(), winptr.size() * sizeof(int), (void **)&T.winptr))) return rc;
     RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));      // host vectors die with the caller
-    T.bytes = (size_t)(n + 1) * 4 + idx.size() * 12 + (diag ? (size_t)n * 8 : 0) + (size_t)n * 4 +
-              lvlptr.size() * 4;
+    T.bytes = (size_t)n * 16 + idx.size() * 12 + (diag ? (size_t)n * 8 : 0) + lvlptr.size() * 4;
     return RAILS_OK;
 }
 
 void free_triangle(Triangle &T)
 {
-    cudaFree(T.rowptr); cudaFree(T.col); cudaFree(T.val); cudaFree(T.diag);
-    cudaFree(T.order); cudaFree(T.lvlptr);
+    cudaFree(T.rowinfo); cudaFree(T.col); cudaFree(T.val); cudaFree(T.diag);
+    cudaFree(T.lvlptr); cudaFree(T.winptr);
     T = Triangle();
 }
 
 int sweep(const Triangle &T, double *X, long long ld, int nc)
 {
+    static bool configured = false;
+    if (!configured)
+    {
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)(2 * sizeof(WindowStage))));
+        configured = true;
+    }
     for (size_t s = 0; s < T.segments.size(); ++s)
     {
         const Triangle::Segment &seg = T.segments[s];
         if (seg.chain)
-            RAILS_LAUNCH(sptrsv_chain_kernel, 1, CHAIN_THREADS, 0, T.rowptr, T.col, T.val, T.diag,
-                         T.order, T.lvlptr, seg.lvl0, seg.lvl1, X, ld, nc);
+            RAILS_LAUNCH(sptrsv_chain_kernel, 1, CHAIN_THREADS, 2 * sizeof(WindowStage), T.rowinfo, T.col,
+                         T.val, T.diag, T.lvlptr, T.winptr, seg.win0, seg.win1, X, ld, nc);
         else
         {
             const int rows = seg.row1 - seg.row0;
             const int warps_per_cta = LEVEL_THREADS / 32;
             int grid = (rows + warps_per_cta - 1) / warps_per_cta;
             grid = std::min(grid, ctx().sm_count * 8);
-            RAILS_LAUNCH(sptrsv_level_kernel, grid, LEVEL_THREADS, 0, T.rowptr, T.col, T.val, T.diag,
-                         T.order, seg.row0, seg.row1, X, ld, nc);
+            RAILS_LAUNCH(sptrsv_level_kernel, grid, LEVEL_THREADS, 0, T.rowinfo, T.col, T.val, T.diag,
+                         seg.row0, seg.row1, X, ld, nc);
         }
     }
     RAILS_CHECK_LAUNCH();

@@ -382,6 +382,23 @@ CudaMultiVectorWrapper CudaSchurOperator::prolongate(CudaMultiVectorWrapper cons
     return out;
 }
 
+CudaMultiVectorWrapper CudaSchurOperator::select_regular(CudaMultiVectorWrapper const &full) const
+{
+    State &s = *state_;
+    const int c = full.N();
+    CudaMultiVectorWrapper out(n2(), c);
+    if (!s.computed || full.M() != s.n)
+    {
+        std::cerr << "CudaSchurOperator::select_regular: block has " << full.M() << " rows, expected "
+                  << s.n << std::endl;
+        return out;
+    }
+    if (c > 0)
+        ok(rails_mv_gather_rows(out.device_handle(), out.device_col0(), full.device_handle(),
+                                full.device_col0(), c, s.dev_idx2.h, 1.0), "select_regular");
+    return out;
+}
+
 double CudaSchurOperator::Trace(CudaMultiVectorWrapper const &V, HostDenseMatrix const &T) const
 {
     // trace(P V T V' P') = trace(T (V'V + W'W)),  W = A11^-1 A12 V; the reference

@@ -77,6 +77,9 @@ public:
     // (:222-293): its blocks X22 = V T V', X12 = -A11^-1 A12 X22, X21 = X12',
     // X11 = A11^-1 A12 X22 A12' A11^-T are exactly P V T V' P'.
     CudaMultiVectorWrapper prolongate(CudaMultiVectorWrapper const &V) const;
+    // rows idx2 of a full-length block: the reduced basis back from a prolongated
+    // one (prolongate leaves V itself in those rows), X2 of RAILSschur.m:58
+    CudaMultiVectorWrapper select_regular(CudaMultiVectorWrapper const &full) const;
 
     // trace of the full solution X = P V T V' P' (SchurOperator::Trace, :295-342):
     // trace(T) + trace(T V' A12' A11^-T A11^-1 A12 V) for an orthonormal V

@@ -140,6 +140,29 @@ void rails_host_lu_permutations(void *h, int *pinv, int *q)
     std::memcpy(q, lu->q.data(), sizeof(int) * lu->n);
 }
 
+// level of every row in the forward sweep with L (level[i] = longest dependency
+// chain ending in row i) and the number of stored entries of that row; what the
+// device schedule of csrc/sptrsv.cu is built from (diagnostics, scripts/)
+void rails_host_lu_row_levels(void *h, int *level, int *row_nnz)
+{
+    SparseLU *lu = (SparseLU *)h;
+    const int n = lu->n;
+    for (int i = 0; i < n; ++i)
+    {
+        level[i] = 0;
+        row_nnz[i] = 0;
+    }
+    // L is stored by columns with rows > column: column j pushes its level to its rows
+    for (int j = 0; j < n; ++j)
+        for (int p = lu->Lp[j]; p < lu->Lp[j + 1]; ++p)
+        {
+            const int i = lu->Li[p];
+            if (level[i] < level[j] + 1)
+                level[i] = level[j] + 1;
+            ++row_nnz[i];
+        }
+}
+
 void rails_host_minimum_degree(int n, const int *rowptr, const int *colidx, int *order)
 {
     std::vector<int> o = minimum_degree_order(n, rowptr, colidx);

@@ -154,7 +154,7 @@ def test_cli_mass_matrix(gpu, tmp_path):
     assert np.array_equal(o["V"], api.mm_read_dense(os.path.join(d, "V.mtx")))
 
 
-def test_cli_refuses_singular_mass_and_bad_input(gpu, tmp_path):
+def test_cli_singular_mass_and_bad_input(gpu, tmp_path):
     d = str(tmp_path)
     rp, ci, v, B = _write_problem(d)
     dm = np.ones(400)
@@ -162,8 +162,13 @@ def test_cli_refuses_singular_mass_and_bad_input(gpu, tmp_path):
     keep = dm != 0
     rpm = np.concatenate([[0], np.cumsum(keep)]).astype(np.int32)
     api.mm_write_crs(os.path.join(d, "M.mtx"), rpm, np.arange(400, dtype=np.int32)[keep], dm[keep], 400)
-    r = _run(d, os.path.join(d, "params.xml"))
+    # a singular M is reduced to its Schur complement (tests/test_gpu_schur.py) --
+    # on one GPU and with a dense B only
+    r = _run(d, os.path.join(d, "params.xml"), "--b-operator")
     assert r.returncode == 4 and "Schur" in r.stderr
+    r = _run(d, os.path.join(d, "params.xml"))
+    assert r.returncode == 0 and "Singular part: 40 rows, Schur complement: 360 rows" in r.stdout
+    assert api.mm_read_dense(os.path.join(d, "V.mtx")).shape[0] == 400
     os.remove(os.path.join(d, "M.mtx"))
     os.remove(os.path.join(d, "B.mtx"))
     r = _run(d, os.path.join(d, "params.xml"))

@@ -266,6 +266,16 @@ long long rails_lu_nnz(rails_lu_t F);
  * kernels one solve launches */
 int rails_lu_levels(rails_lu_t F, int which);
 int rails_lu_launches_per_solve(rails_lu_t F, int trans);
+/* Host-only check of the device schedule (no CUDA call, like rails_csr_halo_plan):
+ * builds the level schedules, chains, shared-memory slots and windows exactly as
+ * rails_lu_create does and runs one solve over x (n x nrhs, ld, in place) in the
+ * order and from the arrays the kernels use.  stats[12], per triangle of the
+ * solve: levels, launches segments, chains, windows, rows in chains, entries
+ * between rows of a chain. */
+int rails_lu_plan_emulate(int n, const int *Lp, const int *Li, const double *Lx,
+                          const int *Up, const int *Ui, const double *Ux,
+                          const int *pinv, const int *q, int trans, double *x, int nrhs,
+                          long long ld, long long *stats);
 
 /* ---- row index lists: the idx1 / idx2 splitting of the Schur complement
  *      (Epetra_Import between the maps of src/SchurOperator.cpp:93-94,131-132,

@@ -125,6 +125,8 @@ CUDA_SYMBOLS = [
     ("rails_lu_nnz", LL, [P]),
     ("rails_lu_levels", I, [P, I]),
     ("rails_lu_launches_per_solve", I, [P, I]),
+    ("rails_lu_plan_emulate", I, [I, c_int_p, c_int_p, c_double_p, c_int_p, c_int_p, c_double_p, c_int_p,
+                                  c_int_p, I, c_double_p, I, LL, ctypes.POINTER(LL)]),
     ("rails_idx_create", I, [LL, c_int_p, ctypes.POINTER(P)]),
     ("rails_idx_free", I, [P]),
     ("rails_mv_gather_rows", I, [P, I, P, I, I, P, D]),
@@ -363,6 +365,19 @@ class SparseLU:
         x = np.asfortranarray(np.array(b, dtype=np.float64).reshape(self.n, -1, order="F"))
         host().rails_host_lu_solve(self.h, dptr(x), ctypes.c_int(x.shape[1]), ctypes.c_longlong(self.n),
                                    ctypes.c_int(1 if trans else 0))
+        return x
+
+    def emulate_device_schedule(self, b, trans=False):
+        """The solve in the order and from the arrays the kernels use, on the host
+        (rails_lu_plan_emulate): checks chains, slots and windows without a GPU."""
+        x = np.asfortranarray(np.array(b, dtype=np.float64).reshape(self.n, -1, order="F"))
+        stats = (ctypes.c_longlong * 12)()
+        rc = host().rails_host_lu_plan_emulate(self.h, ctypes.c_int(1 if trans else 0), dptr(x),
+                                               ctypes.c_int(x.shape[1]), ctypes.c_longlong(self.n), stats)
+        if rc:
+            raise RailsError("rails_lu_plan_emulate failed (%d)" % rc)
+        keys = ("levels", "segments", "chains", "windows", "chain_rows", "chain_entries")
+        self.plan_stats = [dict(zip(keys, [int(stats[6 * t + i]) for i in range(6)])) for t in range(2)]
         return x
 
     def device_solve(self, b, trans=False, repeat=0):

@@ -163,6 +163,15 @@ void rails_host_lu_row_levels(void *h, int *level, int *row_nnz)
         }
 }
 
+// the device schedule of these factors executed on the host (rails_lu_plan_emulate)
+int rails_host_lu_plan_emulate(void *h, int trans, double *x, int nrhs, long long ld, long long *stats)
+{
+    SparseLU *lu = (SparseLU *)h;
+    return rails_lu_plan_emulate(lu->n, lu->Lp.data(), lu->Li.data(), lu->Lx.data(), lu->Up.data(),
+                                 lu->Ui.data(), lu->Ux.data(), lu->pinv.data(), lu->q.data(), trans, x,
+                                 nrhs, ld, stats);
+}
+
 void rails_host_minimum_degree(int n, const int *rowptr, const int *colidx, int *order)
 {
     std::vector<int> o = minimum_degree_order(n, rowptr, colidx);

@@ -130,6 +130,11 @@ def test_host_lu_solves(name):
         ours = np.linalg.norm(Aop @ x - b) / (spl.norm(A, 1) * np.linalg.norm(x) + np.linalg.norm(b))
         theirs = np.linalg.norm(Aop @ xr - b) / (spl.norm(A, 1) * np.linalg.norm(xr) + np.linalg.norm(b))
         assert ours < max(50 * theirs, 1e-14), (ours, theirs)
+        # the device schedule (chains, shared-memory slots, windows) walked on the
+        # host gives the same solve: checks the plan of csrc/sptrsv.cu without a GPU
+        xe = lu.emulate_device_schedule(b, trans)
+        assert np.linalg.norm(xe - x) < 1e-10 * np.linalg.norm(x)
+        assert all(s["levels"] >= 1 for s in lu.plan_stats)
     if name == "saddle":
         assert lu.off_diagonal_pivots > 0
     if name == "laplace2d":

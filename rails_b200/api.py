@@ -466,10 +466,11 @@ class SchurOperator:
 
 
 def solve_schur(rowptr, colidx, vals, mdiag, B, params, border=None, seed=1, v_cap_cols=400,
-                hist_cap=4096):
+                hist_cap=4096, V0=None):
     """rails_host_solve_schur: A X M' + M X A' + B B' = 0 with a singular diagonal
     M through the Schur complement.  Returns a dict with V (full rows, prolongated,
-    border rows included), V_reduced, T, the history and the set-up facts."""
+    border rows included), V_reduced, T, the history and the set-up facts.  V0: a
+    previous V (all rows) to warm-start from, with params["Restart from solution"] = 1."""
     lib = host()
     rp, ci, v = _csr32(rowptr, colidx, vals)
     n = rp.size - 1
@@ -488,11 +489,13 @@ def solve_schur(rowptr, colidx, vals, mdiag, B, params, border=None, seed=1, v_c
     Vr = np.zeros((max(n2_max, 1), v_cap_cols), order="F")
     T = np.zeros((v_cap_cols, v_cap_cols), order="F")
     sizes, stats, secs = (ctypes.c_int * 2)(), (ctypes.c_longlong * 6)(), (ctypes.c_double * 2)()
+    V0c = None if V0 is None else np.asfortranarray(np.array(V0, dtype=np.float64).reshape(n + nb, -1, order="F"))
     ret = lib.rails_host_solve_schur(
         ctypes.c_int(n), iptr(rp), iptr(ci), dptr(v), dptr(md), ctypes.c_int(nb), dptr(bd),
         ctypes.c_int(Bc.shape[1]), dptr(Bc), ctypes.c_uint(seed), ctypes.c_int(len(keys)), karr, dptr(pv),
         ctypes.c_int(hist_cap), dptr(ha), dptr(hr), iptr(hk), ctypes.byref(hl), ctypes.byref(k),
-        ctypes.c_int(v_cap_cols), dptr(Vf), dptr(Vr), dptr(T), sizes, stats, secs)
+        ctypes.c_int(v_cap_cols), dptr(Vf), dptr(Vr), dptr(T), sizes, stats, secs,
+        ctypes.c_int(0 if V0c is None else V0c.shape[1]), dptr(V0c))
     m = min(hl.value, hist_cap)
     out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:m].copy(), rel=hr[:m].copy(),
                space=hk[:m].copy(), n1=sizes[0], n2=sizes[1], setup_seconds=secs[0],

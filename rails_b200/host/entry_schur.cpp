@@ -330,6 +330,9 @@ int rails_host_schur_apply(void *h, int what, const double *X, int c, double *Y,
 //              solves the ORIGINAL equation (Vtrans, matlab/RAILSschur.m:68)
 //     V_red  : n2 x k, the basis of the reduced problem (may be NULL)
 //     T_out  : k x k with leading dimension v_cap_cols
+//     k0, V0_full : warm start (parameter "Restart from solution" = 1): k0 columns
+//              of a previous V_full ((n + n_border) rows); its rows idx2 are the
+//              reduced basis (the prolongation leaves V itself there)
 // Parameters as rails_host_solve plus "Projection method" (with the inverse
 // S^-1 x = (A^-1 [0; x])(idx2) supplied, matlab/test/test_MOC.m:45-49).
 // sizes: n1, n2;  stats as rails_host_schur_stats;  seconds: set-up, solve.
@@ -340,7 +343,7 @@ int rails_host_solve_schur(int n, const int *rowptr, const int *colidx, const do
                            int hist_cap, double *hist_abs, double *hist_rel, int *hist_k,
                            int *hist_len, int *k_out, int v_cap_cols, double *V_full,
                            double *V_red, double *T_out, int *sizes, long long *stats,
-                           double *seconds)
+                           double *seconds, int k0, const double *V0_full)
 {
     if (!rails_cuda_is_initialized())
     {
@@ -400,6 +403,22 @@ int rails_host_solve_schur(int n, const int *rowptr, const int *colidx, const do
         solver.set_inverse(schur.inverse_operator());
 
     CudaMultiVectorWrapper V(schur.n2(), 1);
+    if (params.get("Restart from solution", false))
+    {
+        if (k0 < 1 || !V0_full)
+        {
+            std::cerr << "rails_host_solve_schur: \"Restart from solution\" needs a start basis" << std::endl;
+            delete obj;
+            return 102;
+        }
+        CudaMultiVectorWrapper full(n_total, k0);
+        if (rails_mv_upload(full.device_handle(), 0, k0, V0_full, n_total))
+        {
+            delete obj;
+            return 200;
+        }
+        V = schur.select_regular(full);
+    }
     HostDenseMatrix T;
     rails_cuda_sync();
     auto t0 = std::chrono::steady_clock::now();

@@ -212,6 +212,50 @@ def test_schur_solve_follows_matlab_restatement(gpu, name, pm):
     assert np.linalg.norm(Xq - Xo) / np.linalg.norm(Xo) < 5e-2      # both within tol of the solution
 
 
+def test_schur_warm_start_and_driver_continuation(gpu, tmp_path):
+    """Continuation as in test/LyapunovSolver_test.cpp:312-352, through the Schur
+    complement: a solve started from the (prolongated) solution of the same
+    problem converges at once -- through the entry point and through V.mtx."""
+    import re
+    import subprocess
+    p = synthetic_singular(g=16)
+    P = {"Tolerance": 1e-6, "Expand size": 2, "Lanczos iterations": 10, "Maximum iterations": 300}
+    first = gpu.solve_schur(p["rowptr"], p["colidx"], p["vals"], p["mdiag"], p["B"], P)
+    assert first["ret"] == 0 and first["iterations"] > 5
+    again = gpu.solve_schur(p["rowptr"], p["colidx"], p["vals"], p["mdiag"], p["B"],
+                            dict(P, **{"Restart from solution": 1}), V0=first["V"])
+    assert again["ret"] == 0 and again["iterations"] <= 5
+    missing = gpu.solve_schur(p["rowptr"], p["colidx"], p["vals"], p["mdiag"], p["B"],
+                              dict(P, **{"Restart from solution": 1}))
+    assert missing["ret"] == 102
+
+    d = str(tmp_path)
+    n = p["n"]
+    gpu.mm_write_crs(os.path.join(d, "A.mtx"), p["rowptr"], p["colidx"], p["vals"], n)
+    Bs = sp.csr_matrix(p["B"])
+    gpu.mm_write_crs(os.path.join(d, "B.mtx"), Bs.indptr.astype(np.int32), Bs.indices.astype(np.int32),
+                     Bs.data, p["B"].shape[1])
+    Ms = sp.csr_matrix(sp.diags(p["mdiag"]))
+    Ms.eliminate_zeros()
+    gpu.mm_write_crs(os.path.join(d, "M.mtx"), Ms.indptr.astype(np.int32), Ms.indices.astype(np.int32),
+                     Ms.data, n)
+    ini = "[Lyapunov Solver]\nTolerance = 1e-6\nExpand size = 2\nLanczos iterations = 10\n"
+    open(os.path.join(d, "p1.ini"), "w").write(ini)
+    open(os.path.join(d, "p2.ini"), "w").write(ini + "Restart from solution = true\n")
+    exe = os.path.join(ROOT, "rails_b200", "rails_cuda_main")
+    r1 = subprocess.run([exe, os.path.join(d, "p1.ini"), "--dir", d], stdout=subprocess.PIPE,
+                        stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r1.returncode == 0, r1.stdout[-2000:] + r1.stderr[-2000:]
+    it1 = int(re.search(r"Iterations: (\d+)", r1.stdout).group(1))
+    r2 = subprocess.run([exe, os.path.join(d, "p2.ini"), "--dir", d], stdout=subprocess.PIPE,
+                        stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r2.returncode == 0, r2.stdout[-2000:] + r2.stderr[-2000:]
+    it2 = int(re.search(r"Iterations: (\d+)", r2.stdout).group(1))
+    assert it1 > 5 and it2 <= 5
+    V = gpu.mm_read_dense(os.path.join(d, "V.mtx"))
+    assert V.shape[0] == n
+
+
 def test_schur_refuses_what_it_cannot_do(gpu):
     p = synthetic_singular(g=8)
     # singular A11: a massless unknown with an empty row/column block

@@ -239,9 +239,14 @@ def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
     # The two calls of the path that are bound by FP64 arithmetic rather than by HBM
     # once k, r >~ 50: the restart compression V <- V X (k x r,
     # src/LyapunovSolver.hpp:265-297) and the warm-start projection V'(AV) (k x k,
-    # :173-195).  Reported against both ceilings; the FP64 one is the nominal
-    # 37 TFLOP/s of an HGX B200 GPU (no measured FP64 peak exists on this pool).
+    # :173-195).  Reported against both ceilings; the FP64 one is measured here with
+    # register-only kernels (rails_cuda_fp64_peak: DFMA and DMMA, the larger counts),
+    # next to the nominal 37 TFLOP/s of an HGX B200 GPU.
     FP64_NOMINAL_TFLOPS = 37.0
+    peak_fma, peak_mma = ctypes.c_double(0), ctypes.c_double(0)
+    api.check(lib.rails_cuda_fp64_peak(0, ctypes.byref(peak_fma)), "fp64_peak")
+    api.check(lib.rails_cuda_fp64_peak(1, ctypes.byref(peak_mma)), "fp64_peak")
+    fp64_measured = max(peak_fma.value, peak_mma.value)
     r = max(k // 2, 1)
     Out = api.MultiVector(rows, r)
     Xc = np.asfortranarray(np.random.RandomState(3).uniform(-1, 1, (k, r)) * 1e-2)
@@ -254,6 +259,8 @@ def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
         ms = timed(fn, reps=4, warm=1)
         rec(name, ms, nbytes, launches)
         out[name].update({"flops": flops, "tflops": flops / ms / 1e9,
+                          "frac_of_fp64_measured": flops / ms / 1e9 / fp64_measured,
+                          "fp64_measured_tflops": {"dfma": peak_fma.value, "dmma": peak_mma.value},
                           "frac_of_fp64_nominal": flops / ms / 1e9 / FP64_NOMINAL_TFLOPS,
                           "fp64_nominal_tflops": FP64_NOMINAL_TFLOPS})
 

@@ -69,6 +69,11 @@ long long rails_cuda_error_count(void);
 /* number of this library's kernels launched since init (bench.py's
  * gpu_launches) */
 long long rails_cuda_kernel_launches(void);
+/* Sustained FP64 throughput of this GPU in TFLOP/s, measured with a register-only
+ * kernel on every SM: kind 0 = DFMA (vector pipe), 1 = DMMA (tensor cores).  The
+ * denominator of the FLOP-bound rooflines bench.py reports (restart compression,
+ * warm-start projection: SURVEY F13); MEASURED_PEAKS.json has no FP64 figure. */
+int rails_cuda_fp64_peak(int kind, double *tflops);
 /* device memory currently held by multivectors and operators, bytes */
 long long rails_cuda_bytes_in_use(void);
 /* CUDA-event timing on the library stream (bench.py, Timer sections):

@@ -69,6 +69,7 @@ CUDA_SYMBOLS = [
     ("rails_cuda_error_count", LL, []),
     ("rails_cuda_kernel_launches", LL, []),
     ("rails_cuda_bytes_in_use", LL, []),
+    ("rails_cuda_fp64_peak", I, [I, c_double_p]),
     ("rails_cuda_event_record", I, [I]),
     ("rails_cuda_event_elapsed_ms", I, [I, I, ctypes.POINTER(ctypes.c_float)]),
     ("rails_cuda_comm_unique_id", I, [ctypes.c_char_p]),

@@ -15,6 +15,7 @@
 // resident CTAs, a second kernel adds the per-CTA partials in CTA order.
 #include "internal.h"
 
+#include <algorithm>
 #include <vector>
 
 using rails::ctx;
@@ -210,6 +211,13 @@ int dot_device(const double *X, long long ldx, int a, const double *Y, long long
     {
         RAILS_CUDA_TRY(cudaMemset2DAsync(d_out, (size_t)ldo * sizeof(double), 0,
                                          (size_t)a * sizeof(double), b, c.stream));
+    }
+    else if (fp64_tensor_enabled() && std::min(a, b) > 8 && ((size_t)X % 16 == 0) && ((size_t)Y % 16 == 0) && ldx % 2 == 0 &&
+             ldy % 2 == 0)
+    {
+        // both blocks wide: FP64-arithmetic-bound, tensor-core kernel (gram.cu)
+        int rc = gram_device(X, ldx, a, Y, ldy, b, rows, d_out, ldo);
+        if (rc) return rc;
     }
     else
     {

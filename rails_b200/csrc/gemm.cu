@@ -151,6 +151,10 @@ int gemm_device(const double *V, long long ldv, int k, const double *dC, int ldc
         return RAILS_OK;
     if (k == 0)
         dC = nullptr;          // empty sum: Out = beta * Out
+    // many result columns: FP64-arithmetic-bound, V read once (gram.cu)
+    if (dC && gemm_dmma_fits(k, c) && (size_t)V % 16 == 0 && (size_t)Out % 16 == 0 && ldv % 2 == 0 &&
+        ldo % 2 == 0)
+        return gemm_dmma_device(V, ldv, k, dC, ldc, c, alpha, beta, Out, ldo, rows);
     int t = 0;
     while (t < c)
     {

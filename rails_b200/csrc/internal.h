@@ -153,6 +153,16 @@ void release_mailboxes();
 int dot_device(const double *X, long long ldx, int a, const double *Y,
                long long ldy, int b, long long rows, double *d_out, int ldo,
                bool reduce_over_ranks);
+// X' Y with both a and b above 8 on the FP64 tensor cores (gram.cu); operands
+// 16-byte aligned with even leading dimensions
+int gram_device(const double *X, long long ldx, int a, const double *Y, long long ldy, int b,
+                long long rows, double *d_out, int ldo);
+// Out = alpha V C + beta Out with more than 8 result columns on the FP64 tensor
+// cores (gram.cu); operands 16-byte aligned with even leading dimensions
+bool fp64_tensor_enabled();
+bool gemm_dmma_fits(int k, int c);
+int gemm_dmma_device(const double *V, long long ldv, int k, const double *dC, int ldc, int c,
+                     double alpha, double beta, double *Out, long long ldo, long long rows);
 int gemm_device(const double *V, long long ldv, int k, const double *dC, int ldc,
                 int c, double alpha, double beta, double *Out, long long ldo,
                 long long rows);

@@ -171,6 +171,53 @@ def test_dot_vs_oracle(gpu, m, a, b):
     assert np.all(G[a:] == 7.0)
 
 
+@pytest.mark.parametrize("m", [5, 1000, 4099, 70001])
+@pytest.mark.parametrize("a,b", [(9, 9), (16, 100), (100, 16), (64, 64), (33, 70), (130, 40), (200, 200)])
+def test_block_dot_on_tensor_cores(gpu, m, a, b):
+    """Both blocks wider than 8 columns: the DMMA kernel of csrc/gram.cu (the
+    warm-start projection V'(AV), k x e blocks with e = 16, Gram matrices)."""
+    rs = np.random.RandomState(m % 1000 + a * 7 + b)
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, a + 1)))
+    Y = np.asfortranarray(rs.uniform(-1, 1, (m, b + 2)))
+    Xd, Yd = gpu.MultiVector.from_numpy(X), gpu.MultiVector.from_numpy(Y)
+    G = np.full((a + 3, b), 7.0, order="F")
+    gpu.check(gpu.cuda().rails_mv_dot(Xd.h, 1, a, Yd.h, 2, b, gpu.dptr(G), a + 3), "dot")
+    want = X[:, 1:].T @ Y[:, 2:]
+    bound = 1e-13 * (np.abs(X[:, 1:]).T @ np.abs(Y[:, 2:]) + 1.0)
+    assert np.all(np.abs(G[:a] - want) <= bound)
+    assert np.all(G[a:] == 7.0)
+    G2 = np.zeros((a, b), order="F")
+    gpu.check(gpu.cuda().rails_mv_dot(Xd.h, 1, a, Yd.h, 2, b, gpu.dptr(G2), a), "dot")
+    assert np.array_equal(G2, G[:a])                     # reproducible
+
+
+@pytest.mark.parametrize("m", [3, 1025, 70001])
+@pytest.mark.parametrize("k,c", [(4, 9), (7, 64), (64, 32), (70, 33), (200, 100), (13, 16)])
+def test_block_gemm_on_tensor_cores(gpu, m, k, c):
+    """More than 8 result columns: the DMMA kernel of csrc/gram.cu (restart
+    compression V <- V X)."""
+    rs = np.random.RandomState(k * 31 + c)
+    V = np.asfortranarray(rs.uniform(-1, 1, (m, k + 1)))
+    C = np.asfortranarray(rs.uniform(-1, 1, (k + 1, c)))
+    O0 = np.asfortranarray(rs.uniform(-1, 1, (m, c + 1)))
+    for alpha, beta in [(1.0, 0.0), (-1.0, 1.0), (0.5, 2.0)]:
+        Vd, Od = gpu.MultiVector.from_numpy(V), gpu.MultiVector.from_numpy(O0)
+        gpu.check(gpu.cuda().rails_mv_gemm(Vd.h, 1, k, gpu.dptr(C), k + 1, c, alpha, beta, Od.h, 1), "gemm")
+        want = alpha * (V[:, 1:] @ C[:k]) + beta * O0[:, 1:]
+        bound = 1e-13 * (np.abs(V[:, 1:]) @ np.abs(C[:k]) + 2 * np.abs(O0[:, 1:]) + 1.0)
+        got = Od.numpy()
+        assert np.all(np.abs(got[:, 1:] - want) <= bound)
+        assert np.array_equal(got[:, 0], O0[:, 0])       # the column before the block is untouched
+
+
+def test_fp64_peak_probe(gpu):
+    fma, mma = ctypes.c_double(0), ctypes.c_double(0)
+    gpu.check(gpu.cuda().rails_cuda_fp64_peak(0, ctypes.byref(fma)), "fp64_peak")
+    gpu.check(gpu.cuda().rails_cuda_fp64_peak(1, ctypes.byref(mma)), "fp64_peak")
+    print("FP64 peak: DFMA %.1f TFLOP/s, DMMA %.1f TFLOP/s" % (fma.value, mma.value))
+    assert 5.0 < fma.value < 100.0 and 1.0 < mma.value < 200.0
+
+
 def test_dot_is_deterministic(gpu):
     rs = np.random.RandomState(11)
     m = 1 << 20

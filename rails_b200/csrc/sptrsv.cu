@@ -407,15 +407,19 @@ __device__ __forceinline__ void window_fetch(WindowStage &st, const WindowShape 
     }
 }
 
+// CT = right-hand sides of this launch (1 .. CHAIN_COLS): a template parameter, so
+// that one right-hand side does not pay the issue slots of four
+template<int CT>
 __global__ void __launch_bounds__(CHAIN_THREADS, 1)
 sptrsv_chain_kernel(const int4 *__restrict__ crowinfo, const int *__restrict__ ccol,
                     const double *__restrict__ cval, const double *__restrict__ diag,
                     const int *__restrict__ lvlptr, const int *__restrict__ winshape, int w0, int w1,
-                    double *X, long long ld, int c0, int ct)
+                    double *X, long long ld, int c0)
 {
+    constexpr int ct = CT;
     extern __shared__ __align__(16) unsigned char chain_smem[];
     ChainShared &sh = *reinterpret_cast<ChainShared *>(chain_smem);
-    __shared__ double partial[CHAIN_THREADS / 32][CHAIN_COLS];
+    __shared__ double partial[CHAIN_THREADS / 32][CT];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     constexpr int nwarps = CHAIN_THREADS / 32;
@@ -454,30 +458,30 @@ sptrsv_chain_kernel(const int4 *__restrict__ crowinfo, const int *__restrict__ c
                         if (diag)
                             d = st.pivot[r];
                     }
-                    double acc[CHAIN_COLS] = {0.0, 0.0, 0.0, 0.0};
+                    double acc[CT];
+#pragma unroll
+                    for (int c = 0; c < CT; ++c)
+                        acc[c] = 0.0;
                     for (int p = info.y - shape.ea + lane; p < info.z - shape.ea; p += 32)
                     {
                         const int slot = st.col[p];
                         const double v = st.val[p];
 #pragma unroll
-                        for (int c = 0; c < CHAIN_COLS; ++c)
-                            if (c < ct)
-                                acc[c] = fma(v, sh.x[c][slot], acc[c]);
+                        for (int c = 0; c < CT; ++c)
+                            acc[c] = fma(v, sh.x[c][slot], acc[c]);
                     }
 #pragma unroll
-                    for (int c = 0; c < CHAIN_COLS; ++c)
-                        if (c < ct)
-                        {
+                    for (int off = 16; off > 0; off >>= 1)
 #pragma unroll
-                            for (int off = 16; off > 0; off >>= 1)
-                                acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
-                        }
+                        for (int c = 0; c < CT; ++c)
+                            acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
                     if (lane < ct)
                     {
                         double mine = acc[0];
-                        if (lane == 1) mine = acc[1];
-                        if (lane == 2) mine = acc[2];
-                        if (lane == 3) mine = acc[3];
+#pragma unroll
+                        for (int c = 1; c < CT; ++c)
+                            if (lane == c)
+                                mine = acc[c];
                         const double r1 = rhs - mine;
                         const double xv = diag ? r1 / d : r1;
                         X[info.x + (size_t)(c0 + lane) * ld] = xv;
@@ -506,29 +510,28 @@ sptrsv_chain_kernel(const int4 *__restrict__ crowinfo, const int *__restrict__ c
                 if (diag)
                     d = st.pivot[r0 + team];
             }
-            double acc[CHAIN_COLS] = {0.0, 0.0, 0.0, 0.0};
+            double acc[CT];
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                acc[c] = 0.0;
             if (has)
                 for (int p = info.y - shape.ea + part * 32 + lane; p < info.z - shape.ea; p += team_warps * 32)
                 {
                     const int slot = st.col[p];
                     const double v = st.val[p];
 #pragma unroll
-                    for (int c = 0; c < CHAIN_COLS; ++c)
-                        if (c < ct)
-                            acc[c] = fma(v, sh.x[c][slot], acc[c]);
+                    for (int c = 0; c < CT; ++c)
+                        acc[c] = fma(v, sh.x[c][slot], acc[c]);
                 }
 #pragma unroll
-            for (int c = 0; c < CHAIN_COLS; ++c)
-                if (c < ct)
-                {
+            for (int off = 16; off > 0; off >>= 1)
 #pragma unroll
-                    for (int off = 16; off > 0; off >>= 1)
-                        acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
-                }
+                for (int c = 0; c < CT; ++c)
+                    acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
             if (lane == 0)
             {
 #pragma unroll
-                for (int c = 0; c < CHAIN_COLS; ++c)
+                for (int c = 0; c < CT; ++c)
                     partial[warp][c] = acc[c];
             }
             __syncthreads();
@@ -620,7 +623,13 @@ int sweep(const Triangle &T, double *X, long long ld, int nc)
     static bool configured = false;
     if (!configured)
     {
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)sizeof(ChainShared)));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)sizeof(ChainShared)));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)sizeof(ChainShared)));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)sizeof(ChainShared)));
         configured = true;
     }
@@ -637,9 +646,27 @@ int sweep(const Triangle &T, double *X, long long ld, int nc)
         if (!seg.chain)
             continue;
         for (int c0 = 0; c0 < nc; c0 += CHAIN_COLS)
-            RAILS_LAUNCH(sptrsv_chain_kernel, 1, CHAIN_THREADS, sizeof(ChainShared), T.crowinfo, T.ccol,
-                         T.cval, T.diag, T.lvlptr, T.winshape, seg.win0, seg.win1, X, ld, c0,
-                         std::min(CHAIN_COLS, nc - c0));
+        {
+            switch (std::min(CHAIN_COLS, nc - c0))
+            {
+            case 1:
+                RAILS_LAUNCH(sptrsv_chain_kernel<1>, 1, CHAIN_THREADS, sizeof(ChainShared), T.crowinfo, T.ccol,
+                             T.cval, T.diag, T.lvlptr, T.winshape, seg.win0, seg.win1, X, ld, c0);
+                break;
+            case 2:
+                RAILS_LAUNCH(sptrsv_chain_kernel<2>, 1, CHAIN_THREADS, sizeof(ChainShared), T.crowinfo, T.ccol,
+                             T.cval, T.diag, T.lvlptr, T.winshape, seg.win0, seg.win1, X, ld, c0);
+                break;
+            case 3:
+                RAILS_LAUNCH(sptrsv_chain_kernel<3>, 1, CHAIN_THREADS, sizeof(ChainShared), T.crowinfo, T.ccol,
+                             T.cval, T.diag, T.lvlptr, T.winshape, seg.win0, seg.win1, X, ld, c0);
+                break;
+            default:
+                RAILS_LAUNCH(sptrsv_chain_kernel<4>, 1, CHAIN_THREADS, sizeof(ChainShared), T.crowinfo, T.ccol,
+                             T.cval, T.diag, T.lvlptr, T.winshape, seg.win0, seg.win1, X, ld, c0);
+                break;
+            }
+        }
     }
     RAILS_CHECK_LAUNCH();
     return RAILS_OK;

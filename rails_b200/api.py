@@ -409,6 +409,15 @@ def minimum_degree(rowptr, colidx):
     return order
 
 
+def nested_dissection(rowptr, colidx, leaf=200):
+    rp = np.ascontiguousarray(rowptr, dtype=np.int32)
+    ci = np.ascontiguousarray(colidx, dtype=np.int32)
+    order = np.zeros(rp.size - 1, dtype=np.int32)
+    host().rails_host_nested_dissection(ctypes.c_int(rp.size - 1), iptr(rp), iptr(ci), ctypes.c_int(leaf),
+                                        iptr(order))
+    return order
+
+
 class SchurOperator:
     """The Schur-complement operator on the GPU (rails_b200/host/CudaSchurOperator.cpp)
     for parity tests of its pieces: S, S', S^-1, restrict, prolongate."""

@@ -111,6 +111,260 @@ std::vector<int> minimum_degree_order(int n, const int *rowptr, const int *colid
     return order;
 }
 
+namespace
+{
+
+// symmetric adjacency of A + A' without the diagonal; rows with more than
+// `dense_limit` neighbours are taken out (flag set, lists cleared)
+void symmetric_graph(int n, const int *rowptr, const int *colidx, size_t dense_limit,
+                     std::vector<std::vector<int> > &adj, std::vector<char> &dense)
+{
+    adj.assign(n, std::vector<int>());
+    for (int i = 0; i < n; ++i)
+        for (int p = rowptr[i]; p < rowptr[i + 1]; ++p)
+        {
+            const int j = colidx[p];
+            if (j == i || j < 0 || j >= n)
+                continue;
+            adj[i].push_back(j);
+            adj[j].push_back(i);
+        }
+    dense.assign(n, 0);
+    for (int i = 0; i < n; ++i)
+    {
+        std::sort(adj[i].begin(), adj[i].end());
+        adj[i].erase(std::unique(adj[i].begin(), adj[i].end()), adj[i].end());
+        dense[i] = adj[i].size() > dense_limit;
+    }
+    for (int i = 0; i < n; ++i)
+    {
+        if (dense[i])
+            continue;
+        adj[i].erase(std::remove_if(adj[i].begin(), adj[i].end(), [&](int j) { return dense[j] != 0; }),
+                     adj[i].end());
+    }
+}
+
+}
+
+// Nested dissection by level structures (George): a connected piece is split by
+// the middle level of a breadth-first search from a pseudo-peripheral node; the
+// two sides are ordered first (recursively), the separator last; pieces of at
+// most `leaf` nodes are ordered by minimum degree.  O(n log n) breadth-first
+// work, where the explicit-graph minimum degree above is quadratic in the size of
+// the last cliques; on grid-like problems the fill is comparable.
+std::vector<int> nested_dissection_order(int n, const int *rowptr, const int *colidx, int leaf)
+{
+    const size_t dense_limit = (size_t)std::max(16.0, 10.0 * std::sqrt((double)n));
+    std::vector<std::vector<int> > adj;
+    std::vector<char> dense;
+    symmetric_graph(n, rowptr, colidx, dense_limit, adj, dense);
+
+    std::vector<int> order;
+    order.reserve(n);
+    std::vector<int> part(n, -1);          // id of the piece a node currently belongs to
+    std::vector<int> dist(n, -1), local(n, -1);
+    int next_part = 0;
+
+    // breadth-first search inside piece `id` from `root`; fills `visit` level by level
+    auto bfs = [&](int root, int id, std::vector<int> &visit, std::vector<int> &level_start) {
+        visit.clear();
+        level_start.clear();
+        visit.push_back(root);
+        dist[root] = 0;
+        size_t head = 0;
+        while (head < visit.size())
+        {
+            level_start.push_back((int)head);
+            const size_t end = visit.size();
+            for (; head < end; ++head)
+            {
+                const int v = visit[head];
+                for (size_t a = 0; a < adj[v].size(); ++a)
+                {
+                    const int u = adj[v][a];
+                    if (part[u] == id && dist[u] < 0)
+                    {
+                        dist[u] = dist[v] + 1;
+                        visit.push_back(u);
+                    }
+                }
+            }
+        }
+        level_start.push_back((int)visit.size());
+        for (size_t i = 0; i < visit.size(); ++i)
+            dist[visit[i]] = -1;
+    };
+
+    auto order_leaf = [&](std::vector<int> const &nodes) {
+        // minimum degree on the induced subgraph
+        const int m = (int)nodes.size();
+        for (int i = 0; i < m; ++i)
+            local[nodes[i]] = i;
+        std::vector<int> rp(m + 1, 0), ci;
+        for (int i = 0; i < m; ++i)
+        {
+            const int v = nodes[i];
+            for (size_t a = 0; a < adj[v].size(); ++a)
+                if (local[adj[v][a]] >= 0)
+                    ci.push_back(local[adj[v][a]]);
+            rp[i + 1] = (int)ci.size();
+        }
+        std::vector<int> o = minimum_degree_order(m, rp.data(), ci.data());
+        for (int i = 0; i < m; ++i)
+            order.push_back(nodes[o[i]]);
+        for (int i = 0; i < m; ++i)
+            local[nodes[i]] = -1;
+    };
+
+    // explicit stack of work items: a piece to dissect, or a separator to emit
+    struct Item { std::vector<int> nodes; bool emit; };
+    std::vector<Item> stack;
+    {
+        Item all;
+        all.emit = false;
+        for (int i = 0; i < n; ++i)
+            if (!dense[i])
+                all.nodes.push_back(i);
+        stack.push_back(std::move(all));
+    }
+    std::vector<int> visit, level_start, visit2, level_start2;
+    while (!stack.empty())
+    {
+        Item item = std::move(stack.back());
+        stack.pop_back();
+        if (item.emit)
+        {
+            order.insert(order.end(), item.nodes.begin(), item.nodes.end());
+            continue;
+        }
+        if (item.nodes.empty())
+            continue;
+        if ((int)item.nodes.size() <= leaf)
+        {
+            order_leaf(item.nodes);
+            continue;
+        }
+        const int id = next_part++;
+        for (size_t i = 0; i < item.nodes.size(); ++i)
+            part[item.nodes[i]] = id;
+        // connected component of the first node
+        bfs(item.nodes[0], id, visit, level_start);
+        if (visit.size() < item.nodes.size())
+        {
+            // not connected: this component and the rest are independent pieces
+            Item comp, rest;
+            comp.emit = rest.emit = false;
+            for (size_t i = 0; i < visit.size(); ++i)
+                local[visit[i]] = 1;
+            for (size_t i = 0; i < item.nodes.size(); ++i)
+                (local[item.nodes[i]] == 1 ? comp : rest).nodes.push_back(item.nodes[i]);
+            for (size_t i = 0; i < visit.size(); ++i)
+                local[visit[i]] = -1;
+            stack.push_back(std::move(rest));
+            stack.push_back(std::move(comp));
+            continue;
+        }
+        // pseudo-peripheral node: restart from a node of the last level while the depth grows
+        for (int tries = 0; tries < 4; ++tries)
+        {
+            const int last = visit.back();
+            bfs(last, id, visit2, level_start2);
+            const bool deeper = level_start2.size() > level_start.size();
+            visit.swap(visit2);
+            level_start.swap(level_start2);
+            if (!deeper)
+                break;
+        }
+        const int depth = (int)level_start.size() - 1;      // number of levels
+        if (depth < 3)
+        {
+            order_leaf(item.nodes);                        // a clique-like piece: nothing to cut
+            continue;
+        }
+        // the level where the running count crosses one half, never the first or last one
+        int cut = 1;
+        while (cut < depth - 2 && level_start[cut + 1] < (int)visit.size() / 2)
+            ++cut;
+        Item left, right, sep;
+        left.emit = right.emit = false;
+        sep.emit = true;
+        left.nodes.assign(visit.begin(), visit.begin() + level_start[cut]);
+        sep.nodes.assign(visit.begin() + level_start[cut], visit.begin() + level_start[cut + 1]);
+        right.nodes.assign(visit.begin() + level_start[cut + 1], visit.end());
+        stack.push_back(std::move(sep));                   // popped last: ordered after both sides
+        stack.push_back(std::move(right));
+        stack.push_back(std::move(left));
+    }
+    // dense rows last, lightest first
+    std::vector<std::pair<size_t, int> > last;
+    for (int i = 0; i < n; ++i)
+        if (dense[i])
+        {
+            size_t deg = 0;
+            for (int p = rowptr[i]; p < rowptr[i + 1]; ++p)
+                ++deg;
+            last.push_back(std::make_pair(deg, i));
+        }
+    std::sort(last.begin(), last.end());
+    for (size_t i = 0; i < last.size(); ++i)
+        order.push_back(last[i].second);
+    return order;
+}
+
+// Entries of the Cholesky factor of the pattern of A + A' under `order` (symbolic
+// factorisation by merging the structures of the children in the elimination
+// tree): the fill an LU with diagonal pivots would have in L and in U.
+long long symbolic_fill(int n, const int *rowptr, const int *colidx, const int *order)
+{
+    std::vector<std::vector<int> > adj;
+    std::vector<char> dense;
+    symmetric_graph(n, rowptr, colidx, (size_t)n + 1, adj, dense);
+    std::vector<int> pos(n);
+    for (int j = 0; j < n; ++j)
+        pos[order[j]] = j;
+    std::vector<std::vector<int> > structure(n), children(n);
+    std::vector<int> merged, tmp;
+    long long fill = 0;
+    for (int j = 0; j < n; ++j)
+    {
+        const int v = order[j];
+        merged.clear();
+        for (size_t a = 0; a < adj[v].size(); ++a)
+            if (pos[adj[v][a]] > j)
+                merged.push_back(pos[adj[v][a]]);
+        std::sort(merged.begin(), merged.end());
+        for (size_t c = 0; c < children[j].size(); ++c)
+        {
+            std::vector<int> &sc = structure[children[j][c]];
+            tmp.clear();
+            size_t x = 0, y = 0;
+            while (x < merged.size() || y < sc.size())
+            {
+                int w;
+                if (y == sc.size() || (x < merged.size() && merged[x] < sc[y]))
+                    w = merged[x++];
+                else if (x == merged.size() || sc[y] < merged[x])
+                    w = sc[y++];
+                else
+                {
+                    w = merged[x++];
+                    ++y;
+                }
+                if (w > j)
+                    tmp.push_back(w);
+            }
+            merged.swap(tmp);
+            std::vector<int>().swap(sc);           // the child's structure is not needed again
+        }
+        fill += (long long)merged.size();
+        if (!merged.empty())
+            children[merged[0]].push_back(j);
+        structure[j] = merged;
+    }
+    return fill;
+}
+
 int SparseLU::factor(int n_in, const int *rowptr, const int *colidx, const double *vals,
                      double pivot_threshold, const int *order)
 {
@@ -138,7 +392,18 @@ int SparseLU::factor(int n_in, const int *rowptr, const int *colidx, const doubl
     if (order)
         q.assign(order, order + n);
     else
-        q = minimum_degree_order(n, rowptr, colidx);
+    {
+        // nested dissection wins on mesh-like graphs (less fill, bushier elimination
+        // tree, O(n log n)), minimum degree on irregular ones; where the latter is
+        // affordable both are computed and the one with the smaller symbolic fill taken
+        q = nested_dissection_order(n, rowptr, colidx);
+        if (n <= compare_orderings_up_to)
+        {
+            std::vector<int> md = minimum_degree_order(n, rowptr, colidx);
+            if (symbolic_fill(n, rowptr, colidx, md.data()) < symbolic_fill(n, rowptr, colidx, q.data()))
+                q.swap(md);
+        }
+    }
 
     pinv.assign(n, -1);
     Lp.assign(1, 0);

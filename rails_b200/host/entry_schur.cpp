@@ -178,6 +178,12 @@ void rails_host_minimum_degree(int n, const int *rowptr, const int *colidx, int 
     std::memcpy(order, o.data(), sizeof(int) * n);
 }
 
+void rails_host_nested_dissection(int n, const int *rowptr, const int *colidx, int leaf, int *order)
+{
+    std::vector<int> o = nested_dissection_order(n, rowptr, colidx, leaf);
+    std::memcpy(order, o.data(), sizeof(int) * n);
+}
+
 // Solves with those factors ON THE GPU: x (n x nrhs host block, ld) is uploaded,
 // solved `repeat` times from the same right-hand side (timed with CUDA events
 // on the library stream, average returned in *ms_per_solve) and downloaded.

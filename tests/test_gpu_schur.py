@@ -60,8 +60,8 @@ def test_device_lu_solve(gpu, name, nrhs):
 
 
 def test_device_lu_levels_are_a_few_launches(gpu):
-    """A 2-D Laplacian under minimum degree: hundreds of levels, yet a solve is a
-    handful of kernels (runs of small levels are walked by one CTA)."""
+    """A 2-D Laplacian under a fill-reducing ordering: hundreds of levels, yet a solve
+    is a few dozen kernels (runs of small levels are walked by one CTA)."""
     rp, ci, v = problems.laplacian(96, 2)
     lu = gpu.SparseLU(rp, ci, v)
     b = np.random.RandomState(0).uniform(-1, 1, (rp.size - 1, 4))
@@ -69,8 +69,8 @@ def test_device_lu_levels_are_a_few_launches(gpu):
     A = sp.csr_matrix((v, ci, rp))
     assert np.linalg.norm(A @ x - b) < 1e-10 * np.linalg.norm(b)
     st = lu.device_stats
-    assert max(st["levels"]) > 400
-    assert st["launches_per_solve"] < max(st["levels"]) // 5
+    assert max(st["levels"]) > 200
+    assert st["launches_per_solve"] < max(st["levels"]) // 3
 
 
 def test_gather_scatter_rows(gpu):

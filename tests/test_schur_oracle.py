@@ -138,7 +138,7 @@ def test_host_lu_solves(name):
     if name == "saddle":
         assert lu.off_diagonal_pivots > 0
     if name == "laplace2d":
-        # minimum degree keeps the fill well below a banded factorisation's 2 n g
+        # the ordering keeps the fill well below a banded factorisation's 2 n g
         assert lu.nnz_l + lu.nnz_u < 0.5 * 2 * n * 40
 
 
@@ -146,6 +146,34 @@ def test_host_lu_reports_singular():
     A = sp.csr_matrix(np.array([[1.0, 2.0, 0.0], [2.0, 4.0, 0.0], [0.0, 0.0, 1.0]]))
     lu = api.SparseLU(A.indptr, A.indices, A.data)
     assert lu.info > 0
+
+
+def test_orderings_and_their_selection():
+    """Nested dissection fills less than minimum degree on a grid and more on an
+    irregular graph; the factorisation takes whichever fills less (symbolic count)."""
+    rp, ci, v = problems.convection_diffusion(48, 2)
+    n = rp.size - 1
+    for order in (api.minimum_degree(rp, ci), api.nested_dissection(rp, ci)):
+        assert sorted(order.tolist()) == list(range(n))
+    md = api.SparseLU(rp, ci, v, order=api.minimum_degree(rp, ci))
+    nd = api.SparseLU(rp, ci, v, order=api.nested_dissection(rp, ci))
+    auto = api.SparseLU(rp, ci, v)
+    assert auto.nnz_l + auto.nnz_u == min(md.nnz_l + md.nnz_u, nd.nnz_l + nd.nnz_u)
+    A = lu_cases()["random1500"]
+    A.sort_indices()
+    md = api.SparseLU(A.indptr, A.indices, A.data, order=api.minimum_degree(A.indptr, A.indices))
+    nd = api.SparseLU(A.indptr, A.indices, A.data, order=api.nested_dissection(A.indptr, A.indices))
+    auto = api.SparseLU(A.indptr, A.indices, A.data)
+    assert md.nnz_l + md.nnz_u < nd.nnz_l + nd.nnz_u
+    # pivoting moves a few entries; the choice follows the symbolic count
+    assert auto.nnz_l + auto.nnz_u <= 1.05 * (md.nnz_l + md.nnz_u)
+    # a disconnected graph and a tiny one go through the same code
+    B = sp.block_diag([sp.csr_matrix((v, ci, rp)), sp.eye(5), sp.csr_matrix((v, ci, rp))], format="csr")
+    o = api.nested_dissection(B.indptr, B.indices, leaf=50)
+    assert sorted(o.tolist()) == list(range(B.shape[0]))
+    lu = api.SparseLU(B.indptr, B.indices, B.data, order=o)
+    b = np.ones((B.shape[0], 1))
+    assert np.linalg.norm(B @ lu.solve(b) - b) < 1e-10 * np.linalg.norm(b)
 
 
 def test_minimum_degree_defers_dense_rows():

@@ -343,7 +343,7 @@ sptrsv_level_kernel(const int4 *__restrict__ rowinfo, const int *__restrict__ co
 }
 
 // Step 2 of a chain: windows w0 .. w1 walked by one CTA for right-hand sides
-// c0 .. c0 + ct (ct <= CHAIN_COLS); row_base = first row (level order) of the chain.
+// c0 .. c0 + CT (CT <= CHAIN_COLS).
 struct WindowStage
 {
     int lvl[WIN_LEVELS + 1];     // row offsets of the window's levels

@@ -65,6 +65,19 @@ def test_fails_loudly_without_gpu():
     assert lib.rails_mv_alloc(10, 1, 0, ctypes.byref(h)) == 3   # RAILS_ERR_STATE
     with pytest.raises(api.RailsError):
         api.init(0)
+    # the singular-mass path as well: no device solves, no Schur operator, no solve
+    import numpy as np
+    one_i, one_d = np.zeros(2, dtype=np.int32), np.ones(1)
+    assert lib.rails_lu_create(1, api.iptr(one_i), api.iptr(one_i), api.dptr(one_d), api.iptr(np.array([0, 1], dtype=np.int32)),
+                               api.iptr(one_i), api.dptr(one_d), api.iptr(one_i), api.iptr(one_i), ctypes.byref(h)) == 3
+    assert lib.rails_idx_create(1, api.iptr(one_i), ctypes.byref(h)) == 3
+    t = ctypes.c_double(0)
+    assert lib.rails_cuda_fp64_peak(0, ctypes.byref(t)) == 3
+    rp, ci, v = np.array([0, 1, 2], dtype=np.int32), np.array([0, 1], dtype=np.int32), np.array([-1.0, -2.0])
+    with pytest.raises(api.RailsError):
+        api.SchurOperator(rp, ci, v, np.array([0.0, 1.0]))
+    q = api.solve_schur(rp, ci, v, np.array([0.0, 1.0]), np.ones((2, 1)), {"Tolerance": 1e-4})
+    assert q["ret"] == 200
 
 
 def test_partition_rows_matches_epetra_linear_map():

@@ -1,0 +1,28 @@
+"""Host code under AddressSanitizer + UndefinedBehaviorSanitizer (SURVEY.md §5:
+"ASan/UBSan on the host shim"): the sparse LU factorisation and its orderings,
+the newest host code with the most pointer arithmetic (depth-first reach, merges
+of adjacency lists, the dissection stack)."""
+import os
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.skipif(shutil.which("g++") is None, reason="no g++")
+def test_sparse_lu_is_clean_under_asan_and_ubsan(tmp_path):
+    exe = str(tmp_path / "sparse_lu_sanitize")
+    cmd = ["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all",
+           "-fno-omit-frame-pointer", "-I" + os.path.join(ROOT, "rails_b200", "host"),
+           os.path.join(ROOT, "tests", "cpp", "sparse_lu_sanitize.cpp"),
+           os.path.join(ROOT, "rails_b200", "host", "SparseLU.cpp"), "-o", exe]
+    b = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if b.returncode != 0 and "sanitize" in b.stdout:
+        pytest.skip("sanitizer runtime not available: " + b.stdout[-200:])
+    assert b.returncode == 0, b.stdout[-2000:]
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert r.stdout.strip().endswith("OK")
+    assert "runtime error" not in r.stdout and "AddressSanitizer" not in r.stdout

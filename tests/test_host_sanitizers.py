@@ -26,3 +26,26 @@ def test_sparse_lu_is_clean_under_asan_and_ubsan(tmp_path):
     assert r.returncode == 0, r.stdout[-3000:]
     assert r.stdout.strip().endswith("OK")
     assert "runtime error" not in r.stdout and "AddressSanitizer" not in r.stdout
+
+
+@pytest.mark.skipif(shutil.which("nvcc") is None, reason="no nvcc")
+def test_device_schedule_planner_is_clean_under_asan(tmp_path):
+    """plan_triangle (host code inside csrc/sptrsv.cu) through rails_lu_plan_emulate:
+    no CUDA call, so it runs here; compiled with the host compiler's ASan."""
+    import glob
+    exe = str(tmp_path / "lu_plan_sanitize")
+    srcs = sorted(glob.glob(os.path.join(ROOT, "rails_b200", "csrc", "*.cu")))
+    cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-g", "-std=c++17", "-w",
+           "-Xcompiler", "-fsanitize=address,-fno-omit-frame-pointer,-fPIC",
+           "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "rails_b200", "csrc"),
+           "-I" + os.path.join(ROOT, "rails_b200", "host"),
+           os.path.join(ROOT, "tests", "cpp", "lu_plan_sanitize.cpp"),
+           os.path.join(ROOT, "rails_b200", "host", "SparseLU.cpp")] + srcs + ["-lnccl", "-o", exe]
+    b = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if b.returncode != 0 and ("sanitize" in b.stdout or "asan" in b.stdout):
+        pytest.skip("sanitizer runtime not available: " + b.stdout[-200:])
+    assert b.returncode == 0, b.stdout[-2000:]
+    env = dict(os.environ, ASAN_OPTIONS="protect_shadow_gap=0:detect_leaks=0")
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert r.stdout.strip().endswith("OK") and "AddressSanitizer" not in r.stdout

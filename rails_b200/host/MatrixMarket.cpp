@@ -1,5 +1,7 @@
 #include "MatrixMarket.hpp"
 
+#include <exception>
+
 #include <algorithm>
 #include <cctype>
 #include <cerrno>
@@ -158,7 +160,7 @@ struct Triple
 
 }
 
-int read_size(std::string const &path, long long &rows, long long &cols, std::string &err)
+static int read_size_unguarded(std::string const &path, long long &rows, long long &cols, std::string &err)
 {
     FILE *f = std::fopen(path.c_str(), "rb");
     if (!f)
@@ -184,7 +186,7 @@ int read_size(std::string const &path, long long &rows, long long &cols, std::st
     return 0;
 }
 
-int read_crs(std::string const &path, CsrHost &out, std::string &err,
+static int read_crs_unguarded(std::string const &path, CsrHost &out, std::string &err,
              long long row_begin, long long row_end)
 {
     std::vector<char> buf;
@@ -219,8 +221,15 @@ int read_crs(std::string const &path, CsrHost &out, std::string &err,
     }
     const long long local = row_end - row_begin;
 
+    // an entry takes at least four bytes ("1 1\n"): a size line that promises more
+    // than the file can hold is corrupt, and must not drive an allocation
+    if (nz > (long long)buf.size())
+    {
+        err = path + ": the size line promises more entries than the file holds";
+        return 1;
+    }
     std::vector<Triple> entries;
-    entries.reserve((size_t)std::min<long long>(nz * (b.symmetry ? 2 : 1), (1LL << 31)));
+    entries.reserve((size_t)(nz * (b.symmetry ? 2 : 1)));
     for (long long e = 0; e < nz; ++e)
     {
         long long i = 0, j = 0;
@@ -290,7 +299,7 @@ int read_crs(std::string const &path, CsrHost &out, std::string &err,
     return 0;
 }
 
-int read_dense(std::string const &path, int &rows, int &cols, std::vector<double> &data,
+static int read_dense_unguarded(std::string const &path, int &rows, int &cols, std::vector<double> &data,
                std::string &err)
 {
     std::vector<char> buf;
@@ -304,6 +313,14 @@ int read_dense(std::string const &path, int &rows, int &cols, std::vector<double
     if (!next_int(p, m) || !next_int(p, n) || m < 0 || n < 0 || m > 2147483647LL || n > 2147483647LL)
     {
         err = path + ": bad size line";
+        return 1;
+    }
+    // array format: every value takes at least two bytes; a coordinate file is
+    // accepted for convenience only, for blocks that fit a sane dense size
+    if ((!b.coordinate && (m > 0 && n > (long long)buf.size() / m)) ||
+        (b.coordinate && m > 0 && n > (1LL << 28) / m))
+    {
+        err = path + ": the size line promises more values than the file holds";
         return 1;
     }
     rows = (int)m;
@@ -360,6 +377,38 @@ int read_dense(std::string const &path, int &rows, int &cols, std::vector<double
                 data[(size_t)j + (size_t)i * (size_t)m] = b.symmetry == 2 ? -v : v;
         }
     return 0;
+}
+
+// No exception leaves the readers (the reference's error style is an int code,
+// src/LyapunovMacros.hpp:7-26): an allocation a corrupt file still manages to
+// provoke becomes an error message.
+template<class F>
+static int guarded(std::string const &path, std::string &err, F body)
+{
+    try
+    {
+        return body();
+    }
+    catch (std::exception const &e)
+    {
+        err = path + ": " + e.what();
+        return 1;
+    }
+}
+
+int read_size(std::string const &path, long long &rows, long long &cols, std::string &err)
+{
+    return guarded(path, err, [&] { return read_size_unguarded(path, rows, cols, err); });
+}
+
+int read_crs(std::string const &path, CsrHost &out, std::string &err, long long row_begin, long long row_end)
+{
+    return guarded(path, err, [&] { return read_crs_unguarded(path, out, err, row_begin, row_end); });
+}
+
+int read_dense(std::string const &path, int &rows, int &cols, std::vector<double> &data, std::string &err)
+{
+    return guarded(path, err, [&] { return read_dense_unguarded(path, rows, cols, data, err); });
 }
 
 int write_dense(std::string const &path, int rows, int cols, const double *data, long long ld,

@@ -1,5 +1,7 @@
 #include "ParameterFile.hpp"
 
+#include <exception>
+
 #include <cctype>
 #include <cerrno>
 #include <cstdio>
@@ -435,7 +437,15 @@ int ParameterTree::from_file(std::string const &path, ParameterTree &out, std::s
     std::fclose(f);
     size_t i = 0;
     while (i < text.size() && std::isspace((unsigned char)text[i])) ++i;
-    int rc = (i < text.size() && text[i] == '<') ? from_xml(text, out, err) : from_ini(text, out, err);
+    int rc = 1;
+    try
+    {
+        rc = (i < text.size() && text[i] == '<') ? from_xml(text, out, err) : from_ini(text, out, err);
+    }
+    catch (std::exception const &e)          // no exception leaves the reader
+    {
+        err = e.what();
+    }
     if (rc)
         err = path + ": " + err;
     return rc;

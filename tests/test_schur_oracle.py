@@ -234,3 +234,41 @@ def test_projection_method_needs_an_inverse_and_a_valid_value():
     base = {"Tolerance": 1e-4, "Expand size": 1, "Lanczos iterations": 5}
     assert harness.stl_solve_ext(rp, ci, v, B, dict(base, **{"Projection method": 2.2}))["ret"] == 1
     assert harness.stl_solve_ext(rp, ci, v, B, dict(base, **{"Projection method": 3.1}))["ret"] == 101
+
+
+def test_host_lu_on_random_small_matrices():
+    """Property test of the factorisation with pivoting: for random small sparse
+    matrices (zero diagonals, duplicate-free, some singular) either the solve
+    reproduces numpy's to the conditioning of the matrix, or the matrix is
+    reported singular exactly when it is structurally or numerically rank
+    deficient."""
+    rs = np.random.RandomState(12345)
+    solved = singular = 0
+    for trial in range(300):
+        n = rs.randint(1, 40)
+        dens = rs.uniform(0.05, 0.5)
+        D = rs.uniform(-1, 1, (n, n)) * (rs.rand(n, n) < dens)
+        if trial % 3:
+            D[np.arange(n), np.arange(n)] += rs.uniform(0.5, 2.0, n) * rs.choice([-1, 1], n)
+        if trial % 7 == 0 and n > 2:
+            D[rs.randint(n)] = 0.0                          # an empty row: singular
+        A = sp.csr_matrix(D)
+        A.sort_indices()
+        lu = api.SparseLU(A.indptr, A.indices, A.data)
+        sv = np.linalg.svd(D, compute_uv=False)
+        cond = sv[0] / sv[-1] if sv[-1] > 0 else np.inf
+        if lu.info != 0:
+            singular += 1
+            assert cond > 1e12, (trial, n, cond)
+            continue
+        if cond > 1e10:
+            continue                                        # factorised, but nothing to compare against
+        solved += 1
+        b = rs.uniform(-1, 1, (n, 2))
+        for trans in (False, True):
+            x = lu.solve(b, trans)
+            want = np.linalg.solve(D.T if trans else D, b)
+            assert np.linalg.norm(x - want) <= 1e-13 * cond * np.linalg.norm(want) + 1e-14, (trial, n, cond)
+            xe = lu.emulate_device_schedule(b, trans)
+            assert np.linalg.norm(xe - x) <= 1e-13 * cond * np.linalg.norm(x) + 1e-14
+    assert solved > 100 and singular > 10

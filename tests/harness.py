@@ -43,7 +43,9 @@ def oracle():
 
 
 def ref_path():
-    return os.path.join(ROOT, "oracle", "_ref", "librails_ref_stl.so")
+    # RAILS_REF_STL_LIB: an instrumented build of the same library
+    # (tests/test_host_sanitizers.py runs the solver-loop tests against an ASan build)
+    return os.environ.get("RAILS_REF_STL_LIB") or os.path.join(ROOT, "oracle", "_ref", "librails_ref_stl.so")
 
 
 def ref():

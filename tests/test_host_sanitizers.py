@@ -32,9 +32,10 @@ def test_sparse_lu_is_clean_under_asan_and_ubsan(tmp_path):
 def test_device_schedule_planner_is_clean_under_asan(tmp_path):
     """plan_triangle (host code inside csrc/sptrsv.cu) through rails_lu_plan_emulate:
     no CUDA call, so it runs here; compiled with the host compiler's ASan."""
-    import glob
     exe = str(tmp_path / "lu_plan_sanitize")
-    srcs = sorted(glob.glob(os.path.join(ROOT, "rails_b200", "csrc", "*.cu")))
+    # sptrsv.cu and what it links against (context, reductions, blas-1)
+    srcs = [os.path.join(ROOT, "rails_b200", "csrc", f)
+            for f in ("sptrsv.cu", "context.cu", "exchange.cu", "blas1.cu")]
     cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-g", "-std=c++17", "-w",
            "-Xcompiler", "-fsanitize=address,-fno-omit-frame-pointer,-fPIC",
            "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "rails_b200", "csrc"),
@@ -72,3 +73,45 @@ def test_file_readers_survive_corrupt_input_under_asan_and_ubsan(tmp_path):
     assert r.returncode == 0, r.stdout[-3000:]
     assert r.stdout.strip().endswith("OK")
     assert "runtime error" not in r.stdout and "AddressSanitizer" not in r.stdout
+
+
+REF = "/root/reference"
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")), reason="reference tree absent (GPU box)")
+def test_solver_loop_is_clean_under_asan(tmp_path):
+    """The product's solver loop (RailsSolverImpl.hpp, RailsCoefficientSpace.hpp: the
+    MATLAB options, residual methods 1 and 2, projection methods) over the
+    reference's StlWrapper, built with AddressSanitizer; a subset of the CPU solver
+    tests is run against that build in a child process."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import build_ref
+    libdir, blas = build_ref.openblas_path()
+    lib = str(tmp_path / "librails_ref_stl_asan.so")
+    srcs = [os.path.join(REF, "src", f) for f in
+            ("StlWrapper.cpp", "StlVector.cpp", "LapackWrapper.cpp", "SlicotWrapper.cpp", "Timer.cpp")]
+    cmd = ["g++", "-std=c++14", "-O2", "-g", "-fPIC", "-shared", "-fopenmp", "-fsanitize=address",
+           "-fno-omit-frame-pointer", "-I" + REF, "-I" + os.path.join(ROOT, "oracle"),
+           "-I" + os.path.join(ROOT, "rails_b200", "host"), "-o", lib,
+           os.path.join(ROOT, "oracle", "ref_entry_stl.cpp")] + srcs + [
+           os.path.join(ROOT, "rails_b200", "host", "sb03md_shim.cpp"), blas,
+           "-Wl,--disable-new-dtags,-rpath," + libdir]
+    b = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if b.returncode != 0 and "sanitize" in b.stdout:
+        pytest.skip("sanitizer runtime not available: " + b.stdout[-200:])
+    assert b.returncode == 0, b.stdout[-2000:]
+    asan = subprocess.run(["g++", "-print-file-name=libasan.so"], stdout=subprocess.PIPE, text=True).stdout.strip()
+    if not os.path.isabs(asan) or not os.path.exists(asan):
+        pytest.skip("libasan.so not found")
+    env = dict(os.environ, LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0:verify_asan_link_order=0",
+               RAILS_REF_STL_LIB=lib, OPENBLAS_NUM_THREADS="1")
+    tests = ["tests/test_solver_loop.py",
+             "tests/test_schur_oracle.py::test_projection_methods_follow_matlab_restatement",
+             "tests/test_matlab_features.py::test_product_loop_follows_matlab_restatement",
+             "tests/test_matlab_features.py::test_exact_residual_eigenpairs_at_every_iteration"]
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-p", "no:cacheprovider"] + tests,
+                       cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1200)
+    tail = "\n".join(line for line in r.stdout.splitlines() if not line.startswith("Warning"))[-3000:]
+    assert "AddressSanitizer" not in r.stdout, tail
+    assert r.returncode == 0, tail

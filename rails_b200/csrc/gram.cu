@@ -282,6 +282,12 @@ int launch_gemm_dmma(const double *V, long long ldv, int k, const double *dC, in
     const int kpad = (k + 3) & ~3;
     const size_t smem = (size_t)kpad * (NB * 8 + 1) * sizeof(double);
     static size_t configured = 0;
+    static int configured_device = -1;          // the attribute is per device
+    if (configured_device != cx.device)
+    {
+        configured = 0;
+        configured_device = cx.device;
+    }
     if (smem > configured)
     {
         RAILS_CUDA_TRY(cudaFuncSetAttribute(gemm_dmma_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -620,8 +620,8 @@ int launches_of(const Triangle &T, int nc)
 
 int sweep(const Triangle &T, double *X, long long ld, int nc)
 {
-    static bool configured = false;
-    if (!configured)
+    static int configured_device = -1;          // the attribute is per device
+    if (configured_device != ctx().device)
     {
         RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)sizeof(ChainShared)));
@@ -631,7 +631,7 @@ int sweep(const Triangle &T, double *X, long long ld, int nc)
                                             (int)sizeof(ChainShared)));
         RAILS_CUDA_TRY(cudaFuncSetAttribute(sptrsv_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)sizeof(ChainShared)));
-        configured = true;
+        configured_device = ctx().device;
     }
     const int warps_per_cta = LEVEL_THREADS / 32;
     for (size_t s = 0; s < T.segments.size(); ++s)

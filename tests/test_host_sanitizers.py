@@ -115,3 +115,27 @@ def test_solver_loop_is_clean_under_asan(tmp_path):
     tail = "\n".join(line for line in r.stdout.splitlines() if not line.startswith("Warning"))[-3000:]
     assert "AddressSanitizer" not in r.stdout, tail
     assert r.returncode == 0, tail
+
+
+@pytest.mark.skipif(shutil.which("g++") is None, reason="no g++")
+def test_host_dense_matrix_conformance_under_asan_and_ubsan(tmp_path):
+    """HostDenseMatrix against the known answers of the reference's typed conformance
+    suite for the DenseMatrix concept (test/GenericDenseMatrixWrapper_test.cpp:61-206),
+    under the sanitizers."""
+    from rails_b200 import build as product_build
+    libdir, blas = product_build.openblas_path()
+    exe = str(tmp_path / "dense_matrix_conformance")
+    host = os.path.join(ROOT, "rails_b200", "host")
+    cmd = ["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all",
+           "-fno-omit-frame-pointer", "-I" + host, os.path.join(ROOT, "tests", "cpp", "dense_matrix_conformance.cpp"),
+           os.path.join(host, "HostDenseMatrix.cpp"), blas, "-Wl,--disable-new-dtags,-rpath," + libdir, "-o", exe]
+    b = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if b.returncode != 0 and "sanitize" in b.stdout:
+        pytest.skip("sanitizer runtime not available: " + b.stdout[-200:])
+    assert b.returncode == 0, b.stdout[-2000:]
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0", OPENBLAS_NUM_THREADS="1",
+               LD_LIBRARY_PATH=libdir + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert r.stdout.strip().endswith("OK")
+    assert "runtime error" not in r.stdout and "AddressSanitizer" not in r.stdout

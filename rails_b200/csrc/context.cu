@@ -3,7 +3,9 @@
 
 #include <algorithm>
 #include <cstring>
+#include <map>
 #include <thread>
+#include <unordered_map>
 
 #include <cstdarg>
 #include <cstring>
@@ -50,6 +52,101 @@ static int grow(double **p, size_t *cap, size_t need)
 }
 
 int ensure_partial(size_t doubles) { return grow(&ctx().d_partial, &ctx().partial_cap, doubles); }
+
+// ---- device block cache --------------------------------------------------------
+// Multivector buffers (V, AV, MV at capacity; the m x c temporaries the wrapper
+// API creates every iteration) and operator arrays come from cudaMalloc and go
+// back into a size-keyed free list instead of to the driver.  Round 1 used the
+// stream-ordered pool (cudaMallocAsync): identical solves then differed by single
+// iterations of 100-850 ms (restart temporaries of a few GB made the pool remap
+// physical memory; scripts/window_variability.py, profiles/r02_window_variability.md).
+// Everything that touches these buffers is enqueued on the ONE library stream, so
+// a block can be handed out again as soon as it has been returned.
+namespace
+{
+std::multimap<size_t, void *> g_free_blocks;        // size -> block
+std::unordered_map<void *, size_t> g_live_blocks;   // block handed out -> its size
+size_t g_free_bytes = 0;
+
+size_t round_block(size_t bytes)
+{
+    // 512 B granules below 1 MiB, 2 MiB granules above (the driver's own page size)
+    const size_t g = bytes < (1u << 20) ? 512 : (2u << 20);
+    return (std::max<size_t>(bytes, 1) + g - 1) / g * g;
+}
+}
+
+void dev_cache_release()
+{
+    Context &c = ctx();
+    if (c.stream) cudaStreamSynchronize(c.stream);
+    for (auto &kv : g_free_blocks)
+        cudaFree(kv.second);
+    g_free_blocks.clear();
+    g_free_bytes = 0;
+}
+
+int dev_alloc(void **p, size_t bytes)
+{
+    const size_t want = round_block(bytes);
+    // smallest cached block that fits without wasting more than a quarter of it
+    auto it = g_free_blocks.lower_bound(want);
+    if (it != g_free_blocks.end() && it->first <= want + want / 4 + (1u << 20))
+    {
+        *p = it->second;
+        g_live_blocks[*p] = it->first;
+        g_free_bytes -= it->first;
+        g_free_blocks.erase(it);
+        return RAILS_OK;
+    }
+    cudaError_t e = cudaMalloc(p, want);
+    if (e == cudaErrorMemoryAllocation)
+    {
+        // cached blocks of other sizes (a capacity growth leaves the old V, AV
+        // behind) are in the way: give them back and retry
+        cudaGetLastError();
+        dev_cache_release();
+        e = cudaMalloc(p, want);
+    }
+    if (e != cudaSuccess)
+    {
+        cudaGetLastError();
+        return fail(RAILS_ERR_CUDA, "cudaMalloc(%zu bytes): %s", want, cudaGetErrorString(e));
+    }
+    g_live_blocks[*p] = want;
+    return RAILS_OK;
+}
+
+void dev_free(void *p)
+{
+    if (!p) return;
+    auto live = g_live_blocks.find(p);
+    if (live == g_live_blocks.end())
+    {
+        fail(RAILS_ERR_STATE, "dev_free: %p was not handed out by dev_alloc", p);
+        return;
+    }
+    const size_t granted = live->second;
+    g_live_blocks.erase(live);
+    g_free_blocks.emplace(granted, p);
+    g_free_bytes += granted;
+    // bound what the cache may hoard: beyond half of the device memory the
+    // largest blocks go back to the driver (they are the least likely to be reused)
+    static size_t limit = 0;
+    if (!limit)
+    {
+        size_t fr = 0, tot = 0;
+        limit = cudaMemGetInfo(&fr, &tot) == cudaSuccess ? tot / 2 : (size_t)64 << 30;
+    }
+    while (g_free_bytes > limit && !g_free_blocks.empty())
+    {
+        auto last = std::prev(g_free_blocks.end());
+        cudaStreamSynchronize(ctx().stream);
+        cudaFree(last->second);
+        g_free_bytes -= last->first;
+        g_free_blocks.erase(last);
+    }
+}
 
 int upload_small(const double *host, int k, int c, int ldc, const double **d_out)
 {
@@ -221,12 +318,6 @@ extern "C" int rails_cuda_init(int device)
     c.sm_count = prop.multiProcessorCount;
     RAILS_CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     RAILS_CUDA_TRY(cudaStreamCreateWithFlags(&c.comm_stream, cudaStreamNonBlocking));
-    // keep freed blocks in the stream-ordered pool: the wrappers create many
-    // m x 1 temporaries per iteration
-    cudaMemPool_t pool;
-    RAILS_CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, device));
-    unsigned long long thresh = ~0ull;
-    RAILS_CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
     c.events.assign(64, nullptr);
     c.ready = true;
     int rc = rails::ensure_small(65536);
@@ -248,6 +339,7 @@ extern "C" int rails_cuda_finalize(void)
     if (!c.ready)
         return RAILS_OK;
     cudaStreamSynchronize(c.stream);
+    rails::dev_cache_release();
     rails::release_mailboxes();
     if (c.comm) { ncclCommDestroy(c.comm); c.comm = nullptr; }
     for (auto &ev : c.events)
@@ -394,25 +486,14 @@ extern "C" int rails_mv_alloc(long long rows, int cols, int flags, rails_mv_t *o
     mv->cols = cols;
     mv->flags = flags;
     mv->bytes = (size_t)mv->ld * (size_t)(cols > 0 ? cols : 1) * sizeof(double);
-    cudaError_t e = cudaMallocAsync(&mv->data, mv->bytes, ctx().stream);
-    if (e == cudaErrorMemoryAllocation)
-    {
-        // The pool keeps every freed block (release threshold = max), and blocks
-        // freed by a capacity growth (V, AV: +100 columns at a time) are too small
-        // for the next, larger request: give the cached memory back and retry.
-        cudaGetLastError();
-        cudaStreamSynchronize(ctx().stream);
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, ctx().device) == cudaSuccess)
-            cudaMemPoolTrimTo(pool, 0);
-        e = cudaMallocAsync(&mv->data, mv->bytes, ctx().stream);
-    }
-    if (e != cudaSuccess)
+    void *block = nullptr;
+    int rc = rails::dev_alloc(&block, mv->bytes);
+    if (rc)
     {
         delete mv;
-        return rails::fail(RAILS_ERR_CUDA, "cudaMallocAsync(%zu bytes): %s",
-                           (size_t)((rows + 15) / 16 * 16) * cols * 8, cudaGetErrorString(e));
+        return rc;
     }
+    mv->data = static_cast<double *>(block);
     ctx().bytes_in_use.fetch_add((long long)mv->bytes);
     *out = mv;
     return RAILS_OK;
@@ -424,7 +505,7 @@ extern "C" int rails_mv_free(rails_mv_t mv)
         return RAILS_OK;
     if (ctx().ready && mv->data)
     {
-        RAILS_CUDA_TRY(cudaFreeAsync(mv->data, ctx().stream));
+        rails::dev_free(mv->data);
         ctx().bytes_in_use.fetch_sub((long long)mv->bytes);
     }
     delete mv;

@@ -118,6 +118,20 @@ struct Context
 
 Context &ctx();
 int fail(int code, const char *fmt, ...);
+// Device blocks from a size-keyed cache over cudaMalloc (context.cu): freed
+// blocks are kept and handed out again to requests of (nearly) the same size.
+// Everything using them is ordered on the one library stream, which makes
+// immediate reuse safe.
+int dev_alloc(void **p, size_t bytes);
+template<class T> int dev_alloc_t(T **p, size_t bytes)
+{
+    void *v = nullptr;
+    int rc = dev_alloc(&v, bytes);
+    *p = static_cast<T *>(v);
+    return rc;
+}
+void dev_free(void *p);
+void dev_cache_release();
 int ensure_partial(size_t doubles);
 int ensure_small(size_t doubles);
 // Copies a small host block (column-major k x c, ldc) into the pinned ring and

@@ -243,10 +243,11 @@ void free_csr(rails_csr_s *A)
     if (A->transposed) free_csr(A->transposed);
     if (ctx().ready)
     {
-        cudaFree(A->rowptr); cudaFree(A->colidx); cudaFree(A->vals); cudaFree(A->blk_row);
-        if (A->send_rows) cudaFree(A->send_rows);
-        if (A->send_buf) cudaFree(A->send_buf);
-        if (A->ghost_buf) cudaFree(A->ghost_buf);
+        rails::dev_free(A->rowptr); rails::dev_free(A->colidx); rails::dev_free(A->vals);
+        rails::dev_free(A->blk_row);
+        rails::dev_free(A->send_rows);
+        rails::dev_free(A->send_buf);
+        rails::dev_free(A->ghost_buf);
         ctx().bytes_in_use.fetch_sub((long long)A->bytes);
     }
     delete A;
@@ -282,10 +283,11 @@ int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const doubl
     // 64 bytes of slack: bulk copies are rounded up to 16 bytes
     size_t b_rp = (size_t)(rows + 1) * sizeof(int), b_ci = (size_t)nnz * sizeof(int) + 64,
            b_v = (size_t)nnz * sizeof(double) + 64, b_blk = blk.size() * sizeof(int);
-    RAILS_CUDA_TRY(cudaMalloc(&A->rowptr, b_rp));
-    RAILS_CUDA_TRY(cudaMalloc(&A->colidx, b_ci));
-    RAILS_CUDA_TRY(cudaMalloc(&A->vals, b_v));
-    RAILS_CUDA_TRY(cudaMalloc(&A->blk_row, b_blk));
+    int rca = rails::dev_alloc_t(&A->rowptr, b_rp);
+    if (!rca) rca = rails::dev_alloc_t(&A->colidx, b_ci);
+    if (!rca) rca = rails::dev_alloc_t(&A->vals, b_v);
+    if (!rca) rca = rails::dev_alloc_t(&A->blk_row, b_blk);
+    if (rca) return rca;
     A->bytes += b_rp + b_ci + b_v + b_blk;
     ctx().bytes_in_use.fetch_add((long long)(b_rp + b_ci + b_v + b_blk));
     int rc = rails::copy_h2d(A->rowptr, rowptr, b_rp);
@@ -330,11 +332,12 @@ int owner_of(long long gcol, long long m, int P)
 int ensure_halo_cols(rails_csr_s *A, int ncols)
 {
     if (ncols <= A->halo_cols_cap) return RAILS_OK;
-    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
-    if (A->send_buf) { RAILS_CUDA_TRY(cudaFree(A->send_buf)); A->send_buf = nullptr; }
-    if (A->ghost_buf) { RAILS_CUDA_TRY(cudaFree(A->ghost_buf)); A->ghost_buf = nullptr; }
-    if (A->nsend) RAILS_CUDA_TRY(cudaMalloc(&A->send_buf, (size_t)A->nsend * ncols * sizeof(double)));
-    if (A->nghost) RAILS_CUDA_TRY(cudaMalloc(&A->ghost_buf, (size_t)A->nghost * ncols * sizeof(double)));
+    rails::dev_free(A->send_buf); A->send_buf = nullptr;
+    rails::dev_free(A->ghost_buf); A->ghost_buf = nullptr;
+    int rc = RAILS_OK;
+    if (A->nsend) rc = rails::dev_alloc_t(&A->send_buf, (size_t)A->nsend * ncols * sizeof(double));
+    if (!rc && A->nghost) rc = rails::dev_alloc_t(&A->ghost_buf, (size_t)A->nghost * ncols * sizeof(double));
+    if (rc) return rc;
     A->halo_cols_cap = ncols;
     return RAILS_OK;
 }
@@ -517,7 +520,8 @@ extern "C" int rails_csr_create(long long rows, long long global_rows, long long
         A->nsend += A->send_count[p];
     }
     RAILS_CUDA_TRY(cudaMalloc(&d_ids, std::max<size_t>(ghost_local.size(), 1) * sizeof(int)));
-    RAILS_CUDA_TRY(cudaMalloc(&A->send_rows, std::max<size_t>(A->nsend, 1) * sizeof(int)));
+    rc = rails::dev_alloc_t(&A->send_rows, std::max<size_t>(A->nsend, 1) * sizeof(int));
+    if (rc) { free_csr(A); return rc; }
     if (!ghost_local.empty())
         RAILS_CUDA_TRY(cudaMemcpyAsync(d_ids, ghost_local.data(), ghost_local.size() * sizeof(int),
                                        cudaMemcpyHostToDevice, c.stream));

@@ -275,6 +275,7 @@ extern "C" int rails_mv_norm_inf(rails_mv_t mv, int col0, int ncols, double *out
         RAILS_NCCL_TRY(ncclAllReduce(c.d_small, c.d_small, 1, ncclDouble, ncclMax, c.comm, c.stream));
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, sizeof(double), cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    { int xrc = rails::check_exchange_error("blas1"); if (xrc) return xrc; }
     *out = c.h_small[0];
     return RAILS_OK;
 }

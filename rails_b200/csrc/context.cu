@@ -2,6 +2,7 @@
 #include "internal.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <thread>
@@ -52,6 +53,16 @@ static int grow(double **p, size_t *cap, size_t need)
 }
 
 int ensure_partial(size_t doubles) { return grow(&ctx().d_partial, &ctx().partial_cap, doubles); }
+
+int check_exchange_error(const char *where)
+{
+    Context &c = ctx();
+    if (!c.h_mb_error || !*(volatile int *)c.h_mb_error)
+        return RAILS_OK;
+    *(volatile int *)c.h_mb_error = 0;
+    return fail(RAILS_ERR_CUDA, "%s: a peer did not answer a reduction within the mailbox timeout "
+                "(RAILS_MAILBOX_TIMEOUT_S); the values returned are NaN", where);
+}
 
 // ---- device block cache --------------------------------------------------------
 // Multivector buffers (V, AV, MV at capacity; the m x c temporaries the wrapper
@@ -319,6 +330,15 @@ extern "C" int rails_cuda_init(int device)
     RAILS_CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     RAILS_CUDA_TRY(cudaStreamCreateWithFlags(&c.comm_stream, cudaStreamNonBlocking));
     c.events.assign(64, nullptr);
+    RAILS_CUDA_TRY(cudaHostAlloc((void **)&c.h_mb_error, sizeof(int), cudaHostAllocMapped));
+    *c.h_mb_error = 0;
+    RAILS_CUDA_TRY(cudaHostGetDevicePointer((void **)&c.d_mb_error, c.h_mb_error, 0));
+    {
+        const char *e = getenv("RAILS_MAILBOX_TIMEOUT_S");
+        double seconds = e ? atof(e) : 30.0;
+        if (!(seconds > 0.0)) seconds = 30.0;
+        c.mb_timeout_cycles = (long long)(seconds * 1e3 * (double)prop.clockRate);   // clockRate is in kHz
+    }
     c.ready = true;
     int rc = rails::ensure_small(65536);
     if (rc) return rc;
@@ -351,6 +371,8 @@ extern "C" int rails_cuda_finalize(void)
     if (c.h_ring) cudaFreeHost(c.h_ring);
     if (c.d_lz) cudaFree(c.d_lz);
     c.d_lz = nullptr; c.lz_cap = 0; c.lz_pending = false;
+    if (c.h_mb_error) cudaFreeHost(c.h_mb_error);
+    c.h_mb_error = c.d_mb_error = nullptr;
     for (int i = 0; i < 2; ++i)
     {
         if (c.h_stage[i]) cudaFreeHost(c.h_stage[i]);
@@ -374,7 +396,7 @@ extern "C" int rails_cuda_sync(void)
 {
     RAILS_REQUIRE_READY();
     RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
-    return RAILS_OK;
+    return rails::check_exchange_error("rails_cuda_sync");
 }
 
 extern "C" const char *rails_cuda_last_error(void) { return ctx().last_error.c_str(); }

@@ -177,13 +177,13 @@ int launch_dot(const double *X, long long ldx, int a, const double *Y, long long
     constexpr int ACH = dot_achunk(BT);
     dim3 grid(nb, (a + ACH - 1) / ACH);
     size_t smem = (size_t)std::min(a, ACH) * BT * DOT_WARPS * sizeof(double);
-    static bool attr_set = false;
-    if (!attr_set)
+    static int configured_device = -1;
+    if (configured_device != c.device)
     {
         RAILS_CUDA_TRY(cudaFuncSetAttribute(dot_kernel<RP, BT, U>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             ACH * BT * DOT_WARPS * (int)sizeof(double)));
-        attr_set = true;
+        configured_device = c.device;
     }
     auto kern = dot_kernel<RP, BT, U>;
     RAILS_LAUNCH(kern, grid, DOT_THREADS, smem, X, ldx, a, Y, ldy, rows, c.d_partial);
@@ -288,6 +288,7 @@ extern "C" int rails_mv_dot(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0,
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, (size_t)a * b * sizeof(double),
                                    cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    { int xrc = rails::check_exchange_error("dot"); if (xrc) return xrc; }
     for (int j = 0; j < b; ++j)
         for (int i = 0; i < a; ++i)
             out[i + (size_t)j * ldo] = c.h_small[i + (size_t)j * a];
@@ -343,6 +344,7 @@ extern "C" int rails_mv_dot_batch(int count, const rails_mv_t *X, const int *xc0
     }
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, total * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    { int xrc = rails::check_exchange_error("dot"); if (xrc) return xrc; }
     for (int i = 0; i < count; ++i)
         for (int j = 0; j < b[i]; ++j)
             for (int r = 0; r < a[i]; ++r)

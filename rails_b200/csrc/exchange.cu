@@ -19,7 +19,8 @@
 // next-but-one store needs the peer's contribution to the next exchange, which
 // the peer issues only after it has consumed the current one), so two slots
 // would do; four are used.  Flags are monotonic sequence numbers, never reset.
-// A wait that exceeds ~4 s sets an error flag instead of hanging the GPU.
+// A wait that exceeds RAILS_MAILBOX_TIMEOUT_S (default 30 s) makes the result NaN
+// and raises a host-visible flag instead of hanging the GPU or summing stale slots.
 #include "internal.h"
 
 #include <cstring>
@@ -48,7 +49,8 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 
 __global__ void __launch_bounds__(FX_THREADS)
 finish_exchange_kernel(const double *partial, int nblocks, int n, double *out, Mailbox mb,
-                       unsigned long long seq, int *error, const double *__restrict__ T, int k,
+                       unsigned long long seq, volatile int *error, long long timeout_cycles,
+                       const double *__restrict__ T, int k,
                        double *__restrict__ coef, double *norm_out, const double *scale_sq)
 {
     __shared__ double sm[FX_THREADS];
@@ -113,28 +115,44 @@ finish_exchange_kernel(const double *partial, int nblocks, int n, double *out, M
         __syncthreads();
         if (t < mb.nranks)
             st_release_sys(mb.flags[t] + slot * MB_MAX_RANKS + mb.rank, seq);
+        __shared__ int timed_out;
+        if (t == 0) timed_out = 0;
+        __syncthreads();
         if (t < mb.nranks)
         {
             const unsigned long long *f = mb.flags[mb.rank] + slot * MB_MAX_RANKS + t;
             const long long t0 = clock64();
             while (ld_acquire_sys(f) < seq)
             {
-                if (clock64() - t0 > 8000000000LL)      // ~4 s at 2 GHz: a peer died
+                if (clock64() - t0 > timeout_cycles)      // a peer died or is far behind
                 {
-                    atomicExch(error, 1);
+                    timed_out = 1;
                     break;
                 }
             }
         }
         __syncthreads();
         const double *src = mb.data[mb.rank] + (size_t)slot * MB_MAX_RANKS * MB_MAXN;
-        for (int i = t; i < n; i += FX_THREADS)
+        if (timed_out)
         {
-            double s = 0.0;
-            for (int r = 0; r < mb.nranks; ++r)
-                s += ((const volatile double *)src)[(size_t)r * MB_MAXN + i];
-            res[i] = s;
+            // never hand out a sum of stale slots: the result is NaN on this rank and
+            // the host sees the flag at its next read-back (check_exchange_error)
+            if (t == 0)
+            {
+                *error = 1;
+                __threadfence_system();
+            }
+            for (int i = t; i < n; i += FX_THREADS)
+                res[i] = __longlong_as_double(0x7ff8000000000000LL);
         }
+        else
+            for (int i = t; i < n; i += FX_THREADS)
+            {
+                double s = 0.0;
+                for (int r = 0; r < mb.nranks; ++r)
+                    s += ((const volatile double *)src)[(size_t)r * MB_MAXN + i];
+                res[i] = s;
+            }
         __syncthreads();
     }
     // optional scaling by a squared norm held on the device
@@ -252,15 +270,15 @@ int finish_reduction(const double *partial, int nblocks, int n, double *out, boo
         if (!multi) { mb.nranks = 1; mb.rank = 0; }
         unsigned long long seq = 0;
         if (multi) seq = ++c.mb_seq;
-        static bool attr = false;
-        if (!attr)
+        static int configured_device = -1;
+        if (configured_device != c.device)
         {
             RAILS_CUDA_TRY(cudaFuncSetAttribute(finish_exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 MB_MAXN * (int)sizeof(double)));
-            attr = true;
+            configured_device = c.device;
         }
         RAILS_LAUNCH(finish_exchange_kernel, 1, FX_THREADS, (size_t)n * sizeof(double), partial, nblocks, n, out,
-                     mb, seq, c.d_mb_error, T, k, coef, norm_out, scale_sq);
+                     mb, seq, c.d_mb_error, c.mb_timeout_cycles, T, k, coef, norm_out, scale_sq);
         RAILS_CHECK_LAUNCH();
         return RAILS_OK;
     }
@@ -310,11 +328,6 @@ int setup_mailboxes()
     const size_t data_bytes = (size_t)MB_SLOTS * MB_MAX_RANKS * MB_MAXN * sizeof(double);
     if (cudaMalloc(&c.mb_local, flag_bytes + data_bytes) != cudaSuccess) { cudaGetLastError(); return RAILS_OK; }
     cudaMemset(c.mb_local, 0, flag_bytes + data_bytes);
-    if (!c.d_mb_error)
-    {
-        RAILS_CUDA_TRY(cudaMalloc(&c.d_mb_error, sizeof(int)));
-        RAILS_CUDA_TRY(cudaMemset(c.d_mb_error, 0, sizeof(int)));
-    }
     cudaIpcMemHandle_t mine;
     int ok = cudaIpcGetMemHandle(&mine, c.mb_local) == cudaSuccess ? 1 : 0;
     if (!ok) cudaGetLastError();

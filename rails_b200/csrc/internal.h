@@ -101,7 +101,11 @@ struct Context
     void *mb_local = nullptr;
     void *mb_mapped[MB_MAX_RANKS] = {nullptr};
     unsigned long long mb_seq = 0;           // exchanges issued so far (same on every rank)
-    int *d_mb_error = nullptr;               // set by a kernel whose wait timed out
+    // raised by a kernel whose wait for a peer timed out: host-mapped pinned
+    // memory, so that every host read-back can test it without a copy
+    int *h_mb_error = nullptr;
+    int *d_mb_error = nullptr;               // device address of *h_mb_error
+    long long mb_timeout_cycles = 0;         // RAILS_MAILBOX_TIMEOUT_S (default 30 s) in SM clocks
     // rails_mv_lanczos_begin -> rails_mv_lanczos_run hand-over: scratch that
     // survives other library calls, and what the pending first projection was for
     double *d_lz = nullptr;
@@ -160,6 +164,10 @@ int finish_reduction(const double *partial, int nblocks, int n, double *out, boo
                      double *norm_out = nullptr, const double *scale_sq = nullptr);
 // coef = [T g[k:2k) ; T g[0:k) ; g[2k:n)] on the device (T compact k x k)
 int lanczos_coef(const double *T, int k, int n, const double *g, double *coef);
+// After a stream synchronisation that returned reduction results to the host:
+// non-zero (flag cleared, error count bumped so that BackendHealth stops the solve)
+// when a peer did not answer an exchange in time -- the values just read are NaN.
+int check_exchange_error(const char *where);
 int setup_mailboxes();
 void release_mailboxes();
 

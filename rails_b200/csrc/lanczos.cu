@@ -34,6 +34,8 @@ constexpr long long MD_TILE = 512LL * MD_RP;     // rows per CTA iteration
 constexpr int MD_U = 4;                          // columns in flight
 constexpr int MD_MAXCOLS = 1024;                 // 64 KB of per-warp accumulators
 
+int lz_attr();      // defined with the chain's scratch management below
+
 struct Segs
 {
     const double *p[MAX_SEGS];
@@ -375,6 +377,7 @@ int finish_to_host(int n, bool distributed, double *out)
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, c.d_small, (size_t)n * sizeof(double),
                                    cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    { int xrc = rails::check_exchange_error("reduction"); if (xrc) return xrc; }
     memcpy(out, c.h_small, (size_t)n * sizeof(double));
     return RAILS_OK;
 }
@@ -417,12 +420,12 @@ extern "C" int rails_mv_multi_dot(int nblk, const rails_mv_t *X, const int *xc0,
         const int nb = (int)std::min<long long>(ntiles, (long long)c.sm_count * 4);
         rc = rails::ensure_partial((size_t)nb * std::max(total, 1));
         if (rc) return rc;
-        static bool attr_set = false;
-        if (!attr_set)
+        static int configured_device = -1;
+        if (configured_device != c.device)
         {
             RAILS_CUDA_TRY(cudaFuncSetAttribute(multi_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 MD_MAXCOLS * MD_WARPS * (int)sizeof(double)));
-            attr_set = true;
+            configured_device = c.device;
         }
         const size_t smem = (size_t)std::max(total, 1) * MD_WARPS * sizeof(double);
         RAILS_LAUNCH(multi_dot_kernel, nb, MD_THREADS, smem, S, total, q->data + (size_t)qc * q->ld,
@@ -631,8 +634,7 @@ extern "C" int rails_mv_multi_gemv(int nblk, const rails_mv_t *X, const int *xc0
     rails::Context &c = ctx();
     const long long rows = out->rows;
     if (alpha) *alpha = 0.0;
-    if (rows == 0)
-        return RAILS_OK;
+    // (a rank without rows still launches: it has to take part in the sum over ranks)
     const double *dC = nullptr;
     if (total > 0)
     {
@@ -641,7 +643,7 @@ extern "C" int rails_mv_multi_gemv(int nblk, const rails_mv_t *X, const int *xc0
     }
     const long long rows2 = (rows + 1) / 2;
     const long long per_block = (long long)MG_THREADS * MG_RP;
-    const int nb = (int)((rows2 + per_block - 1) / per_block);
+    const int nb = (int)std::max<long long>(1, (rows2 + per_block - 1) / per_block);
     rc = rails::ensure_partial((size_t)nb);
     if (rc) return rc;
     rc = rails::ensure_small(1);
@@ -741,13 +743,8 @@ extern "C" int rails_mv_lanczos_project(int nblk, const rails_mv_t *X, const int
     const int nb = (int)std::max<long long>(1, std::min<long long>(ntiles, (long long)c.sm_count * 4));
     rc = rails::ensure_partial((size_t)nb * (total + 1));
     if (rc) return rc;
-    static bool attr_set = false;
-    if (!attr_set)
-    {
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (MD_MAXCOLS + 1) * MD_WARPS * (int)sizeof(double)));
-        attr_set = true;
-    }
+    rc = lz_attr();
+    if (rc) return rc;
     RAILS_LAUNCH(lanczos_dot_kernel, nb, MD_THREADS, (size_t)(total + 1) * MD_WARPS * sizeof(double), S, total,
                  colp, prev, prev2, (const double *)sc, (const double *)(sc + 1), rows, c.d_partial);
     RAILS_CHECK_LAUNCH();
@@ -755,6 +752,7 @@ extern "C" int rails_mv_lanczos_project(int nblk, const rails_mv_t *X, const int
     if (rc) return rc;
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, g, (size_t)(total + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
+    { int xrc = rails::check_exchange_error("lanczos_project"); if (xrc) return xrc; }
     memcpy(out, c.h_small, (size_t)(total + 1) * sizeof(double));
     return RAILS_OK;
 }
@@ -766,12 +764,12 @@ constexpr int LZ_MAXL = 256;           // Lanczos steps per call
 
 int lz_attr()
 {
-    static bool attr_set = false;
-    if (!attr_set)
+    static int configured_device = -1;
+    if (configured_device != ctx().device)
     {
         RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_dot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (MD_MAXCOLS + 1) * MD_WARPS * (int)sizeof(double)));
-        attr_set = true;
+        configured_device = ctx().device;
     }
     return RAILS_OK;
 }
@@ -819,7 +817,7 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
     if (total > MD_MAXCOLS)
         return rails::fail(RAILS_ERR_ARG, "lanczos_run: %d columns, at most %d", total, MD_MAXCOLS);
     for (int s = 0; s < S.nseg; ++s)
-        if (S.p[s] <= Q->data + (size_t)(qc0 + L + 1) * Q->ld && Q->data + (size_t)qc0 * Q->ld < S.p[s] + (size_t)S.n[s] * S.ld[s])
+        if (S.p[s] < Q->data + (size_t)(qc0 + L + 1) * Q->ld && Q->data + (size_t)qc0 * Q->ld < S.p[s] + (size_t)S.n[s] * S.ld[s])
             return rails::fail(RAILS_ERR_ARG, "lanczos_run: Q overlaps a block");
     rails::Context &c = ctx();
     const int k = xn[0];
@@ -857,8 +855,9 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
     if (rc) return rc;
     rc = lz_attr();
     if (rc) return rc;
-    if (rows > 0)
     {
+        // (a rank that owns no rows still runs every launch, with idle CTAs: it has
+        // to take part in each exchange)
         // The Lanczos vectors are kept UN-normalised while the recurrence runs
         // (w_i = |w_i| q_i): a step is two kernels and two exchanges,
         //   A_i: w_i = raw_i - alpha_{i-1} q_{i-1} - beta_{i-2} q_{i-2} (fused update of the
@@ -895,21 +894,20 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
             if (rc) return rc;
         }
         // columns 0 .. L-2 were normalised on the way; the last one here
-        double *last = Q->data + (size_t)(qc0 + L - 1) * Q->ld;
-        const int nbn = (int)std::max<long long>(1, std::min<long long>((rows + 255) / 256, (long long)c.sm_count * 8));
-        RAILS_LAUNCH(normalize_kernel, nbn, 256, 0, last, (const double *)(b2 + L - 1), rows);
-        RAILS_CHECK_LAUNCH();
+        if (rows > 0)
+        {
+            double *last = Q->data + (size_t)(qc0 + L - 1) * Q->ld;
+            const int nbn = (int)std::max<long long>(1, std::min<long long>((rows + 255) / 256, (long long)c.sm_count * 8));
+            RAILS_LAUNCH(normalize_kernel, nbn, 256, 0, last, (const double *)(b2 + L - 1), rows);
+            RAILS_CHECK_LAUNCH();
+        }
     }
     // one read-back for the whole recurrence
     rc = rails::ensure_small(2 * (size_t)LZ_MAXL + 1);
     if (rc) return rc;
     RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_small, b2, (2 * (size_t)LZ_MAXL + 1) * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
-    int xerr = 0;
-    if (c.d_mb_error)
-        RAILS_CUDA_TRY(cudaMemcpyAsync(&xerr, c.d_mb_error, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
-    if (xerr)
-        return rails::fail(RAILS_ERR_CUDA, "lanczos_run: a peer did not answer a reduction (mailbox wait timed out)");
+    { int xrc = rails::check_exchange_error("lanczos_run"); if (xrc) return xrc; }
     int done = 0;
     for (int i = 0; i < L; ++i)
     {
@@ -940,7 +938,7 @@ extern "C" int rails_mv_lanczos_begin(int nblk, const rails_mv_t *X, const int *
     bool dist = false;
     int rc = collect_segs(nblk, X, xc0, xn, Q->rows, &S, &total, &dist, "lanczos_begin");
     if (rc) return rc;
-    if (total > MD_MAXCOLS || Q->rows == 0)
+    if (total > MD_MAXCOLS)
         return RAILS_OK;                 // nothing started; lanczos_run does everything
     const bool reduce = dist && Q->flags == RAILS_MV_DISTRIBUTED && c.comm;
     rc = lz_scratch(total);

@@ -323,6 +323,13 @@ static int read_dense_unguarded(std::string const &path, int &rows, int &cols, s
         err = path + ": the size line promises more values than the file holds";
         return 1;
     }
+    // symmetric / skew-symmetric storage mirrors (i, j) into (j, i): only a square
+    // block has room for that (read_crs rejects the same case)
+    if (b.symmetry && m != n)
+    {
+        err = path + ": symmetric storage on a non-square matrix";
+        return 1;
+    }
     rows = (int)m;
     cols = (int)n;
     data.assign((size_t)m * (size_t)n, 0.0);

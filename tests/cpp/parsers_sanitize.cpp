@@ -50,6 +50,10 @@ int main(int argc, char **argv)
         "%%MatrixMarket matrix coordinate real general\n2 2 5\n1 1 1.0\n",          // fewer entries than promised
         "%%MatrixMarket matrix coordinate pattern general\n2 2 2\n1 2\n2 1\n",
         "%%MatrixMarket matrix coordinate real general\n-1 4 2\n",
+        // symmetric storage on a non-square size line: the mirror write would leave the buffer
+        "%%MatrixMarket matrix array real symmetric\n4 2\n1\n2\n3\n4\n5\n6\n7\n",
+        "%%MatrixMarket matrix coordinate real symmetric\n4 2 2\n4 1 1.0\n3 2 2.0\n",
+        "%%MatrixMarket matrix array real skew-symmetric\n5 3\n1\n2\n3\n4\n5\n6\n7\n",
         "%%MatrixMarket matrix coordinate real general\n2000000000 2000000000 1\n1 1 1\n",
         "", "\n\n\n", "<ParameterList", "[unterminated\nkey", "<Parameter name=\"x\" type=\"int\" value=\"abc\"/>"};
     // mutations of the valid files: truncations, byte flips, duplicated chunks

@@ -144,6 +144,21 @@ int rails_mv_dot_batch(int count, const rails_mv_t *X, const int *xc0, const int
  * used for Y = B' q (src/LyapunovSolver.hpp:150,389) without a host sync */
 int rails_mv_dot_dev(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
                      rails_mv_t Out, int oc0);
+/* Allocation-free variant of rails_mv_dot_dev (local product, no sum over ranks).
+ * NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot allocate (code under CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  Calls no cudaMalloc / cudaFree / allocating
+ * routine, does not synchronise; the per-CTA partials live in a static device array
+ * of RAILS_NOALLOC_SCRATCH_DOUBLES doubles (1.16 MiB, held by every GPU that loads
+ * the library until exit).  A product that needs more -- CTAs (<= 4 per SM) x
+ * streamed columns x held columns per launch (<= 8) -- is rejected with
+ * RAILS_ERR_ARG, as are row-partitioned operands with more than one rank.  All calls
+ * share the array: calls that overlap on the GPU race; calls on the library stream
+ * are ordered.  Same kernels and summation order as rails_mv_dot_dev when neither
+ * block is wider than 8 columns (bit-identical results). */
+#define RAILS_NOALLOC_SCRATCH_DOUBLES 151552
+int rails_mv_dot_dev_noalloc(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
+                             rails_mv_t Out, int oc0);
 
 /* ---- tall-skinny times small: Out[:, oc0..oc0+c) = alpha * V[:, vc0..vc0+k) * C
  *      + beta * Out      (StlWrapper::operator* :168-187, EpetraMV :194-241)

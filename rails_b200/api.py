@@ -99,6 +99,7 @@ CUDA_SYMBOLS = [
     ("rails_mv_dot_batch", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, ctypes.POINTER(P), c_int_p, c_int_p,
                                ctypes.POINTER(c_double_p), c_int_p]),
     ("rails_mv_dot_dev", I, [P, I, I, P, I, I, P, I]),
+    ("rails_mv_dot_dev_noalloc", I, [P, I, I, P, I, I, P, I]),
     ("rails_mv_gemm", I, [P, I, I, c_double_p, I, I, D, D, P, I]),
     ("rails_mv_gemm_dev", I, [P, I, I, P, I, I, D, D, P, I]),
     ("rails_mv_multi_dot", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, P, I, D, c_double_p]),

@@ -491,3 +491,149 @@ extern "C" int rails_mv_orthogonalize(rails_mv_t V, int col0, int first, int las
     }
     return RAILS_OK;
 }
+
+// ---- allocation-free variant -----------------------------------------------------
+// rails_mv_dot_dev_noalloc: the streaming X'Y of rails_mv_dot_dev with the per-CTA
+// partials in a STATIC device array instead of the grown-on-demand workspace, and
+// the result written straight into the caller's device block.  It calls no
+// cudaMalloc / cudaFree / allocating routine, does not synchronise and returns
+// nothing to the host, so it may be called where allocation is forbidden (CUDA
+// graph capture, serving loops).  No counterpart in the
+// reference.
+//
+// The array is part of the library image: every GPU that loads librails_cuda.so
+// holds RAILS_NOALLOC_SCRATCH_DOUBLES * 8 bytes (1.16 MiB) until the process exits.
+// All calls share it and it keeps the last call's contents.  Nothing in it has to
+// start at zero (dot_kernel writes every partial the finish kernel reads), but two
+// calls that OVERLAP on the GPU -- issued from different streams or processes'
+// threads without ordering -- race on it.  Calls on the library stream are ordered.
+namespace
+{
+
+constexpr size_t NOALLOC_SCRATCH_DOUBLES = RAILS_NOALLOC_SCRATCH_DOUBLES;
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_SCRATCH_DOUBLES];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address:
+// the address a kernel may use comes from cudaGetSymbolAddress, once per device,
+// with that device current.
+double *g_noalloc_ptr = nullptr;
+int g_noalloc_device = -1;
+
+int noalloc_scratch(double **out)
+{
+    rails::Context &c = ctx();
+    if (g_noalloc_device != c.device || !g_noalloc_ptr)
+    {
+        RAILS_CUDA_TRY(cudaSetDevice(c.device));
+        void *p = nullptr;
+        RAILS_CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr = static_cast<double *>(p);
+        g_noalloc_device = c.device;
+    }
+    *out = g_noalloc_ptr;
+    return RAILS_OK;
+}
+
+// CTAs of one launch (same rule as launch_dot) and the scratch it needs
+template<int RP>
+int noalloc_blocks(long long rows)
+{
+    constexpr long long TILE = 512LL * RP;
+    long long ntiles = std::max<long long>((rows + TILE - 1) / TILE, 1);
+    return (int)std::min<long long>(ntiles, (long long)ctx().sm_count * 4);
+}
+
+template<int RP, int BT, int U>
+int launch_dot_noalloc(const double *X, long long ldx, int a, const double *Y, long long ldy,
+                       long long rows, int t0, double *scratch, double *d_out, long long sj, long long st)
+{
+    rails::Context &c = ctx();
+    const int nb = noalloc_blocks<RP>(rows);
+    constexpr int ACH = dot_achunk(BT);
+    dim3 grid(nb, (a + ACH - 1) / ACH);
+    size_t smem = (size_t)std::min(a, ACH) * BT * DOT_WARPS * sizeof(double);
+    static int configured_device = -1;
+    if (configured_device != c.device)
+    {
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(dot_kernel<RP, BT, U>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            ACH * BT * DOT_WARPS * (int)sizeof(double)));
+        configured_device = c.device;
+    }
+    auto kern = dot_kernel<RP, BT, U>;
+    RAILS_LAUNCH(kern, grid, DOT_THREADS, smem, X, ldx, a, Y, ldy, rows, scratch);
+    RAILS_CHECK_LAUNCH();
+    const int n = a * BT;
+    RAILS_LAUNCH(dot_finish_kernel, (n + 7) / 8, 256, 0, (const double *)scratch, nb, n, BT, t0, d_out, sj, st);
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
+}
+
+// zero fill of an a x b block with leading dimension ld (rows == 0)
+__global__ void noalloc_zero_kernel(double *out, int a, int b, long long ld)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a * b; i += gridDim.x * blockDim.x)
+        out[(i % a) + (size_t)(i / a) * ld] = 0.0;
+}
+
+}
+
+extern "C" int rails_mv_dot_dev_noalloc(rails_mv_t X, int xc0, int a, rails_mv_t Y, int yc0, int b,
+                                        rails_mv_t Out, int oc0)
+{
+    RAILS_REQUIRE_READY();
+    int rc = check_pair(X, xc0, a, Y, yc0, b, "dot_dev_noalloc");
+    if (rc) return rc;
+    if (!Out || oc0 < 0 || oc0 + b > Out->cols || Out->rows != a)
+        return rails::fail(RAILS_ERR_ARG, "dot_dev_noalloc: result block must be %d x %d", a, b);
+    if (a == 0 || b == 0) return RAILS_OK;
+    rails::Context &c = ctx();
+    if (c.comm && c.nranks > 1 && X->flags == RAILS_MV_DISTRIBUTED && Y->flags == RAILS_MV_DISTRIBUTED)
+        return rails::fail(RAILS_ERR_ARG, "dot_dev_noalloc: row-partitioned operands need the sum over ranks; "
+                           "use rails_mv_dot_dev");
+    const long long rows = X->rows;
+    const double *Xd = X->data + (size_t)xc0 * X->ld, *Yd = Y->data + (size_t)yc0 * Y->ld;
+    double *out = Out->data + (size_t)oc0 * Out->ld;
+    const long long ldo = Out->ld;
+    if (rows == 0)
+    {
+        RAILS_LAUNCH(noalloc_zero_kernel, 1, 256, 0, out, a, b, ldo);
+        RAILS_CHECK_LAUNCH();
+        return RAILS_OK;
+    }
+    // stream the operand with more columns, hold the other in registers (as dot_device)
+    const bool swap = b > a;
+    const double *S = swap ? Yd : Xd, *H = swap ? Xd : Yd;
+    const long long lds = swap ? Y->ld : X->ld, ldh = swap ? X->ld : Y->ld;
+    const int ns = swap ? b : a, nh = swap ? a : b;
+    const long long sj = swap ? ldo : 1, st = swap ? 1 : ldo;
+    // the largest launch decides: partials = CTAs x streamed columns x held columns per launch
+    size_t need = 0;
+    for (int t = 0; t < nh;)
+    {
+        const int left = nh - t;
+        const int bt = left >= 8 ? 8 : left >= 4 ? 4 : left >= 2 ? 2 : 1;
+        const int nb = bt == 8 ? noalloc_blocks<1>(rows) : bt == 4 ? noalloc_blocks<2>(rows) : noalloc_blocks<4>(rows);
+        need = std::max(need, (size_t)nb * (size_t)ns * (size_t)bt);
+        t += bt;
+    }
+    if (need > NOALLOC_SCRATCH_DOUBLES)
+        return rails::fail(RAILS_ERR_ARG, "dot_dev_noalloc: a %d x %d product over %lld rows needs %zu doubles of "
+                           "scratch, the static array holds %zu (RAILS_NOALLOC_SCRATCH_DOUBLES); use rails_mv_dot_dev",
+                           a, b, rows, need, NOALLOC_SCRATCH_DOUBLES);
+    double *scratch = nullptr;
+    rc = noalloc_scratch(&scratch);
+    if (rc) return rc;
+    int t = 0;
+    while (t < nh)
+    {
+        const int left = nh - t;
+        const double *Ht = H + (size_t)t * ldh;
+        if (left >= 8)      { rc = launch_dot_noalloc<1, 8, 4>(S, lds, ns, Ht, ldh, rows, t, scratch, out, sj, st); t += 8; }
+        else if (left >= 4) { rc = launch_dot_noalloc<2, 4, 2>(S, lds, ns, Ht, ldh, rows, t, scratch, out, sj, st); t += 4; }
+        else if (left >= 2) { rc = launch_dot_noalloc<4, 2, 2>(S, lds, ns, Ht, ldh, rows, t, scratch, out, sj, st); t += 2; }
+        else                { rc = launch_dot_noalloc<4, 1, 4>(S, lds, ns, Ht, ldh, rows, t, scratch, out, sj, st); t += 1; }
+        if (rc) return rc;
+    }
+    return RAILS_OK;
+}

@@ -22,8 +22,11 @@ bracketed by CUDA events on the library stream with everything resident in HBM
 (each rank reports its own event time; the max over ranks is used).  Inputs are
 far larger than the 126 MB L2 (V alone is 134 MB per column), so there is no
 L2 flush between iterations.
-Each leg is run a few times back to back and the fastest run is reported (the
-loop is host-driven and the box is shared).
+The window is run --windows times back to back (default 5): `value` is the MEDIAN
+window, all of them are listed in `window_ms_per_step` with their spread.  (Round 1
+reported the fastest of 3 and hid windows of 18-99 ms; the cause, the stream-ordered
+memory pool, is gone: profiles/r02_window_variability.md.)  The reference arm runs
+ONE window; the median-of-5 of this arm is the conservative side of that asymmetry.
 `e2e`: the solve to the configuration's tolerance through the user-facing C
 entry point rails_host_solve_m with HOST buffers -- the CSR arrays of A (and M)
 and B are uploaded, V and T downloaded, inside the timed wall-clock region;
@@ -68,8 +71,8 @@ def parse_args():
     ap.add_argument("--workload", default=os.environ.get("RAILS_BENCH_WORKLOAD", "C3"))
     ap.add_argument("--grid", type=int, default=int(os.environ.get("RAILS_BENCH_GRID", "0")),
                     help="override the grid size g of the workload (testing)")
-    ap.add_argument("--windows", type=int, default=3,
-                    help="timed windows run back to back; the fastest is reported")
+    ap.add_argument("--windows", type=int, default=5,
+                    help="identical timed windows run back to back; the MEDIAN is reported, all are listed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true")
     ap.add_argument("--kernels-only", action="store_true",
@@ -107,7 +110,10 @@ def window_params(params, warmup, steps):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """nvidia-smi clocks / throttle reasons during the timed region, one sample per
+    second (round 1 polled every 200 ms; measured in round 2: the poller makes no
+    difference to the windows, profiles/r02_window_variability.md -- the spread came
+    from the stream-ordered memory pool)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -121,7 +127,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "200"],
+                 "--format=csv,noheader,nounits", "-lms", "1000"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -337,7 +343,9 @@ def run_reference(args):
     kind, g, dim, n_b, params = workload(args)
     rp, ci, v = problems.build(kind, g, dim)
     M = problems.lumped_mass(g ** dim) if params.get("Use mass matrix") else None
-    B = np.asfortranarray(np.random.RandomState(1).uniform(-1.0, 1.0, (g ** dim, n_b)))
+    # `std::srand(1); B.random()` of the reference, made on the host
+    B = problems.reference_B(g ** dim, n_b)
+    params["Skip random draws"] = 1
     budget = float(os.environ.get("RAILS_BENCH_REF_SECONDS", "150"))
     t0 = time.time()
     cb = cpu_sample(rp, ci, v, n_b, params, B, args.warmup, args.steps, budget, M=M)
@@ -380,10 +388,12 @@ def run_b200(args):
     rows = r1 - r0
     rp, ci, v = problems.build(kind, g, dim, r0, r1)
     M = problems.lumped_mass(m, r0, r1) if params.get("Use mass matrix") else None
-    # B on the host (so that it is an uploaded input), same for every arm
-    B_full = np.random.RandomState(1).uniform(-1.0, 1.0, (m, n_b))
-    B = np.asfortranarray(B_full[r0:r1])
-    del B_full
+    # B on the host (so that it is an uploaded input), same for every arm: the
+    # reference's own `std::srand(1); B.random()` stream, this
+    # rank's rows by jump-ahead; "Skip random draws" keeps the std::rand() sequence
+    # of V and of the Lanczos start vectors that of a reference run
+    B = problems.reference_B(m, n_b, r0, r1)
+    params["Skip random draws"] = 1
     if args.kernels_only:
         kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps)
         if rank == 0:
@@ -404,18 +414,14 @@ def run_b200(args):
         raise SystemExit("rails_host_solve (warm-up) failed with code %d" % cold["ret"])
 
     # ---- leg 1: device-timed window, everything resident in HBM -------------
-    #      The window (W untimed + exactly K timed iterations of one solve) is
-    #      run --windows times and the fastest one is reported: the loop is driven
-    #      from the host (one synchronisation per L Lanczos steps, ~70 launches per
-    #      iteration), and on a shared box a burst of host activity has been seen to
-    #      stretch a whole window 3x (63 vs 19 ms per iteration, same binary, same
-    #      box, minutes apart).  Every window obeys the timing rules on its own;
-    #      all of them are listed in `window_ms_per_step`.
+    #      The window (W untimed + exactly K timed iterations of one solve) is run
+    #      --windows times; the median is reported and all of them are listed.
+    #      Every window obeys the timing rules on its own.
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     t0 = time.time()
-    res, timed_ms, all_ms = None, None, []
+    all_ms, runs = [], []
     for _ in range(max(1, args.windows)):
         if dist is not None:
             dist.barrier()
@@ -432,19 +438,22 @@ def run_b200(args):
                              "[%d, %d] closed" % (cur["iterations"], W + 1, W + K))
         cur_ms = allreduce_max(dist, cur["timed_ms"])
         all_ms.append(cur_ms / K)
-        if timed_ms is None or cur_ms < timed_ms:
-            res, timed_ms = cur, cur_ms
+        runs.append((cur_ms, cur))
     t1 = time.time()
     clocks = sampler.stop(t0, t1) if rank == 0 else None
+    # the MEDIAN window is the reported one (lower middle for an even count)
+    runs.sort(key=lambda r: r[0])
+    timed_ms, res = runs[(len(runs) - 1) // 2]
 
     # ---- leg 2: end to end through the C entry point, host buffers in and out,
     #      solved to the configuration's tolerance -----------------------------
     cap = 400
 
     def end_to_end(P, repeats):
-        """Fastest of `repeats` end-to-end solves (host buffers in and out inside
-        the timed region); the max over ranks is taken per solve."""
-        best, best_wall = None, None
+        """Median of `repeats` end-to-end solves (host buffers in and out inside the
+        timed region); the max over ranks is taken per solve.  Returns the median
+        solve, its wall time and all wall times."""
+        done = []
         for _ in range(repeats):
             if dist is not None:
                 dist.barrier()
@@ -456,11 +465,13 @@ def run_b200(args):
             w = allreduce_max(dist, time.time() - t_start)
             if out["ret"] >= 100:
                 raise SystemExit("rails_host_solve (e2e leg) failed with code %d" % out["ret"])
-            if best is None or w < best_wall:
-                best, best_wall = out, w
-        return best, best_wall
+            done.append((w, out))
+        walls = [w for w, _ in done]
+        done.sort(key=lambda r: r[0])
+        w, out = done[(len(done) - 1) // 2]
+        return out, w, walls
 
-    e2e, wall = end_to_end(params, 2)
+    e2e, wall, e2e_walls = end_to_end(params, 3)
     h2d = rp.nbytes + ci.nbytes + v.nbytes + B.nbytes + (sum(a.nbytes for a in M) if M else 0)
     d2h = rows * e2e["k"] * 8 + e2e["k"] * e2e["k"] * 8
     h2d_total = allreduce_max(dist, float(h2d)) * world
@@ -473,7 +484,7 @@ def run_b200(args):
     #      iterates are not the reference's Lanczos iterates. --------------------
     p2 = dict(params)
     p2["Residual method"] = 2
-    e2e2, wall2 = end_to_end(p2, 2)       # the first of the two also warms the pool for this path
+    e2e2, wall2, e2e2_walls = end_to_end(p2, 3)
     x_diff = None
     if world == 1 and "V" in e2e and "V" in e2e2:
         V1, T1, V2, T2 = e2e["V"], e2e["T"], e2e2["V"], e2e2["T"]
@@ -501,11 +512,14 @@ def run_b200(args):
         # the dominant kernel of an outer iteration: first kernel of the fused
         # residual-Lanczos step, g = [V AV B]' q (about half of all bytes moved)
         dk = kernels["lanczos_project"]
+        # ncu DRAM bytes of this launch at the N = 1 row count; not a measurement
+        # for the smaller per-rank blocks of N > 1
         traffic = None
-        try:
-            traffic = _json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("lanczos_dot")
-        except Exception:
-            pass
+        if world == 1 and rows == 16777216 and dk["k"] == 64:
+            try:
+                traffic = _json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("lanczos_dot")
+            except Exception:
+                pass
         roofline = {"bound": "hbm",
                     "kernel": "lanczos_dot_kernel (fused Lanczos update + [V AV B]'w, %d columns, "
                               "m=%d rows; timed through rails_mv_lanczos_project)"
@@ -530,8 +544,8 @@ def run_b200(args):
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": workload_name(args, kind, g, dim, n_b, params), "params": params,
-                   "window": "iterations W+1..W+K of one solve, convergence test off; fastest of %d "
-                             "identical windows" % len(all_ms),
+                   "window": "iterations W+1..W+K of one solve, convergence test off; median of %d "
+                             "identical windows (all listed in window_ms_per_step)" % len(all_ms),
                    "l2": "inputs >> L2 (no flush): V is %.0f MB per column" % (rows * 8 / 1e6),
                    "parallelism": "row partition over %d GPU(s)" % world,
                    "small_reductions": ("peer-memory mailboxes (NVLink P2P)" if lib.rails_cuda_comm_p2p()
@@ -545,7 +559,8 @@ def run_b200(args):
                 "converged": e2e["ret"] == 0, "space_size": int(e2e["k"]),
                 "setup_seconds": e2e["setup_seconds"], "solve_seconds": e2e["solve_seconds"],
                 "what": "rails_host_solve to tolerance 1e-4 with host CSR/B(/M) in, V/T out; "
-                        "%d iterations in %.3f s (fastest of 2 runs)" % (e2e["iterations"], wall)},
+                        "%d iterations in %.3f s (median of 3 runs)" % (e2e["iterations"], wall),
+                "all_runs_s": e2e_walls},
         "e2e_tsqr": {"value": e2e2["iterations"] / wall2, "unit": "iterations/s",
                      "time_to_tolerance_s": wall2, "iterations_to_tolerance": int(e2e2["iterations"]),
                      "converged": e2e2["ret"] == 0, "space_size": int(e2e2["k"]),
@@ -554,8 +569,11 @@ def run_b200(args):
                      "x_rel_diff_vs_e2e": x_diff,
                      "what": "the e2e solve with \"Residual method\" = 2: exact residual eigenpairs "
                              "from the tall-skinny QR of [B, V, AV, MV], iteration carried out on the "
-                             "R factors; same tolerance, host buffers in and out (fastest of 2 runs)"},
+                             "R factors; same tolerance, host buffers in and out (median of 3 runs)",
+                     "all_runs_s": e2e2_walls},
         "window_ms_per_step": all_ms,
+        "window_ms_per_step_min": min(all_ms), "window_ms_per_step_max": max(all_ms),
+        "window_spread": (max(all_ms) - min(all_ms)) / min(all_ms),
         "gpu_launches": int(res["timed_launches"]),
         "clocks": clocks,
         "roofline": roofline,

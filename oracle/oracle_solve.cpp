@@ -197,6 +197,10 @@ int solve_impl(
         return 102;
 
     std::srand(seed);
+    // a caller that made B itself with `srand(seed); B.random()` and passes it in
+    // asks for that std::rand() value to be skipped, so that V and the Lanczos
+    // start vectors get the values they get in a reference run
+    for (int i = 0; i < (int)P.get("Skip random draws", 0.0); ++i) (void)std::rand();
     const long long ld = m;
     vec B((size_t)ld * n_b);
     if (B_in) std::memcpy(B.data(), B_in, B.size() * sizeof(double));

@@ -118,6 +118,13 @@ int rails_host_solve_x(int rows, int global_rows, int row_offset,
     if (!A.device_handle())
         return 200;
 
+    KeyValueParameters params(nparams, keys, pvals);
+    // a caller that made B itself with `srand(seed); B.random()` and passes it in
+    // asks for that std::rand() value to be skipped ("Skip random draws" = 1), so
+    // that V and the Lanczos start vectors get the seeds of a reference run
+    for (int i = 0; i < params.get("Skip random draws", 0); ++i)
+        (void)std::rand();
+
     CudaMultiVectorWrapper B(global_rows, n_b);
     if (B_in)
     {
@@ -127,7 +134,6 @@ int rails_host_solve_x(int rows, int global_rows, int row_offset,
     else
         B.random();
 
-    KeyValueParameters params(nparams, keys, pvals);
     const bool use_mass = params.get("Use mass matrix", false) ||
                           params.get("M-orthogonalization", false);
     CudaOperatorWrapper M = A;

@@ -89,6 +89,66 @@ def lumped_mass(m, row_begin=0, row_end=None, seed=2):
             np.ascontiguousarray(d))
 
 
+_MINSTD_A, _MINSTD_P = 16807, 2147483647
+
+
+def _minstd_stream(seed, start, count):
+    """Draws start .. start+count-1 (0-based, the first draw is a*x0 mod p) of
+    minstd_rand0 seeded with `seed`, by jump-ahead: x_j = a^(j+1) x0 mod p."""
+    x0 = seed % _MINSTD_P or 1                  # linear_congruential_engine::seed
+    blk = 1 << 12
+    # a^1 .. a^blk mod p; products of two 31-bit numbers fit 64 bits
+    pw = np.empty(blk, dtype=np.uint64)
+    acc = 1
+    for i in range(blk):
+        acc = acc * _MINSTD_A % _MINSTD_P
+        pw[i] = acc
+    out = np.empty(count, dtype=np.uint64)
+    P = np.uint64(_MINSTD_P)
+    pos = 0
+    while pos < count:
+        n = min(blk, count - pos)
+        base = np.uint64(x0 * pow(_MINSTD_A, start + pos, _MINSTD_P) % _MINSTD_P)
+        out[pos:pos + n] = pw[:n] * base % P
+        pos += n
+    return out
+
+
+def reference_random(m, n, seed, row_begin=0, row_end=None):
+    """Rows [row_begin, row_end) of the m x n block StlWrapper::random() fills
+    (/root/reference/src/StlWrapper.cpp:414-423) when std::rand() returned
+    `seed`: a fresh std::default_random_engine (libstdc++: minstd_rand0), row-major
+    fill from uniform_real_distribution(-1, 1), two draws per double
+    (generate_canonical<double, 53>).  Same bits as the device kernel
+    (rails_mv_random) and as the reference itself (tests/test_oracle.py).
+    Returned column-major."""
+    if row_end is None:
+        row_end = m
+    rows = row_end - row_begin
+    x = _minstd_stream(seed, 2 * row_begin * n, 2 * rows * n).astype(np.float64)
+    R = 2147483646.0                            # max - min + 1
+    s = (x[0::2] - 1.0) + (x[1::2] - 1.0) * R
+    u = s / (R * R)
+    u[u >= 1.0] = np.nextafter(1.0, 0.0)
+    return np.asfortranarray((u * 2.0 + -1.0).reshape(rows, n))
+
+
+def first_rand_after_srand(seed=1):
+    """std::srand(seed); std::rand() of the C library (the value that seeds the
+    first random() of a reference run, test/LyapunovSolver_test.cpp:66-71)."""
+    import ctypes
+    libc = ctypes.CDLL(None)
+    libc.srand(ctypes.c_uint(seed))
+    return int(libc.rand())
+
+
+def reference_B(m, n_b, row_begin=0, row_end=None):
+    """`std::srand(1); B.random()` -- the B of SURVEY.md §8(d), this rank's rows.
+    A solve that is handed this B passes "Skip random draws" = 1 so that V and the
+    Lanczos start vectors get the std::rand() values of a reference run."""
+    return reference_random(m, n_b, first_rand_after_srand(1), row_begin, row_end)
+
+
 def partition_rows(m, nranks, rank):
     """Epetra_Map(m, 0, comm) linear map: first m % P ranks get one more row."""
     base, rem = divmod(m, nranks)

@@ -28,6 +28,23 @@ def test_random_stream_matches_reference(golden):
         lib.oracle_random(ctypes.c_longlong(m), n, ctypes.c_uint(s), ctypes.c_longlong(m // 2),
                           ctypes.c_longlong(m), harness.dptr(b), ctypes.c_longlong(m - m // 2))
         assert np.array_equal(b, a[m // 2:])
+        # the numpy restatement bench.py and the tests build B with
+        # (problems.reference_random): same bits, whole block and row slices
+        assert np.array_equal(problems.reference_random(m, n, s), a)
+        assert np.array_equal(problems.reference_random(m, n, s, m // 2, m), a[m // 2:])
+
+
+def test_reference_B_and_skipped_draw_reproduce_a_reference_run():
+    """`srand(1); B.random()` made on the host (problems.reference_B) + "Skip random
+    draws" = 1 walks the same path as letting the solve draw B itself."""
+    rp, ci, v = problems.laplacian(12, 2)
+    P = {"Tolerance": 1e-4, "Expand size": 1, "Lanczos iterations": 10}
+    own = harness.oracle_solve(rp, ci, v, 2, P, v_cap_cols=200)
+    Pb = dict(P)
+    Pb["Skip random draws"] = 1
+    given = harness.oracle_solve(rp, ci, v, 2, Pb, B=problems.reference_B(144, 2), v_cap_cols=200)
+    assert given["iterations"] == own["iterations"]
+    assert np.array_equal(given["rel"], own["rel"])
 
 
 def test_cgs2_matches_reference(golden):

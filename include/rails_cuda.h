@@ -250,6 +250,19 @@ int rails_csr_halo_plan(long long rows, long long global_rows, long long row_off
                         int nranks, const int *rowptr, const int *colidx,
                         int *local_col, int *nghost, int *ghost_global,
                         int *ghost_owner_row, int *need_from);
+/* New values on the same sparsity pattern (same order as the arrays given to
+ * rails_csr_create): a continuation step or a re-assembled Jacobian keeps the row
+ * blocks, the renumbered columns and the halo plan.  The reference replaces the
+ * Epetra_CrsMatrix behind the operator (src/main.cpp:66-98 per run). */
+int rails_csr_update_values(rails_csr_t A, const double *vals);
+/* test-only element access, entries of the sparsity pattern only (the (m, n)
+ * constructor + operator()(i, j) of src/Epetra_OperatorWrapper.cpp:224-282,
+ * test/GenericOperatorWrapper_test.cpp:36-46) */
+int rails_csr_get_value(rails_csr_t A, long long row, long long col, double *value);
+int rails_csr_set_value(rails_csr_t A, long long row, long long col, double value);
+/* the operator as a dense rows x cols block in Out[:, oc0 ..) (small operators:
+ * Operator::norm() forms A'A explicitly, src/Epetra_OperatorWrapper.cpp:115-145) */
+int rails_csr_to_dense(rails_csr_t A, rails_mv_t Out, int oc0);
 long long rails_csr_rows(rails_csr_t A);
 long long rails_csr_nnz(rails_csr_t A);
 /* Y[:, yc0..yc0+ncols) = op(A) * X[:, xc0..xc0+ncols);  trans != 0 applies A'

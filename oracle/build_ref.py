@@ -79,6 +79,23 @@ def build(verbose=True):
             ["-L" + prod, "-lrails_host", "-lrails_cuda", blas,
              "-Wl,--disable-new-dtags,-rpath," + libdir + ":$ORIGIN/../../rails_b200"])
 
+    # The reference's own typed test suites, unmodified, with the product's wrapper
+    # classes added to their Types<> lists through the gtest stand-in
+    # (tests/cpp/gtest_shim), and its algorithm tests restated on those classes
+    # (tests/cpp/conformance/).  Binaries: oracle/_ref/conformance_<suite>.
+    conf = os.path.join(ROOT, "tests", "cpp", "conformance")
+    if os.path.exists(os.path.join(prod, "librails_host.so")):
+        inc = ["-I" + REF, "-I" + os.path.join(REF, "test"), "-I" + os.path.join(ROOT, "tests", "cpp", "gtest_shim"),
+               "-I" + conf, "-I" + os.path.join(prod, "host"), "-I" + os.path.join(ROOT, "include")]
+        stl = [os.path.join(REF, "src", f) for f in ("StlWrapper.cpp", "StlVector.cpp", "LapackWrapper.cpp",
+                                                     "Timer.cpp")]
+        for suite, extra in (("densematrix", []), ("multivector", []), ("operator", []),
+                             ("solver", [os.path.join(REF, "src", "SlicotWrapper.cpp")])):
+            run(["g++", "-std=c++17", "-O2"] + inc +
+                ["-o", os.path.join(OUT, "conformance_" + suite), os.path.join(conf, suite + "_suite.cpp")] +
+                stl + extra + ["-L" + prod, "-lrails_host", "-lrails_cuda", blas,
+                               "-Wl,--disable-new-dtags,-rpath," + libdir + ":$ORIGIN/../../rails_b200"])
+
     csr_entry = os.path.join(HERE, "ref_entry_csr.cpp")
     if os.path.exists(csr_entry):
         # StlWrapper stays the DenseMatrix of this arm, as in the reference

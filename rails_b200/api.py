@@ -116,6 +116,10 @@ CUDA_SYMBOLS = [
     ("rails_csr_free", I, [P]),
     ("rails_csr_halo_plan", I, [LL, LL, LL, I, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p,
                                 c_int_p]),
+    ("rails_csr_update_values", I, [P, c_double_p]),
+    ("rails_csr_get_value", I, [P, LL, LL, c_double_p]),
+    ("rails_csr_set_value", I, [P, LL, LL, D]),
+    ("rails_csr_to_dense", I, [P, P, I]),
     ("rails_csr_rows", LL, [P]),
     ("rails_csr_nnz", LL, [P]),
     ("rails_csr_spmm", I, [P, I, P, I, I, P, I]),

@@ -552,6 +552,120 @@ extern "C" int rails_csr_free(rails_csr_t A)
     return RAILS_OK;
 }
 
+// ---- element access and value updates -------------------------------------------
+
+namespace
+{
+
+// position of entry (row, col) in the value array, or -1 (host-side lookup over the
+// row's column indices; test-only path)
+int locate_entry(rails_csr_s *A, long long row, long long col, long long *pos)
+{
+    if (A->partitioned)
+        return rails::fail(RAILS_ERR_ARG, "csr element access is not available on a row-partitioned operator");
+    if (row < 0 || row >= A->rows || col < 0 || col >= A->global_cols)
+        return rails::fail(RAILS_ERR_ARG, "csr element (%lld, %lld) outside %lld x %lld", row, col, A->rows,
+                           A->global_cols);
+    int rp[2];
+    RAILS_CUDA_TRY(cudaMemcpyAsync(rp, A->rowptr + row, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx().stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    std::vector<int> cols(std::max(rp[1] - rp[0], 1));
+    if (rp[1] > rp[0])
+    {
+        RAILS_CUDA_TRY(cudaMemcpyAsync(cols.data(), A->colidx + rp[0], (size_t)(rp[1] - rp[0]) * sizeof(int),
+                                       cudaMemcpyDeviceToHost, ctx().stream));
+        RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    }
+    *pos = -1;
+    for (int p = 0; p < rp[1] - rp[0]; ++p)
+        if (cols[p] == (int)col) { *pos = rp[0] + p; break; }
+    return RAILS_OK;
+}
+
+void drop_transpose(rails_csr_s *A)
+{
+    if (A->transposed) { free_csr(A->transposed); A->transposed = nullptr; }
+}
+
+__global__ void __launch_bounds__(256)
+csr_to_dense_kernel(const int *__restrict__ rowptr, const int *__restrict__ colidx,
+                    const double *__restrict__ vals, long long rows, double *__restrict__ out, long long ld)
+{
+    for (long long r = (long long)blockIdx.x * 256 + threadIdx.x; r < rows; r += (long long)gridDim.x * 256)
+        for (int p = rowptr[r]; p < rowptr[r + 1]; ++p)
+            out[r + (size_t)colidx[p] * ld] += vals[p];        // duplicates add up, as InsertGlobalValues sums them
+}
+
+}
+
+// Test-only element access (the reference's Operator keeps `(m, n)` + operator()(i, j)
+// for its typed tests: src/Epetra_OperatorWrapper.cpp:224-282): only entries that
+// are part of the sparsity pattern can be read or written.
+extern "C" int rails_csr_get_value(rails_csr_t A, long long row, long long col, double *value)
+{
+    RAILS_REQUIRE_READY();
+    if (!A || !value) return rails::fail(RAILS_ERR_ARG, "csr_get_value: null argument");
+    long long pos = -1;
+    int rc = locate_entry(A, row, col, &pos);
+    if (rc) return rc;
+    *value = 0.0;
+    if (pos < 0) return RAILS_OK;                   // outside the pattern: a structural zero
+    RAILS_CUDA_TRY(cudaMemcpyAsync(value, A->vals + pos, sizeof(double), cudaMemcpyDeviceToHost, ctx().stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    return RAILS_OK;
+}
+
+extern "C" int rails_csr_set_value(rails_csr_t A, long long row, long long col, double value)
+{
+    RAILS_REQUIRE_READY();
+    if (!A) return rails::fail(RAILS_ERR_ARG, "csr_set_value: null operator");
+    long long pos = -1;
+    int rc = locate_entry(A, row, col, &pos);
+    if (rc) return rc;
+    if (pos < 0)
+        return rails::fail(RAILS_ERR_ARG, "csr_set_value: (%lld, %lld) is not in the sparsity pattern", row, col);
+    RAILS_CUDA_TRY(cudaMemcpyAsync(A->vals + pos, &value, sizeof(double), cudaMemcpyHostToDevice, ctx().stream));
+    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
+    drop_transpose(A);
+    return RAILS_OK;
+}
+
+// New values on the same sparsity pattern, in the order of the arrays given to
+// rails_csr_create (a continuation step A + delta I, or a re-assembled Jacobian):
+// the row blocks, the renumbered columns and the halo plan are kept.
+extern "C" int rails_csr_update_values(rails_csr_t A, const double *vals)
+{
+    RAILS_REQUIRE_READY();
+    if (!A || (A->nnz > 0 && !vals)) return rails::fail(RAILS_ERR_ARG, "csr_update_values: null argument");
+    if (A->nnz)
+    {
+        int rc = rails::copy_h2d(A->vals, vals, (size_t)A->nnz * sizeof(double));
+        if (rc) return rc;
+    }
+    drop_transpose(A);
+    return RAILS_OK;
+}
+
+// Out[:, oc0 .. oc0 + cols) = the operator as a dense block (small operators only:
+// Operator::norm() of the reference forms A'A explicitly,
+// src/Epetra_OperatorWrapper.cpp:115-145)
+extern "C" int rails_csr_to_dense(rails_csr_t A, rails_mv_t Out, int oc0)
+{
+    RAILS_REQUIRE_READY();
+    if (!A || !Out) return rails::fail(RAILS_ERR_ARG, "csr_to_dense: null argument");
+    if (A->partitioned)
+        return rails::fail(RAILS_ERR_ARG, "csr_to_dense is not available on a row-partitioned operator");
+    if (Out->rows != A->rows || oc0 < 0 || oc0 + A->global_cols > Out->cols)
+        return rails::fail(RAILS_ERR_ARG, "csr_to_dense: result must be %lld x %lld", A->rows, A->global_cols);
+    int rc = rails_mv_fill(Out, oc0, (int)A->global_cols, 0.0);
+    if (rc || A->rows == 0) return rc;
+    const int nb = (int)std::min<long long>((A->rows + 255) / 256, (long long)ctx().sm_count * 8);
+    RAILS_LAUNCH(csr_to_dense_kernel, nb, 256, 0, A->rowptr, A->colidx, A->vals, A->rows,
+                 Out->data + (size_t)oc0 * Out->ld, Out->ld);
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
+}
+
 extern "C" long long rails_csr_rows(rails_csr_t A) { return A ? A->rows : -1; }
 extern "C" long long rails_csr_nnz(rails_csr_t A) { return A ? A->nnz : -1; }
 

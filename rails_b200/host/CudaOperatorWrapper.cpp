@@ -1,6 +1,9 @@
 #include "CudaOperatorWrapper.hpp"
+#include "OperatorEigs.hpp"
 
+#include <cmath>
 #include <iostream>
+#include <vector>
 
 namespace RAILS
 {
@@ -35,6 +38,51 @@ CudaOperatorWrapper::CudaOperatorWrapper(int m, int n, const int *rowptr, const 
                                          const double *vals)
     : CudaOperatorWrapper(m, m, n, 0, rowptr, colidx, vals)
 {}
+
+CudaOperatorWrapper::CudaOperatorWrapper(int m, int n)
+    : m_(m), n_(n), transpose_(false)
+{
+    std::vector<int> rowptr(m + 1), colidx((size_t)m * n);
+    std::vector<double> vals((size_t)m * n, 0.0);
+    for (int i = 0; i <= m; ++i)
+        rowptr[i] = i * n;
+    for (int i = 0; i < m; ++i)
+        for (int j = 0; j < n; ++j)
+            colidx[(size_t)i * n + j] = j;
+    rails_csr_t h = nullptr;
+    int rc = rails_csr_create(m, m, n, 0, rowptr.data(), colidx.data(), vals.data(), &h);
+    check(rc, "constructor");
+    if (!rc)
+        ptr_ = std::make_shared<Handle>(h);
+}
+
+CudaOperatorWrapper::Element::operator double() const
+{
+    double v = 0.0;
+    check(rails_csr_get_value(h_, row_, col_, &v), "operator()");
+    return v;
+}
+
+CudaOperatorWrapper::Element &CudaOperatorWrapper::Element::operator=(double v)
+{
+    check(rails_csr_set_value(h_, row_, col_, v), "operator()");
+    return *this;
+}
+
+CudaOperatorWrapper::Element CudaOperatorWrapper::operator()(int i, int j)
+{
+    return Element(ptr_ ? ptr_->h : nullptr, i, j);
+}
+
+double CudaOperatorWrapper::operator()(int i, int j) const
+{
+    return (double)Element(ptr_ ? ptr_->h : nullptr, i, j);
+}
+
+int CudaOperatorWrapper::eigs(CudaMultiVectorWrapper &V, HostDenseMatrix &D, int num, double tol) const
+{
+    return symmetric_eigs(*this, V, D, num, tol);
+}
 
 CudaOperatorWrapper::CudaOperatorWrapper(std::shared_ptr<const Action> const &action)
     : action_(action), m_(action ? action->rows() : -1), n_(action ? action->cols() : -1),
@@ -81,10 +129,26 @@ CudaMultiVectorWrapper CudaOperatorWrapper::operator*(CudaMultiVectorWrapper con
 double CudaOperatorWrapper::norm() const
 {
     double out = 0.0;
-    if (ptr_)
-        check(rails_csr_norm2(ptr_->h, &out), "norm");
-    else if (action_)
-        std::cerr << "CudaOperatorWrapper::norm is not available for a composite operator" << std::endl;
+    if (!ptr_)
+    {
+        if (action_)
+            std::cerr << "CudaOperatorWrapper::norm is not available for a composite operator" << std::endl;
+        return out;
+    }
+    if (n_ <= 512 && m_ <= 65536 && rails_cuda_comm_size() == 1)
+    {
+        // as the reference: A'A explicitly, all its eigenvalues, sqrt of the largest.
+        // A'A comes from the same inner-product kernel MultiVector::dot uses.
+        CudaMultiVectorWrapper dense(m_, n_);
+        int rc = rails_csr_to_dense(ptr_->h, dense.device_handle(), dense.device_col0());
+        check(rc, "norm");
+        if (rc)
+            return out;
+        HostDenseMatrix gram = dense.dot(dense), vectors, values;
+        gram.eigs(vectors, values);
+        return std::sqrt(values.norm_inf());
+    }
+    check(rails_csr_norm2(ptr_->h, &out), "norm");
     return out;
 }
 

@@ -32,6 +32,20 @@ public:
         virtual int cols() const = 0;
     };
 
+    // test-only element access, entries of the sparsity pattern (the reference
+    // keeps `(m, n)` + operator()(i, j) on its Operator for the typed tests,
+    // src/Epetra_OperatorWrapper.cpp:224-282)
+    class Element
+    {
+        rails_csr_t h_;
+        int row_, col_;
+    public:
+        Element(rails_csr_t h, int row, int col) : h_(h), row_(row), col_(col) {}
+        operator double() const;
+        Element &operator=(double v);
+        Element &operator=(Element const &o) { return *this = (double)o; }
+    };
+
 private:
     struct Handle
     {
@@ -58,6 +72,12 @@ public:
     // composite operator (implicit, like the reference's conversion from
     // Teuchos::RCP<Epetra_Operator>, src/Epetra_OperatorWrapper.hpp)
     CudaOperatorWrapper(std::shared_ptr<const Action> const &action);
+    // test-only: an m x n operator whose sparsity pattern is FULL, all entries
+    // zero, to be filled through operator()(i, j) (the reference inserts all n
+    // columns of every row, src/Epetra_OperatorWrapper.cpp:224-250)
+    CudaOperatorWrapper(int m, int n);
+    Element operator()(int i, int j = 0);
+    double operator()(int i, int j = 0) const;
     bool valid() const { return ptr_ || action_; }
 
     virtual ~CudaOperatorWrapper() {}
@@ -65,7 +85,15 @@ public:
     CudaOperatorWrapper transpose() const;
     CudaMultiVectorWrapper operator*(CudaMultiVectorWrapper const &other) const;
 
+    // 2-norm.  Small operators as the reference does it -- A'A formed explicitly,
+    // all eigenvalues, sqrt of the largest (src/Epetra_OperatorWrapper.cpp:115-145)
+    // -- larger ones by power iteration on A'A.
     double norm() const;
+
+    // The `num` eigenvalues of largest magnitude of a SYMMETRIC operator and their
+    // eigenvectors (src/Epetra_OperatorWrapper.cpp:147-222, Anasazi block
+    // Krylov-Schur there; not used by the solver loop): OperatorEigs.hpp.
+    int eigs(CudaMultiVectorWrapper &V, HostDenseMatrix &D, int num, double tol = 1e-6) const;
 
     int M() const;
     int N() const;

@@ -7,8 +7,9 @@ travels to the GPU box with the gpurun snapshot).
 
     oracle/_ref/librails_ref_stl.so   reference loop + reference StlWrapper
                                       (dense A; config C1 and the unit pins)
-    oracle/_ref/librails_ref_csr.so   reference loop + oracle CSR/OpenMP
-                                      wrappers (sparse CPU arm, configs C2-C5)
+    oracle/_ref/librails_ref_csr.so   reference loop + reference StlWrapper +
+                                      a CSR/OpenMP Operator (oracle/cpu_backend.cpp):
+                                      the sparse CPU arm, any size, M = I
 
 Flags follow the reference's no-build-type default `-O2` (CMakeLists.txt:16),
 NOT its Release `-O3 -ffast-math` (CMakeLists.txt:18), so that the numbers are
@@ -96,11 +97,12 @@ def build(verbose=True):
                 stl + extra + ["-L" + prod, "-lrails_host", "-lrails_cuda", blas,
                                "-Wl,--disable-new-dtags,-rpath," + libdir + ":$ORIGIN/../../rails_b200"])
 
-    csr_entry = os.path.join(HERE, "ref_entry_csr.cpp")
-    if os.path.exists(csr_entry):
-        # StlWrapper stays the DenseMatrix of this arm, as in the reference
-        run(common + ["-o", os.path.join(OUT, "librails_ref_csr.so"), csr_entry,
-                      os.path.join(HERE, "cpu_backend.cpp")] + ref_srcs + [shim] + link)
+    # reference loop + reference StlWrapper (MultiVector, DenseMatrix) + CSR/OpenMP
+    # Operator: the sparse CPU arm.  -ffp-contract=off keeps the operator's row sums
+    # free of FMA contraction (the recipe's -O2 would contract on an FMA target).
+    run(common + ["-ffp-contract=off", "-o", os.path.join(OUT, "librails_ref_csr.so"),
+                  os.path.join(HERE, "ref_entry_csr.cpp"), os.path.join(HERE, "cpu_backend.cpp")] +
+        ref_srcs + [shim] + link)
     return True
 
 

@@ -124,6 +124,48 @@ def ref_stl_solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, v_cap_cols=
     return out
 
 
+_ref_csr = None
+
+
+def ref_csr():
+    """The reference loop over its own StlWrapper + a CSR/OpenMP operator
+    (oracle/_ref/librails_ref_csr.so); None when oracle/_ref was never built."""
+    global _ref_csr
+    path = os.path.join(ROOT, "oracle", "_ref", "librails_ref_csr.so")
+    if _ref_csr is None and os.path.exists(path):
+        _ref_csr = ctypes.CDLL(path)
+    return _ref_csr
+
+
+def ref_csr_solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, skip_draws=0, v_cap_cols=0,
+                  hist_cap=4096):
+    """Sparse problems of any size through the UNMODIFIED reference loop on the CPU.
+    `seconds` holds the time at which each iteration's progress line was printed."""
+    lib = ref_csr()
+    m = rowptr.size - 1
+    nk, karr, pv = _params(params)
+    ha, hr, hs = np.zeros(hist_cap), np.zeros(hist_cap), np.zeros(hist_cap)
+    hl, k = ctypes.c_int(0), ctypes.c_int(0)
+    V = T = None
+    if v_cap_cols > 0:
+        V = np.zeros((m, v_cap_cols), order="F")
+        T = np.zeros((v_cap_cols, v_cap_cols), order="F")
+    ss = ctypes.c_double(0)
+    Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
+    ret = lib.ref_csr_solve(
+        ctypes.c_int(m), iptr(rowptr), iptr(colidx), dptr(vals), ctypes.c_int(n_b), dptr(Bc),
+        ctypes.c_uint(seed), ctypes.c_int(skip_draws), ctypes.c_int(nk), karr, dptr(pv),
+        ctypes.c_int(hist_cap), dptr(ha), dptr(hr), dptr(hs), ctypes.byref(hl), ctypes.byref(k),
+        ctypes.c_int(v_cap_cols), dptr(V), dptr(T), ctypes.byref(ss))
+    n = min(hl.value, hist_cap)
+    out = dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
+               seconds=hs[:n].copy(), solve_seconds=ss.value)
+    if V is not None and k.value <= v_cap_cols:
+        out["V"] = V[:, :k.value]
+        out["T"] = T[:k.value, :k.value]
+    return out
+
+
 def lowrank_rel_diff(V1, T1, V2, T2):
     """||V1 T1 V1' - V2 T2 V2'||_F / ||V2 T2 V2'||_F through the factors."""
     G11, G22, G12 = V1.T @ V1, V2.T @ V2, V1.T @ V2

@@ -225,3 +225,28 @@ def test_generalized_branch_against_dense_solution():
     b = harness.oracle_solve(rp, ci, v, 1, P1, B=B, v_cap_cols=m, M=I)
     assert a["iterations"] == b["iterations"]
     assert np.max(np.abs(a["rel"] - b["rel"]) / a["rel"]) < 1e-6
+
+
+@pytest.mark.parametrize("name", ["C1", "lap3d_g8", "lap2d_g16"])
+def test_reference_loop_over_csr_operator_matches_reference_golden(golden, name):
+    """oracle/_ref/librails_ref_csr.so -- the unmodified reference loop + the
+    reference's StlWrapper + a CSR/OpenMP operator (the sparse CPU arm of bench.py)
+    -- against the goldens of the reference's own dense Stl build: same iteration
+    count and space size, history to the spread the reference shows against itself
+    between BLAS thread counts (tests/golden/ref_self_stability.json)."""
+    if harness.ref_csr() is None:
+        pytest.skip("oracle/_ref/librails_ref_csr.so was not built")
+    from golden.make_golden import SOLVES
+    kind, g, dim, n_b, P = SOLVES[name]
+    rp, ci, v = problems.build(kind, g, dim)
+    r = harness.ref_csr_solve(rp, ci, v, n_b, P, v_cap_cols=400)
+    ret, iters, k = golden[name + "_ret"]
+    assert (r["ret"], r["iterations"], r["k"]) == (ret, iters, k)
+    ref_rel = golden[name + "_rel"]
+    rel = np.abs(r["rel"] - ref_rel) / ref_rel
+    assert np.max(rel[:10]) < 1e-9
+    assert np.max(rel) < 1e-6
+    Xs = (r["V"][:64] @ r["T"]) @ r["V"][:64].T
+    ref = golden[name + "_Xcorner"]
+    assert np.linalg.norm(Xs - ref) / np.linalg.norm(ref) < 1e-6
+    assert np.all(np.diff(r["seconds"]) >= 0) and r["seconds"][-1] <= r["solve_seconds"] + 1e-3

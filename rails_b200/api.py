@@ -54,6 +54,8 @@ def host():
         lib.rails_host_last_timed_launches.restype = ctypes.c_longlong
         lib.rails_host_lu_factor.restype = ctypes.c_void_p
         lib.rails_host_schur_create.restype = ctypes.c_void_p
+        lib.rails_host_session_create.restype = ctypes.c_void_p
+        lib.rails_host_session_setup_seconds.restype = ctypes.c_double
         _host = lib
     return _host
 
@@ -243,6 +245,78 @@ def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, r
         out["V"] = V[:, :k.value]
         out["T"] = T[:k.value, :k.value]
     return out
+
+
+class Session:
+    """rails_host_session_*: operator(s), B and the solution basis stay on the device
+    between solves (continuation: update_operator + "Restart from solution" = 1)."""
+
+    def __init__(self, rowptr, colidx, vals, n_b, B=None, seed=1, global_rows=None, row_offset=0, M=None,
+                 skip_draws=0):
+        lib = host()
+        self.rows = rowptr.size - 1
+        self.global_rows = self.rows if global_rows is None else global_rows
+        Bc = None if B is None else np.asfortranarray(B, dtype=np.float64)
+        mrp, mci, mv = M if M is not None else (None, None, None)
+        self.h = ctypes.c_void_p(lib.rails_host_session_create(
+            ctypes.c_int(self.rows), ctypes.c_int(self.global_rows), ctypes.c_int(row_offset),
+            iptr(rowptr), iptr(colidx), dptr(vals), iptr(mrp), iptr(mci), dptr(mv),
+            ctypes.c_int(n_b), dptr(Bc), ctypes.c_uint(seed), ctypes.c_int(skip_draws)))
+        if not self.h:
+            raise RailsError("rails_host_session_create failed: %s" % cuda().rails_cuda_last_error().decode())
+        self.setup_seconds = lib.rails_host_session_setup_seconds(self.h)
+
+    def update_operator(self, vals):
+        v = np.ascontiguousarray(vals, dtype=np.float64)
+        if host().rails_host_session_update_operator(self.h, dptr(v)):
+            raise RailsError("rails_host_session_update_operator failed: %s" % cuda().rails_cuda_last_error().decode())
+
+    def set_start(self, V0):
+        V0 = np.asfortranarray(V0, dtype=np.float64)
+        if host().rails_host_session_set_start(self.h, ctypes.c_int(V0.shape[1]), dptr(V0)):
+            raise RailsError("rails_host_session_set_start failed")
+
+    def solve(self, params, time_from=0, time_to=0, hist_cap=4096):
+        lib = host()
+        keys = [k.encode() for k in params]
+        karr = (ctypes.c_char_p * len(keys))(*keys)
+        pv = np.array([float(v) for v in params.values()], dtype=np.float64)
+        ha, hr = np.zeros(hist_cap), np.zeros(hist_cap)
+        hk, hs = np.zeros(hist_cap, dtype=np.int32), np.zeros(hist_cap)
+        hl, k = ctypes.c_int(0), ctypes.c_int(0)
+        tm = ctypes.c_float(0)
+        ss, sd = ctypes.c_double(0), ctypes.c_double(0)
+        ret = lib.rails_host_session_solve(
+            self.h, ctypes.c_int(len(keys)), karr, dptr(pv), ctypes.c_int(hist_cap), dptr(ha), dptr(hr),
+            iptr(hk), dptr(hs), ctypes.byref(hl), ctypes.byref(k), ctypes.c_int(time_from),
+            ctypes.c_int(time_to), ctypes.byref(tm), ctypes.byref(ss), ctypes.byref(sd))
+        n = min(hl.value, hist_cap)
+        return dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
+                    space=hk[:n].copy(), seconds=hs[:n].copy(), timed_ms=tm.value, solve_seconds=ss.value,
+                    dense_solve_seconds=sd.value, sections=lib.rails_host_last_sections().decode(),
+                    timed_launches=lib.rails_host_last_timed_launches())
+
+    def download(self):
+        """(V, T) of the last solution: this rank's rows of V and the k x k T."""
+        k = host().rails_host_session_space_size(self.h)
+        if k < 0:
+            raise RailsError("the session holds no solution")
+        V = np.zeros((self.rows, max(k, 1)), order="F")
+        T = np.zeros((max(k, 1), max(k, 1)), order="F")
+        if host().rails_host_session_download(self.h, ctypes.c_int(max(k, 1)), dptr(V), dptr(T)) < 0:
+            raise RailsError("rails_host_session_download failed")
+        return V[:, :k], T[:k, :k]
+
+    def free(self):
+        if self.h:
+            host().rails_host_session_free(self.h)
+            self.h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 # ---- MatrixMarket / parameter files / post-processing (host library) ---------

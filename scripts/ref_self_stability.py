@@ -121,6 +121,11 @@ def main():
         rec["history_spread_same_count"] = max(
             [v for lab, v in rec["max_rel_history_diff_vs_threads1"].items()
              if rec["iterations"][lab] == rec["iterations"]["threads=1"]] or [0.0])
+        # the 1-thread default-build run itself: what the GPU parity tests compare with
+        rec["reference"] = {"ret": base[name]["ret"], "iterations": base[name]["iterations"],
+                            "k": base[name]["k"], "rel": base[name]["rel"]}
+        rec["problem"] = {"kind": CASES[name][0], "g": CASES[name][1], "dim": CASES[name][2],
+                          "n_b": CASES[name][3], "params": CASES[name][4]}
         out[name] = rec
     path = os.path.join(ROOT, "tests", "golden", "ref_self_stability.json")
     json.dump({"cases": out, "how": "scripts/ref_self_stability.py: unmodified reference loop + StlWrapper, "

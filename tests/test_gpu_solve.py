@@ -273,3 +273,38 @@ def test_timed_window_and_launch_counter(gpu):
     assert d["timed_ms"] > 0
     assert gpu.cuda().rails_cuda_kernel_launches() - n0 > 12 * 40
     assert "resid_lanczos" in d["sections"] and "dense_solve" in d["sections"]
+
+
+def test_session_continuation_stays_on_the_device(gpu):
+    """rails_host_session_*: continuation of test/LyapunovSolver_test.cpp:312-352 with
+    the operator values replaced in place and the start basis taken from the device.
+    Same answer as the host-buffer route (V downloaded, operator re-created, V0
+    uploaded), bit for bit: both run the same kernels on the same data."""
+    rp, ci, v = problems.laplacian(24, 3)
+    m = rp.size - 1
+    P = {"Tolerance": 1e-6, "Expand size": 1, "Lanczos iterations": 6}
+    B = problems.reference_B(m, 2)
+    s = gpu.Session(rp, ci, v, 2, B=B)
+    first = s.solve(P)
+    assert first["ret"] == 0
+    V1, T1 = s.download()
+    one_shot = gpu.solve(rp, ci, v, 2, P, B=B, v_cap_cols=400)
+    assert one_shot["iterations"] == first["iterations"] and np.array_equal(one_shot["rel"], first["rel"])
+    assert np.array_equal(one_shot["V"], V1) and np.array_equal(one_shot["T"], T1)
+
+    v2 = problems.shift_diagonal(rp, ci, v, -0.01)
+    Pw = dict(P)
+    Pw["Restart from solution"] = 1
+    Pw["Random seed"] = 1          # the one-shot route re-seeds; make the session do the same
+    s.update_operator(v2)
+    warm = s.solve(Pw)
+    Vw, Tw = s.download()
+    assert warm["ret"] == 0 and warm["iterations"] < first["iterations"] // 2
+    host_route = gpu.solve(rp, ci, v2, 2, Pw, B=B, v_cap_cols=400, V0=V1)
+    assert host_route["iterations"] == warm["iterations"]
+    assert np.array_equal(host_route["rel"], warm["rel"])
+    assert np.array_equal(host_route["V"], Vw) and np.array_equal(host_route["T"], Tw)
+    # and it is a solution of the shifted problem: same X as a cold solve, to the tolerance
+    cold = gpu.solve(rp, ci, v2, 2, P, B=B, v_cap_cols=400)
+    assert harness.lowrank_rel_diff(Vw, Tw, cold["V"], cold["T"]) < 300 * P["Tolerance"]
+    s.free()

@@ -189,10 +189,16 @@ def test_block_errors(gpu):
     assert lib.rails_mv_multi_gemv(1, hs, c0, nn, gpu.dptr(g), A.h, 2, None, 0, ctypes.byref(al)) == 2
 
 
-@pytest.mark.parametrize("kind,g,dim,n_b", [("laplacian", 40, 2, 1), ("convdiff", 12, 3, 3)])
-def test_fused_loop_matches_unfused_loop(gpu, kind, g, dim, n_b):
+# cases the reference reproduces against itself (tests/golden/ref_self_stability.json):
+# with n = 1 and L = 10 on the 2-D Laplacian 40^2 the reference's own iteration count
+# moves between 74 and 85 under rounding-level changes, so that case proves nothing
+@pytest.mark.parametrize("kind,g,dim,n_b,L", [("laplacian", 40, 2, 2, 4), ("convdiff", 12, 3, 3, 10)])
+def test_fused_loop_matches_unfused_loop(gpu, kind, g, dim, n_b, L):
     rp, ci, v = problems.build(kind, g, dim)
-    Pm = {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 10}
+    # a fixed number of iterations: what happens a hundred iterations into a solve is
+    # rounding-chaotic for any two implementations (tests/test_gpu_solve.py)
+    Pm = {"Tolerance": 1e-13, "Maximum iterations": 30, "Minimize solution space": 0, "Expand size": 1,
+          "Lanczos iterations": L}
     runs = {}
     for mode in ("1", "step", "0"):      # device-resident chain, per-step fused, operation by operation
         os.environ["RAILS_FUSED_LANCZOS"] = mode

@@ -1,17 +1,20 @@
 """GPU parity tests of the whole hot path: rails_host_solve (solver loop over
-the CUDA wrapper classes, through the C entry point) against
-  * the reference's own outputs (tests/golden/ref_golden.npz, generated from
-    the unmodified reference loop + StlWrapper by tests/golden/make_golden.py),
-  * the CPU oracle on the same seeded inputs at sizes it finishes in seconds.
+the CUDA wrapper classes, through the C entry point) against the REFERENCE ITSELF.
 
-Bars (BASELINE.json north_star): same iteration count, residual history within
-1e-8 relative, |X_gpu - X_ref|_F / |X_ref|_F <= 1e-8 -- where the reference
-itself is reproducible to that level.  The reference differs from ITSELF by
-1.3e-8 between 1 and 8 BLAS threads on C1 after its restarts (each compression
-restart re-amplifies rounding differences; DESIGN.md "Reproducibility"), so the
-1e-8 bar is applied up to the first restart and 1e-5 after it, exactly as
-tests/test_oracle.py does for the CPU oracle against the same goldens.
+tests/golden/ref_self_stability.json (scripts/ref_self_stability.py, run in the build
+container) holds, for 16 problems, the unmodified reference loop + StlWrapper with one
+BLAS thread -- iteration count, space size, residual history -- and how much the
+reference moves AGAINST ITSELF when only rounding changes (2/3/4/8 BLAS threads, an
+FMA-contracted build).  The bars of BASELINE.json's north star -- same iteration
+count, history within 1e-8, X within 1e-8 -- are applied wherever the reference
+meets them against itself; where it does not, the bar is ten times the reference's
+own spread, per case, and where even its iteration count moves (lap2d_g16: 30 or 32;
+lap2d_g128: 85 or 93; ...) the GPU run must land inside the reference's own range.
+Measured values: profiles/r02_parity.md (scripts/parity_report.py).
 """
+import json
+import os
+
 import numpy as np
 import pytest
 
@@ -21,97 +24,93 @@ from rails_b200 import problems
 
 pytestmark = pytest.mark.gpu
 
+STABILITY = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden",
+                                        "ref_self_stability.json")))["cases"]
+MODES = {"chain": "1", "step": "step", "plain": "0"}
+
 
 def _first_restart(space, iters):
     r = np.where(np.diff(space) < 0)[0]
     return r[0] + 1 if r.size else iters
 
 
-@pytest.mark.parametrize("name", sorted(SOLVES))
-def test_solve_matches_reference_golden(gpu, golden, name):
-    kind, g, dim, n_b, P = SOLVES[name]
-    rp, ci, v = problems.build(kind, g, dim)
-    o = gpu.solve(rp, ci, v, n_b, P, v_cap_cols=400)
-    ret, iters, k = golden[name + "_ret"]
-    assert o["ret"] == ret
-    ref_rel = golden[name + "_rel"]
-    if P["Expand size"] > 1:
-        # see tests/test_oracle.py: only the early history and the converged
-        # answer are reproducible across implementations for e > 1
-        rel = np.abs(o["rel"][:8] - ref_rel[:8]) / ref_rel[:8]
-        assert np.max(rel) < 1e-8
-        assert abs(o["iterations"] - iters) <= 0.1 * iters
-        Xs = (o["V"][:64] @ o["T"]) @ o["V"][:64].T
-        ref = golden[name + "_Xcorner"]
-        assert np.linalg.norm(Xs - ref) / np.linalg.norm(ref) < 1e-3
-        return
-    if name == "lap2d_g16":
-        # m = 256, n = 1, L = 10: the residual operator has rank 2k+1 < L for the
-        # first iterations, Lanczos runs past a breakdown and the path from there
-        # on is decided by rounding noise (DESIGN.md "Reproducibility"): the
-        # per-step fused loop reproduces the reference's 30 iterations, the
-        # device-resident chain (k x k products rounded differently) needs 31
-        assert abs(o["iterations"] - iters) <= 2
-        rel = np.abs(o["rel"][:3] - ref_rel[:3]) / ref_rel[:3]
-        assert np.max(rel) < 1e-8
-        Xs = (o["V"][:64] @ o["T"]) @ o["V"][:64].T
-        ref = golden[name + "_Xcorner"]
-        assert np.linalg.norm(Xs - ref) / np.linalg.norm(ref) < 1e-3
-        return
-    assert o["iterations"] == iters
-    assert o["k"] == k
-    rel = np.abs(o["rel"] - ref_rel) / ref_rel
-    first = _first_restart(o["space"], iters)
-    assert np.max(rel[:min(first, 10)]) < 1e-8
-    assert np.max(rel[:first]) < 1e-6
-    assert np.max(rel) < 1e-5
-    Xs = (o["V"][:64] @ o["T"]) @ o["V"][:64].T
-    ref = golden[name + "_Xcorner"]
-    assert np.linalg.norm(Xs - ref) / np.linalg.norm(ref) < 1e-6
+@pytest.mark.parametrize("mode", sorted(MODES))
+@pytest.mark.parametrize("name", sorted(STABILITY))
+def test_solve_matches_the_reference_itself(gpu, golden, name, mode):
+    rec = STABILITY[name]
+    pr, ref = rec["problem"], rec["reference"]
+    rp, ci, v = problems.build(pr["kind"], pr["g"], pr["dim"])
+    os.environ["RAILS_FUSED_LANCZOS"] = MODES[mode]
+    try:
+        o = gpu.solve(rp, ci, v, pr["n_b"], pr["params"], v_cap_cols=400)
+    finally:
+        del os.environ["RAILS_FUSED_LANCZOS"]
+    assert o["ret"] == ref["ret"]
+    ref_rel = np.array(ref["rel"])
+    n = min(o["iterations"], ref["iterations"])
+    rel = np.abs(o["rel"][:n] - ref_rel[:n]) / ref_rel[:n]
+    # how long the reference agrees with itself to 1e-8 (over all its variants)
+    own_first = [f for f in rec["first_iteration_above_1e-8"].values() if f is not None]
+    stable = min(own_first) - 1 if own_first else ref["iterations"]
+    own_spread = rec["history_spread_same_count"]
+    if rec["self_reproducible"]:
+        # the reference reproduces its own iteration count and space size: so must we
+        assert (o["iterations"], o["k"]) == (ref["iterations"], ref["k"])
+        assert np.max(rel[:max(min(stable, 10), 1)]) < 1e-8
+        assert np.max(rel) < 10 * max(own_spread, 1e-8), (np.max(rel), own_spread)
+        if name + "_Xcorner" in golden:
+            Xs = (o["V"][:64] @ o["T"]) @ o["V"][:64].T
+            g = golden[name + "_Xcorner"]
+            assert np.linalg.norm(Xs - g) / np.linalg.norm(g) < 1e-8       # the north-star bar on X
+    else:
+        # the reference's own count moves under rounding-level changes: land inside its range
+        lo, hi = rec["iterations_min_max"]
+        assert lo <= o["iterations"] <= hi, (o["iterations"], lo, hi)
+        if stable >= 1:
+            assert np.max(rel[:stable]) < 1e-8
+        if name + "_Xcorner" in golden:
+            Xs = (o["V"][:64] @ o["T"]) @ o["V"][:64].T
+            g = golden[name + "_Xcorner"]
+            assert np.linalg.norm(Xs - g) / np.linalg.norm(g) < 300 * pr["params"]["Tolerance"]
+
+
+def test_golden_and_stability_references_agree(golden):
+    """The committed goldens (make_golden.py) and the stability study ran the same
+    reference on the same inputs: identical counts and histories."""
+    for name in SOLVES:
+        ref = STABILITY[name]["reference"]
+        assert tuple(golden[name + "_ret"]) == (ref["ret"], ref["iterations"], ref["k"])
+        assert np.allclose(golden[name + "_rel"], ref["rel"], rtol=1e-12, atol=0)
 
 
 @pytest.mark.parametrize("kind,g,dim,n_b,P", [
-    ("laplacian", 128, 2, 1, {"Tolerance": 1e-4, "Expand size": 1, "Lanczos iterations": 10}),
-    ("laplacian", 24, 3, 1, {"Tolerance": 1e-5, "Expand size": 1, "Lanczos iterations": 12,
-                             "Restart size": 60, "Reduced size": 30}),
-    ("convdiff", 20, 3, 1, {"Tolerance": 1e-4, "Expand size": 1, "Lanczos iterations": 10,
-                            "Minimize solution space": 0}),
+    ("laplacian", 96, 2, 2, {"Expand size": 1, "Lanczos iterations": 4}),
+    ("laplacian", 40, 3, 3, {"Expand size": 1, "Lanczos iterations": 5, "Restart size": 24, "Reduced size": 12}),
+    ("convdiff", 32, 3, 1, {"Expand size": 1, "Lanczos iterations": 10}),
 ])
-def test_solve_matches_oracle(gpu, kind, g, dim, n_b, P):
+def test_larger_sparse_solve_matches_the_reference_loop(gpu, kind, g, dim, n_b, P):
+    """Beyond what the dense reference can hold (m = 9 216 .. 64 000): the UNMODIFIED
+    reference loop over its own StlWrapper and a CSR operator
+    (oracle/_ref/librails_ref_csr.so) and the CPU restatement, over a FIXED number of
+    iterations -- solves of a hundred iterations and more are rounding-chaotic for any
+    implementation (the restatement itself needs 170 iterations on one CPU and 165 on
+    another for the first problem), so an unbounded comparison proves nothing."""
     rp, ci, v = problems.build(kind, g, dim)
-    o = harness.oracle_solve(rp, ci, v, n_b, P, v_cap_cols=400)
+    P = dict(P)
+    P.update({"Tolerance": 1e-13, "Maximum iterations": 30, "Minimize solution space": 0})
     d = gpu.solve(rp, ci, v, n_b, P, v_cap_cols=400)
-    if harness.assert_same_solve(d, o, P["Tolerance"], early=min(_first_restart(o["space"], o["iterations"]), 10)):
-        assert np.array_equal(d["space"], o["space"])
-
-
-def test_no_restart_history_and_solution_to_1e8(gpu):
-    """North-star bar where the reference is reproducible: no restart inside
-    the compared window, so nothing amplifies the rounding differences."""
-    rp, ci, v = problems.laplacian(48, 2)
-    # a fixed number of iterations, so that the comparison does not hinge on
-    # which side of the tolerance a marginal iteration falls
-    # (and few enough that rounding differences have not yet been amplified into
-    # a different choice of expansion vector: with 30 iterations the histories
-    # differ by 0.19 at the end, with 12 they agree to 1e-7)
-    P = {"Tolerance": 1e-12, "Maximum iterations": 12, "Expand size": 1, "Lanczos iterations": 10,
-         "Restart iterations": -1, "Minimize solution space": 0}
-    o = harness.oracle_solve(rp, ci, v, 1, P, v_cap_cols=400)
-    assert o["ret"] == -1 and o["iterations"] == 12
-    d = gpu.solve(rp, ci, v, 1, P, v_cap_cols=400)
-    if not harness.assert_same_solve(d, o, P["Tolerance"], early=5, late_tol=1e-6, x_tol=1e-7):
-        pytest.fail("different iteration counts with a fixed iteration cap")
-    rel = np.abs(d["rel"] - o["rel"]) / o["rel"]
-    dx = harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"])
-    print("history diff first 10: %.2e, all %d: %.2e, |dX|/|X| %.2e"
-          % (np.max(rel[:10]), rel.size, np.max(rel), dx))
-    # the residual ESTIMATE is a Ritz value of a 10-step Lanczos run from a
-    # random start: its sensitivity to rounding grows as the residual shrinks
-    # (measured on B200: 3e-15 at iteration 1, 1.3e-8 at 6, 4e-7 at 36); the
-    # solution itself is not affected.  Measured |dX|/|X|: 0.9e-8 operation by
-    # operation, 2.1e-8 with the fused kernels; the reference differs from
-    # itself by 1.3e-8 between 1 and 8 BLAS threads.
-    assert np.max(rel[:10]) < 1e-7
+    arms = {"restatement": harness.oracle_solve(rp, ci, v, n_b, P, v_cap_cols=400)}
+    if harness.ref_csr() is not None:
+        arms["reference loop"] = harness.ref_csr_solve(rp, ci, v, n_b, P, v_cap_cols=400)
+    for label, o in arms.items():
+        assert (d["ret"], d["iterations"], d["k"]) == (o["ret"], o["iterations"], o["k"]) == (-1, 30, o["k"]), label
+        rel = np.abs(d["rel"] - o["rel"]) / o["rel"]
+        # while 2k + n < L the recurrence runs past a breakdown and its estimate is
+        # rounding noise; from there on the three implementations must agree
+        settled = int(np.ceil((P["Lanczos iterations"] - n_b) / 2.0)) + 1
+        assert np.max(rel[:3]) < 1e-8, (label, rel[:3])
+        assert np.max(rel[settled:]) < 1e-6, (label, np.max(rel[settled:]))
+        assert harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"]) < 1e-7, label
 
 
 @pytest.mark.parametrize("kind,g,dim,n_b,P", [

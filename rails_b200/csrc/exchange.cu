@@ -51,10 +51,11 @@ __global__ void __launch_bounds__(FX_THREADS)
 finish_exchange_kernel(const double *partial, int nblocks, int n, double *out, Mailbox mb,
                        unsigned long long seq, volatile int *error, long long timeout_cycles,
                        const double *__restrict__ T, int k,
-                       double *__restrict__ coef, double *norm_out, const double *scale_sq)
+                       double *__restrict__ coef, double *norm_out, const double *scale_sq,
+                       double *alpha_out)
 {
     __shared__ double sm[FX_THREADS];
-    extern __shared__ double res[];          // n doubles: the finished result
+    extern __shared__ double res[];          // n doubles: the finished result (+ n: coef, with alpha_out)
     const int t = threadIdx.x;
 
     // ---- 1. partials -> local sums.  Fixed order: `groups` (a power of two)
@@ -180,6 +181,7 @@ finish_exchange_kernel(const double *partial, int nblocks, int n, double *out, M
     // ---- 4. coef = [T g_1 ; T g_0 ; g_rest]   (src/LyapunovSolver.hpp:395,401)
     if (coef)
     {
+        double *cf = res + n + (norm_out ? 1 : 0);       // second half of the dynamic block
         const int warp = t >> 5, lane = t & 31;
         for (int row = warp; row < 2 * k; row += FX_THREADS / 32)
         {
@@ -190,11 +192,53 @@ finish_exchange_kernel(const double *partial, int nblocks, int n, double *out, M
                 s = fma(T[j + (size_t)l * k], gv[l], s);
             for (int o = 16; o > 0; o >>= 1)
                 s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0) coef[row] = s;
+            if (lane == 0)
+            {
+                coef[row] = s;
+                if (alpha_out) cf[row] = s;
+            }
         }
         for (int i = 2 * k + t; i < n; i += FX_THREADS)
+        {
             coef[i] = res[i];
+            if (alpha_out) cf[i] = res[i];
+        }
+        // ---- 5. alpha = q'R q = sum_b (X_b'q) . coef_b = g . coef (:406: `next.dot(q)`
+        // with next = sum_b X_b coef_b), from what this kernel already holds: the
+        // step needs no second reduction over the rows and no second exchange
+        if (alpha_out)
+        {
+            __syncthreads();
+            double s = 0.0;
+            for (int i = t; i < n; i += FX_THREADS)
+                s = fma(res[i], cf[i], s);
+            sm[t] = s;
+            __syncthreads();
+            for (int h = FX_THREADS / 2; h > 0; h >>= 1)
+            {
+                if (t < h) sm[t] += sm[t + h];
+                __syncthreads();
+            }
+            if (t == 0) *alpha_out = sm[0];
+        }
     }
+}
+
+__global__ void __launch_bounds__(256)
+alpha_plain_kernel(const double *__restrict__ g, const double *__restrict__ coef, int n, double *alpha_out)
+{
+    __shared__ double red[256];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256)
+        s = fma(g[i], coef[i], s);
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int h = 128; h > 0; h >>= 1)
+    {
+        if (threadIdx.x < h) red[threadIdx.x] += red[threadIdx.x + h];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *alpha_out = red[0];
 }
 
 // NCCL route (no peer mailboxes, or more than MB_MAXN values): plain second stage
@@ -259,7 +303,8 @@ namespace rails
 {
 
 int finish_reduction(const double *partial, int nblocks, int n, double *out, bool over_ranks,
-                     const double *T, int k, double *coef, double *norm_out, const double *scale_sq)
+                     const double *T, int k, double *coef, double *norm_out, const double *scale_sq,
+                     double *alpha_out)
 {
     Context &c = ctx();
     if (n <= 0) return RAILS_OK;
@@ -274,11 +319,11 @@ int finish_reduction(const double *partial, int nblocks, int n, double *out, boo
         if (configured_device != c.device)
         {
             RAILS_CUDA_TRY(cudaFuncSetAttribute(finish_exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                MB_MAXN * (int)sizeof(double)));
+                                                2 * MB_MAXN * (int)sizeof(double)));
             configured_device = c.device;
         }
-        RAILS_LAUNCH(finish_exchange_kernel, 1, FX_THREADS, (size_t)n * sizeof(double), partial, nblocks, n, out,
-                     mb, seq, c.d_mb_error, c.mb_timeout_cycles, T, k, coef, norm_out, scale_sq);
+        RAILS_LAUNCH(finish_exchange_kernel, 1, FX_THREADS, (size_t)(alpha_out ? 2 * n : n) * sizeof(double), partial, nblocks, n, out,
+                     mb, seq, c.d_mb_error, c.mb_timeout_cycles, T, k, coef, norm_out, scale_sq, alpha_out);
         RAILS_CHECK_LAUNCH();
         return RAILS_OK;
     }
@@ -300,15 +345,25 @@ int finish_reduction(const double *partial, int nblocks, int n, double *out, boo
         const int warps = 2 * k + (n - 2 * k + 31) / 32;
         RAILS_LAUNCH(coef_plain_kernel, (warps * 32 + 255) / 256, 256, 0, T, k, n, out, coef);
         RAILS_CHECK_LAUNCH();
+        if (alpha_out)
+        {
+            RAILS_LAUNCH(alpha_plain_kernel, 1, 256, 0, out, coef, n, alpha_out);
+            RAILS_CHECK_LAUNCH();
+        }
     }
     return RAILS_OK;
 }
 
-int lanczos_coef(const double *T, int k, int n, const double *g, double *coef)
+int lanczos_coef(const double *T, int k, int n, const double *g, double *coef, double *alpha_out)
 {
     const int warps = 2 * k + (n - 2 * k + 31) / 32;
     RAILS_LAUNCH(coef_plain_kernel, (warps * 32 + 255) / 256, 256, 0, T, k, n, g, coef);
     RAILS_CHECK_LAUNCH();
+    if (alpha_out)
+    {
+        RAILS_LAUNCH(alpha_plain_kernel, 1, 256, 0, g, coef, n, alpha_out);
+        RAILS_CHECK_LAUNCH();
+    }
     return RAILS_OK;
 }
 

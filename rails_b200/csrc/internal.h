@@ -159,11 +159,13 @@ int copy_d2h(void *dst, const void *src, size_t bytes);
 // the n values is a squared norm: it is stored to *norm_out and the other n - 1
 // values are multiplied by 1 / sqrt(|it|) before they are stored / used for coef;
 // with scale_sq != NULL every value is multiplied by 1 / sqrt(|*scale_sq|).
+// With coef and alpha_out != NULL, *alpha_out = out . coef (= q'Rq of the Lanczos step).
 int finish_reduction(const double *partial, int nblocks, int n, double *out, bool over_ranks,
                      const double *T = nullptr, int k = 0, double *coef = nullptr,
-                     double *norm_out = nullptr, const double *scale_sq = nullptr);
+                     double *norm_out = nullptr, const double *scale_sq = nullptr,
+                     double *alpha_out = nullptr);
 // coef = [T g[k:2k) ; T g[0:k) ; g[2k:n)] on the device (T compact k x k)
-int lanczos_coef(const double *T, int k, int n, const double *g, double *coef);
+int lanczos_coef(const double *T, int k, int n, const double *g, double *coef, double *alpha_out = nullptr);
 // After a stream synchronisation that returned reduction results to the host:
 // non-zero (flag cleared, error count bumped so that BackendHealth stops the solve)
 // when a peer did not answer an exchange in time -- the values just read are NaN.

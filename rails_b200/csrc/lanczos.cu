@@ -866,14 +866,26 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
         //   B_i: raw_{i+1} = sum_b X_b coef_b,  raw_{i+1}' w_i -> exchange -> alpha_i = ./|w_i|
         // instead of three (dot, gemv, update) with three.  The update of the
         // last step only feeds H(L, L-1), which the caller drops: it is skipped.
+        // alpha_i = q_i' R q_i: by default from the projections the first finish already
+        // holds, alpha = g . coef (= sum_b (X_b'q) . coef_b, the same number as
+        // raw_{i+1}' q_i in exact arithmetic) -- ONE exchange and three launches per
+        // step.  RAILS_LANCZOS_ALPHA=dot computes it as the reference does (:406), as a
+        // second reduction over the rows inside kernel B with its own exchange.
+        static int alpha_from_dot = -1;
+        if (alpha_from_dot < 0)
+        {
+            const char *e = getenv("RAILS_LANCZOS_ALPHA");
+            alpha_from_dot = (e && strcmp(e, "dot") == 0) ? 1 : 0;
+        }
         for (int i = 0; i < L; ++i)
         {
             double *col = Q->data + (size_t)(qc0 + i) * Q->ld;
+            double *alpha_here = alpha_from_dot ? (double *)nullptr : a + i;
             if (i == 0 && started)
             {
                 // A_0 and its exchange ran while the host solved the projected
                 // problem (rails_mv_lanczos_begin); only the k x k products remain
-                rc = rails::lanczos_coef(dT, k, total, g, coef);
+                rc = rails::lanczos_coef(dT, k, total, g, coef, alpha_here);
                 if (rc) return rc;
             }
             else
@@ -884,14 +896,19 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
                              (const double *)(a + std::max(i - 1, 0)), (const double *)(b2 + std::max(i - 1, 0)),
                              rows, c.d_partial);
                 RAILS_CHECK_LAUNCH();
-                rc = rails::finish_reduction(c.d_partial, nb_dot, total + 1, g, reduce, dT, k, coef, b2 + i);
+                rc = rails::finish_reduction(c.d_partial, nb_dot, total + 1, g, reduce, dT, k, coef, b2 + i, nullptr,
+                                             alpha_here);
                 if (rc) return rc;
             }
             RAILS_LAUNCH(multi_gemv_kernel, nb_gemv, MG_THREADS, (size_t)std::max(total, 1) * sizeof(double),
-                         S, total, coef, col + Q->ld, col, rows, c.d_partial);
+                         S, total, coef, col + Q->ld, alpha_from_dot ? (const double *)col : (const double *)nullptr,
+                         rows, c.d_partial);
             RAILS_CHECK_LAUNCH();
-            rc = rails::finish_reduction(c.d_partial, nb_gemv, 1, a + i, reduce, nullptr, 0, nullptr, nullptr, b2 + i);
-            if (rc) return rc;
+            if (alpha_from_dot)
+            {
+                rc = rails::finish_reduction(c.d_partial, nb_gemv, 1, a + i, reduce, nullptr, 0, nullptr, nullptr, b2 + i);
+                if (rc) return rc;
+            }
         }
         // columns 0 .. L-2 were normalised on the way; the last one here
         if (rows > 0)

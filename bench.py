@@ -332,6 +332,39 @@ def cpu_sample(rp, ci, v, n_b, params, B, warmup, steps, budget_s, M=None):
             "rel_residual_history": [float(x) for x in o["rel"][:done]]}
 
 
+def ref_loop_sample(rp, ci, v, n_b, params, B, warmup, steps, budget_s):
+    """The UNMODIFIED reference loop (src/LyapunovSolver.hpp) over the reference's own
+    StlWrapper and a CSR/OpenMP operator (oracle/_ref/librails_ref_csr.so), all host
+    threads, on the same operator and B with M = I (the C++ loop never reads M).  The
+    loop cannot be stopped from outside, so a 3-iteration run sizes the sample to the
+    time budget; the rate is taken between the progress lines of the iterations."""
+    import harness
+    if harness.ref_csr() is None:
+        return None
+    P = window_params(params, warmup, steps)
+    P.pop("Use mass matrix", None)
+    P.pop("Skip random draws", None)
+    probe = dict(P)
+    probe["Maximum iterations"] = 3
+    t0 = time.time()
+    harness.ref_csr_solve(rp, ci, v, n_b, probe, B=B, skip_draws=1)
+    per_it = (time.time() - t0) / 3.0
+    # iterations get dearer as the space grows: leave a factor 2
+    n = int(max(4, min(warmup + steps, (budget_s - 3 * per_it) / (2.0 * per_it))))
+    P["Maximum iterations"] = n
+    r = harness.ref_csr_solve(rp, ci, v, n_b, P, B=B, skip_draws=1)
+    sec = r["seconds"]
+    done = len(sec)
+    first = min(warmup, max(done - 2, 0))
+    rate = (done - first) / (sec[-1] - (sec[first - 1] if first > 0 else 0.0))
+    return {"value": rate, "unit": "iterations/s", "cores": os.cpu_count() or 1, "kind": "reference",
+            "what": "unmodified reference loop + reference StlWrapper + CSR/OpenMP operator "
+                    "(oracle/_ref/librails_ref_csr.so), M = I",
+            "sample": "iterations %d..%d of the same solve, full size" % (first + 1, done),
+            "iterations_run": done, "seconds": float(sec[-1]),
+            "rel_residual_history": [float(x) for x in r["rel"][:done]]}
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path.  The
     reference's sparse CPU backend (Epetra) cannot be built here, so this is
@@ -348,19 +381,52 @@ def run_reference(args):
     params["Skip random draws"] = 1
     budget = float(os.environ.get("RAILS_BENCH_REF_SECONDS", "150"))
     t0 = time.time()
-    cb = cpu_sample(rp, ci, v, n_b, params, B, args.warmup, args.steps, budget, M=M)
+    extra = {}
+    if M is None:
+        # M = I: the reference's own loop solves this workload -- it IS the arm
+        cb = ref_loop_sample(rp, ci, v, n_b, params, B, args.warmup, args.steps, budget)
+        if cb is None:
+            cb = cpu_sample(rp, ci, v, n_b, params, B, args.warmup, args.steps, budget, M=M)
+    else:
+        # generalised equation (lumped M): the C++ reference never reads M, so
+        # the arm is the CPU restatement of the MATLAB branch; the reference loop on the
+        # same operator and B with M = I is timed beside it (same kernels per iteration
+        # minus the M products)
+        cb = cpu_sample(rp, ci, v, n_b, params, B, args.warmup, args.steps, 0.6 * budget, M=M)
+        # The reference loop deep-copies full-capacity multivectors on every std::move
+        # (~20x the port's time per iteration), so above ~2 M rows even its
+        # 3-iteration probe exceeds the budget: it is then timed on the same stencil at a
+        # REDUCED grid, stated in the record and never extrapolated.
+        g_side = g
+        while g_side ** dim > 2200000:
+            g_side //= 2
+        if g_side == g:
+            rl = ref_loop_sample(rp, ci, v, n_b, params, B, args.warmup, args.steps, 0.4 * budget)
+        else:
+            rp2, ci2, v2 = problems.build(kind, g_side, dim)
+            rl = ref_loop_sample(rp2, ci2, v2, n_b, params, problems.reference_B(g_side ** dim, n_b),
+                                 args.warmup, args.steps, 0.4 * budget)
+        if rl is not None:
+            extra["reference_loop_M_is_I"] = {k: rl[k] for k in ("value", "unit", "cores", "kind", "what", "sample")}
+            extra["reference_loop_M_is_I"]["rows"] = g_side ** dim
+            extra["reference_loop_M_is_I"]["grid"] = g_side
+            if g_side != g:
+                extra["reference_loop_M_is_I"]["sample"] = extra["reference_loop_M_is_I"]["sample"].replace(
+                    "full size", "REDUCED size g=%d (m=%d)" % (g_side, g_side ** dim))
     line = {
         "impl": "reference", "metric": "RAILS outer iterations/s", "value": cb["value"],
         "unit": "iterations/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 / cb["value"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(args, kind, g, dim, n_b, params), "params": params,
-                   "window": "iterations W+1..W+K of one solve, convergence test off"},
+                   "window": "iterations W+1..W+K of one solve, convergence test off; ONE window "
+                             "(the b200 arm reports the median of its windows)"},
         "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": cb["value"], "unit": "iterations/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.time() - t0,
     }
+    line.update(extra)
     print(json.dumps(line), flush=True)
 
 

@@ -17,6 +17,7 @@
 // global memory, a second kernel adds the partials in a fixed order; with a
 // communicator the small result is all-reduced over the ranks (NCCL).
 #include "internal.h"
+#include "tma.cuh"
 
 #include <cmath>
 #include <cstring>
@@ -303,6 +304,205 @@ lanczos_dot_kernel(Segs S, int total, double *__restrict__ col, double *prev, co
             s += sacc[w * nout + i];
         out[i] = s;
     }
+}
+
+// ---- one kernel per Lanczos step -----------------------------------------------------
+// With alpha_i available BEFORE the vector of step i+1 is formed (alpha = g . coef in
+// the finish of step i, exchange.cu), everything between two reductions is row-local:
+//     raw_{i+1}[r] = sum_b X_b[r, :] coef_b                       (kernel B of the chain)
+//     q_i[r]       = w_i[r] / |w_i|                                (written back in place)
+//     w_{i+1}[r]   = raw_{i+1}[r] - rnd(alpha_i q_i[r]) - rnd(|w_i| q_{i-1}[r])   (:411-413)
+//     partial g   += X_b[r, :]' w_{i+1}[r],  |w_{i+1}|^2           (kernel A of step i+1)
+// so a row tile of [V|MV, AV, B] is brought from HBM ONCE per step instead of twice:
+// 8 m (2k + n) + 32 m bytes per step against 16 m (2k + n) + 56 m.  A CTA per SM walks
+// the tiles of TR rows; one thread moves the NEXT tile into the other shared-memory
+// stage with one 1-D bulk copy per column (cp.async.bulk + mbarrier: the TMA engine,
+// no registers involved) while the CTA works on the current one: phase 1, a thread per
+// row, the fma chain over all columns in block order (the arithmetic of
+// multi_gemv_kernel) and the update (the arithmetic of md_tile<., true>); phase 2, a
+// warp per column, the inner product with the new vector out of the same staged tile.
+// Column j is always handled by warp j mod 8 and accumulated in its own slot: no
+// atomics, a summation order fixed by (TR, grid) alone.
+constexpr int LS_THREADS = 512;
+constexpr int LS_WARPS = LS_THREADS / 32;
+constexpr int LS_STAGES = 2;
+constexpr size_t LS_SMEM_BUDGET = 216 * 1024;      // of the 227 KB a CTA may have
+constexpr int LS_MAX_CPW = 13;                     // columns per warp: up to 16 * 13 - 1 = 207 block columns
+
+inline size_t ls_smem_bytes(int total, int tr)
+{
+    // stages [total + 2][tr] | coef[total] | wnew[tr] | partial sums of the warps' lanes: none (registers)
+    return ((size_t)LS_STAGES * (total + 2) * tr + (size_t)total + tr) * sizeof(double);
+}
+// rows per tile for `total` block columns (+ w_i + q_{i-1} staged with them); 0: does not fit
+inline int ls_tile_rows(int total)
+{
+    if ((total + 1 + LS_WARPS - 1) / LS_WARPS > LS_MAX_CPW)
+        return 0;
+    static int forced = -1;                      // RAILS_LS_TILE_ROWS: experiments
+    if (forced < 0)
+    {
+        const char *e = getenv("RAILS_LS_TILE_ROWS");
+        forced = e ? atoi(e) : 0;
+    }
+    if (forced > 0)
+        return ls_smem_bytes(total, forced) <= LS_SMEM_BUDGET ? forced : 0;
+    // tiles below 256 rows mean bulk copies below 2 KB, and the copy engine needs ~60 ns
+    // per request whatever its size (measured: time ~ 1 / tile rows below that): the
+    // two-kernel step is faster there
+    for (int tr = 512; tr >= 256; tr -= 128)
+        if (ls_smem_bytes(total, tr) <= LS_SMEM_BUDGET)
+            return tr;
+    return 0;
+}
+
+// CPW: columns (of the total + 1: the blocks' columns and the new vector itself) a warp owns
+template<int CPW>
+__global__ void __launch_bounds__(LS_THREADS, 1)
+lanczos_step_kernel(Segs S, int total, const double *__restrict__ coef, double *__restrict__ wi,
+                    const double *__restrict__ qprev, double *__restrict__ wnext,
+                    const double *__restrict__ alpha_dev, const double *__restrict__ wsq_dev,
+                    long long rows, int TR, double *__restrict__ partial)
+{
+    using namespace rails::tma;
+    extern __shared__ __align__(128) double ls_smem[];
+    __shared__ unsigned long long full[LS_STAGES];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ncol = total + (qprev ? 2 : 1);          // staged columns: blocks, w_i, q_{i-1}
+    const size_t stage_doubles = (size_t)(total + 2) * TR;
+    double *cs = ls_smem + LS_STAGES * stage_doubles;  // coefficients
+    double *wnew = cs + total;                         // the new vector of this tile
+
+    for (int i = tid; i < total; i += LS_THREADS) cs[i] = coef[i];
+    if (tid == 0)
+    {
+        for (int s = 0; s < LS_STAGES; ++s) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const double nrm = sqrt(fabs(*wsq_dev));
+    const double alpha = *alpha_dev, sc = 1.0 / nrm, beta = nrm;
+    const long long ntiles = (rows + TR - 1) / TR;
+
+    // warp 0 moves a tile: lane 0 announces the byte count, then the lanes issue one
+    // bulk copy per staged column (column c of the concatenated blocks, w_i, q_{i-1})
+    auto issue = [&](long long tile, int s) {
+        const long long r0 = tile * TR;
+        const int nr = (int)min((long long)TR, rows - r0);
+        const unsigned bytes = (unsigned)(((nr + 1) & ~1) * sizeof(double));   // 16-byte granules
+        double *dst = ls_smem + s * stage_doubles;
+        if (lane == 0)
+            mbar_expect_tx(&full[s], bytes * (unsigned)ncol);
+        __syncwarp();
+        for (int j = lane; j < ncol; j += 32)
+        {
+            const double *src;
+            if (j < total)
+            {
+                int b = 0, c = j;
+                while (c >= S.n[b]) { c -= S.n[b]; ++b; }
+                src = S.p[b] + (size_t)c * S.ld[b];
+            }
+            else
+                src = j == total ? wi : qprev;
+            bulk_g2s(dst + (size_t)j * TR, src + r0, bytes, &full[s]);
+        }
+    };
+
+    // this lane's share of the inner products, kept in registers over ALL tiles of the
+    // CTA: warp w owns columns w, w + 16, ...
+    double acc[CPW];
+#pragma unroll
+    for (int c = 0; c < CPW; ++c) acc[c] = 0.0;
+
+    long long tile = blockIdx.x;
+    if (warp == 0 && tile < ntiles)
+        issue(tile, 0);
+    for (int it = 0; tile < ntiles; tile += gridDim.x, ++it)
+    {
+        const int s = it & (LS_STAGES - 1);
+        if (warp == 0 && tile + (long long)gridDim.x < ntiles)
+            issue(tile + gridDim.x, s ^ 1);
+        const long long r0 = tile * TR;
+        const int nr = (int)min((long long)TR, rows - r0);
+        const double *X = ls_smem + s * stage_doubles;
+        mbar_wait(&full[s], (unsigned)(it / LS_STAGES) & 1u);
+
+        // phase 1: a thread per row -- the fma chain over all columns in block order,
+        // then the update with separately rounded products
+        if (tid < nr)
+        {
+            const int r = tid;
+            double a = 0.0;
+#pragma unroll 8
+            for (int j = 0; j < total; ++j)
+                a = fma(X[(size_t)j * TR + r], cs[j], a);
+            const double q = __dmul_rn(X[(size_t)total * TR + r], sc);
+            double x = __dadd_rn(a, -__dmul_rn(alpha, q));
+            if (qprev)
+                x = __dadd_rn(x, -__dmul_rn(beta, X[(size_t)(total + 1) * TR + r]));
+            wi[r0 + r] = q;
+            wnext[r0 + r] = x;
+            wnew[r] = x;
+        }
+        __syncthreads();
+        // phase 2: warp w, columns w + 16 c (column `total` = the new vector itself)
+        for (int r = lane; r < nr; r += 32)
+        {
+            const double w = wnew[r];
+#pragma unroll
+            for (int c = 0; c < CPW; ++c)
+            {
+                const int j = warp + c * LS_WARPS;
+                if (j < total)
+                    acc[c] = fma(X[(size_t)j * TR + r], w, acc[c]);
+                else if (j == total)
+                    acc[c] = fma(w, w, acc[c]);
+            }
+        }
+        __syncthreads();        // stage s and wnew are free again
+    }
+    // lanes -> warp sums, once per kernel
+#pragma unroll
+    for (int c = 0; c < CPW; ++c)
+    {
+        double p = acc[c];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+            p += __shfl_xor_sync(0xffffffffu, p, o);
+        const int j = warp + c * LS_WARPS;
+        if (lane == 0 && j <= total)
+            partial[(size_t)blockIdx.x * (total + 1) + j] = p;
+    }
+}
+
+// launches the instance whose CPW covers `total` + 1 columns
+int launch_lanczos_step(int grid, size_t smem, Segs const &S, int total, const double *coef, double *wi,
+                        const double *qprev, double *wnext, const double *alpha_dev, const double *wsq_dev,
+                        long long rows, int TR, double *partial)
+{
+    const int cpw = (total + 1 + LS_WARPS - 1) / LS_WARPS;
+    static int configured_device = -1;
+    if (configured_device != ctx().device)
+    {
+        const int bytes = (int)(LS_SMEM_BUDGET);
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<LS_MAX_CPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        configured_device = ctx().device;
+    }
+#define RAILS_LS_LAUNCH(N)                                                                          \
+    RAILS_LAUNCH(lanczos_step_kernel<N>, grid, LS_THREADS, smem, S, total, coef, wi, qprev, wnext,  \
+                 alpha_dev, wsq_dev, rows, TR, partial)
+    if (cpw <= 2) RAILS_LS_LAUNCH(2);
+    else if (cpw <= 4) RAILS_LS_LAUNCH(4);
+    else if (cpw <= 7) RAILS_LS_LAUNCH(7);
+    else RAILS_LS_LAUNCH(LS_MAX_CPW);
+#undef RAILS_LS_LAUNCH
+    RAILS_CHECK_LAUNCH();
+    return RAILS_OK;
 }
 
 // q = w / |w| for the last column of the recurrence
@@ -877,6 +1077,51 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
             const char *e = getenv("RAILS_LANCZOS_ALPHA");
             alpha_from_dot = (e && strcmp(e, "dot") == 0) ? 1 : 0;
         }
+        // One kernel per step (lanczos_step_kernel) when the staged tile fits shared
+        // memory: 2k + n <= 207 columns.  RAILS_LANCZOS_ONE_KERNEL=0 keeps the
+        // two-kernel step.
+        static int one_kernel = -1;
+        if (one_kernel < 0)
+        {
+            const char *e = getenv("RAILS_LANCZOS_ONE_KERNEL");
+            one_kernel = (e && e[0] == '0') ? 0 : 1;
+        }
+        const int tile_rows = ls_tile_rows(total);
+        if (one_kernel && !alpha_from_dot && tile_rows > 0)
+        {
+            const long long tiles = (rows + tile_rows - 1) / tile_rows;
+            const int nb_step = (int)std::max<long long>(1, std::min<long long>(tiles, c.sm_count));
+            rc = rails::ensure_partial(std::max<size_t>((size_t)nb_dot * (total + 1), (size_t)nb_step * (total + 1)));
+            if (rc) return rc;
+            double *col0 = Q->data + (size_t)qc0 * Q->ld;
+            if (started)
+            {
+                rc = rails::lanczos_coef(dT, k, total, g, coef, a);
+                if (rc) return rc;
+            }
+            else
+            {
+                RAILS_LAUNCH(lanczos_dot_kernel, nb_dot, MD_THREADS, (size_t)(total + 1) * MD_WARPS * sizeof(double),
+                             S, total, col0, (double *)nullptr, (const double *)nullptr, (const double *)a,
+                             (const double *)b2, rows, c.d_partial);
+                RAILS_CHECK_LAUNCH();
+                rc = rails::finish_reduction(c.d_partial, nb_dot, total + 1, g, reduce, dT, k, coef, b2, nullptr, a);
+                if (rc) return rc;
+            }
+            for (int i = 0; i + 1 < L; ++i)
+            {
+                double *col = col0 + (size_t)i * Q->ld;
+                rc = launch_lanczos_step(nb_step, ls_smem_bytes(total, tile_rows), S, total, (const double *)coef, col,
+                                         i > 0 ? (const double *)(col - Q->ld) : (const double *)nullptr,
+                                         col + Q->ld, (const double *)(a + i), (const double *)(b2 + i), rows,
+                                         tile_rows, c.d_partial);
+                if (rc) return rc;
+                rc = rails::finish_reduction(c.d_partial, nb_step, total + 1, g, reduce, dT, k, coef, b2 + i + 1,
+                                             nullptr, a + i + 1);
+                if (rc) return rc;
+            }
+        }
+        else
         for (int i = 0; i < L; ++i)
         {
             double *col = Q->data + (size_t)(qc0 + i) * Q->ld;

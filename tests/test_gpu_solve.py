@@ -112,7 +112,10 @@ def test_larger_sparse_solve_matches_the_reference_loop(gpu, kind, g, dim, n_b, 
         # rounding noise; from there on the three implementations must agree
         settled = int(np.ceil((P["Lanczos iterations"] - n_b) / 2.0)) + 1
         assert np.max(rel[:3]) < 1e-8, (label, rel[:3])
-        assert np.max(rel[settled:]) < 1e-6, (label, np.max(rel[settled:]))
+        # after the restart at iteration 20 the reference differs from ITSELF by 8e-7 ..
+        # 7e-6 on the comparable cases of ref_self_stability.json (lap2d_g32_n2_L4,
+        # lap3d_g20_n2_L5); measured here: <= 1.8e-6
+        assert np.max(rel[settled:]) < 1e-5, (label, np.max(rel[settled:]))
         # X of an UNCONVERGED 30-iteration iterate (measured on B200: 1e-9 .. 2.5e-7)
         assert harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"]) < 1e-6, label
 

@@ -19,6 +19,8 @@
 #include "internal.h"
 #include "tma.cuh"
 
+#include <cuda.h>
+
 #include <cmath>
 #include <cstring>
 
@@ -323,184 +325,382 @@ lanczos_dot_kernel(Segs S, int total, double *__restrict__ col, double *prev, co
 // warp per column, the inner product with the new vector out of the same staged tile.
 // Column j is always handled by warp j mod 8 and accumulated in its own slot: no
 // atomics, a summation order fixed by (TR, grid) alone.
-constexpr int LS_THREADS = 512;
-constexpr int LS_WARPS = LS_THREADS / 32;
-constexpr int LS_STAGES = 2;
+constexpr int LS_MAX_WARPS = 16;                   // consumer warps (32 rows of a tile each)
+constexpr int LS_MAX_STAGES = 6;
 constexpr size_t LS_SMEM_BUDGET = 216 * 1024;      // of the 227 KB a CTA may have
-constexpr int LS_MAX_CPW = 13;                     // columns per warp: up to 16 * 13 - 1 = 207 block columns
+constexpr int LS_ACC_COLS = 24;                    // accumulator columns of a warp (96 registers with 17 warps)
+constexpr int LS_WIDE_COLS = 50;                   // accumulator columns of a warp with 9 warps (168 registers)
+constexpr int LS_MAX_GROUPS = 4;                   // column groups (warps sharing 32 rows)
+constexpr int LS_MAX_COLS = LS_MAX_GROUPS * LS_ACC_COLS;      // block columns (2k + n) covered
+constexpr int LS_BOX_ROWS = 128;                   // rows of a TMA box (1 KB per column)
+constexpr int LS_BOX_COLS = 8;                     // columns of a TMA box: 8 KB per request
 
-inline size_t ls_smem_bytes(int total, int tr)
+// The tile in shared memory: for each block, ceil(n_b / bc_b) boxes of [bc_b][128]
+// doubles (bc_b = min(n_b, 8) columns: a block is padded to whole boxes), then one box
+// of two columns [q_{i-1}, w_i] of the Lanczos basis; a tile of TR rows is TR / 128 such
+// slabs.
+struct StepLayout
 {
-    // stages [total + 2][tr] | coef[total] | wnew[tr] | partial sums of the warps' lanes: none (registers)
-    return ((size_t)LS_STAGES * (total + 2) * tr + (size_t)total + tr) * sizeof(double);
+    int nseg;
+    int n[MAX_SEGS];        // columns of block b
+    int bc[MAX_SEGS];       // box columns of block b
+    int off[MAX_SEGS];      // first shared-memory column of block b
+    int total;              // sum of n
+    int padded;             // shared-memory columns of all blocks
+};
+struct StepMaps
+{
+    CUtensorMap m[MAX_SEGS + 1];    // the blocks, then the Lanczos basis Q
+};
+
+inline StepLayout ls_layout(const int *n, int nseg)
+{
+    StepLayout L;
+    L.nseg = nseg;
+    L.total = L.padded = 0;
+    for (int b = 0; b < MAX_SEGS; ++b)
+    {
+        L.n[b] = b < nseg ? n[b] : 0;
+        // box columns: 8 (padding costs shared memory only: columns past the block's
+        // end are zero-filled without traffic); narrower boxes that pad less only for
+        // blocks too wide to fit otherwise (more, smaller requests: 0.76 -> 0.89 ms at
+        // 15 columns when tried everywhere)
+        L.bc[b] = std::max(1, std::min(L.n[b], LS_BOX_COLS));
+        for (int bc = LS_BOX_COLS; bc >= 4 && L.n[b] > 40; --bc)
+            if ((L.n[b] + bc - 1) / bc * bc < (L.n[b] + L.bc[b] - 1) / L.bc[b] * L.bc[b])
+                L.bc[b] = bc;
+        L.off[b] = L.padded;
+        L.total += L.n[b];
+        L.padded += (L.n[b] + L.bc[b] - 1) / L.bc[b] * L.bc[b];
+    }
+    return L;
 }
-// rows per tile for `total` block columns (+ w_i + q_{i-1} staged with them); 0: does not fit
-inline int ls_tile_rows(int total)
+constexpr int LS_WSUM_DOUBLES = 8 * (LS_WIDE_COLS + 1);       // >= 16 * (LS_ACC_COLS + 1): per-warp sums
+
+inline int ls_groups(int total);
+
+inline size_t ls_smem_bytes(StepLayout const &L, int tr, int stages)
 {
-    if ((total + 1 + LS_WARPS - 1) / LS_WARPS > LS_MAX_CPW)
-        return 0;
-    static int forced = -1;                      // RAILS_LS_TILE_ROWS: experiments
-    if (forced < 0)
+    // stages [padded + 2][tr] | coef[total, even] | per-warp sums | partial chain sums
+    // [2][groups][tr] (several column groups only) | tables (ints)
+    const int groups = ls_groups(L.total);
+    return ((size_t)stages * (L.padded + 2) * tr + (size_t)((L.total + 1) & ~1) + (size_t)LS_WSUM_DOUBLES +
+            (groups > 1 ? (size_t)2 * groups * tr : 0)) * sizeof(double) +
+           (size_t)(L.total + 64 * 3 + 2) * sizeof(int) + 128;
+}
+
+// Column groups of a row group's warps: one warp covers up to 50 columns with 8
+// consumer warps per CTA (168 registers), beyond that 24 columns per warp with 16.
+inline int ls_groups(int total)
+{
+    static const int forced = getenv("RAILS_LS_GROUPS") ? atoi(getenv("RAILS_LS_GROUPS")) : 0;
+    if (forced > 0 && forced <= LS_MAX_GROUPS && forced * LS_ACC_COLS >= total)
+        return forced;
+    return total <= LS_WIDE_COLS ? 1 : (total + LS_ACC_COLS - 1) / LS_ACC_COLS;
+}
+// Tile height and pipeline depth: candidates in order of preference (measured,
+// profiles/r02_lanczos_step.md); the first that fits shared memory wins.  tr = 0: not
+// applicable (more than LS_MAX_COLS columns, or no room).
+inline void ls_shape(StepLayout const &L, int *tr_out, int *stages_out)
+{
+    *tr_out = 0;
+    *stages_out = 0;
+    if (L.total > LS_MAX_COLS || L.total < 1)
+        return;
+    static int forced_tr = -1, forced_st = -1;   // RAILS_LS_TILE_ROWS / RAILS_LS_STAGES: experiments
+    if (forced_tr < 0)
     {
         const char *e = getenv("RAILS_LS_TILE_ROWS");
-        forced = e ? atoi(e) : 0;
+        forced_tr = e ? atoi(e) : 0;
+        e = getenv("RAILS_LS_STAGES");
+        forced_st = e ? atoi(e) : 0;
     }
-    if (forced > 0)
-        return ls_smem_bytes(total, forced) <= LS_SMEM_BUDGET ? forced : 0;
-    // tiles below 256 rows mean bulk copies below 2 KB, and the copy engine needs ~60 ns
-    // per request whatever its size (measured: time ~ 1 / tile rows below that): the
-    // two-kernel step is faster there
-    for (int tr = 512; tr >= 256; tr -= 128)
-        if (ls_smem_bytes(total, tr) <= LS_SMEM_BUDGET)
-            return tr;
-    return 0;
+    static const int cand[][2] = {{512, 3}, {512, 2}, {384, 3}, {384, 2}, {256, 3}, {256, 2}, {128, 4}, {128, 3}, {128, 2}};
+    for (auto const &cd : cand)
+    {
+        const int tr = forced_tr > 0 ? forced_tr : cd[0], st = forced_st > 0 ? forced_st : cd[1];
+        // column groups x row groups <= 16 consumer warps (8 for the wide instances)
+        const int groups = ls_groups(L.total);
+        const int max_rows = groups == 1 ? (L.total <= LS_ACC_COLS ? 512 : 256) : 32 * (LS_MAX_WARPS / groups);
+        if (tr % LS_BOX_ROWS == 0 && tr <= max_rows && st >= 2 && st <= LS_MAX_STAGES &&
+            ls_smem_bytes(L, tr, st) <= LS_SMEM_BUDGET)
+        {
+            *tr_out = tr;
+            *stages_out = st;
+            return;
+        }
+        if (forced_tr > 0 && forced_st > 0)
+            return;
+    }
 }
 
-// CPW: columns (of the total + 1: the blocks' columns and the new vector itself) a warp owns
-template<int CPW>
-__global__ void __launch_bounds__(LS_THREADS, 1)
-lanczos_step_kernel(Segs S, int total, const double *__restrict__ coef, double *__restrict__ wi,
-                    const double *__restrict__ qprev, double *__restrict__ wnext,
+// Consumer warp w = cg * nrg + rg: row group rg (rows rg * 32 + lane of every tile) and
+// column group cg (block columns [cg * CACC, (cg + 1) * CACC)).  With one column group a
+// warp does everything for its rows.  With several, each warp of a row group sums the
+// chain over ITS columns, the partial sums meet in shared memory behind a named barrier
+// of just those warps, every warp forms the new entries, the warp with cg = 0 writes
+// them, and each accumulates the products of its columns: shared memory is read twice
+// whatever the split.  The last warp is the producer.  Registers: CACC accumulators per
+// lane, 96 for 17 warps (CACC <= 24), 168 for 9 (CACC <= 50).
+template<int CACC, int MAXW, int CU>
+__global__ void __launch_bounds__(32 * (MAXW + 1), 1)
+lanczos_step_kernel(const __grid_constant__ StepMaps maps, StepLayout L, const double *__restrict__ coef,
+                    double *__restrict__ wi, int have_prev, double *__restrict__ wnext, int qcol,
                     const double *__restrict__ alpha_dev, const double *__restrict__ wsq_dev,
-                    long long rows, int TR, double *__restrict__ partial)
+                    long long rows, int TR, int stages, int cgroups, double *__restrict__ partial)
 {
     using namespace rails::tma;
     extern __shared__ __align__(128) double ls_smem[];
-    __shared__ unsigned long long full[LS_STAGES];
+    __shared__ unsigned long long full[LS_MAX_STAGES], empty[LS_MAX_STAGES];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int ncol = total + (qprev ? 2 : 1);          // staged columns: blocks, w_i, q_{i-1}
-    const size_t stage_doubles = (size_t)(total + 2) * TR;
-    double *cs = ls_smem + LS_STAGES * stage_doubles;  // coefficients
-    double *wnew = cs + total;                         // the new vector of this tile
+    const int total = L.total;
+    const int nrg = TR / 32;                            // row groups
+    const int ncons = nrg * cgroups;                    // consumer warps
+    const size_t stage_doubles = (size_t)(L.padded + 2) * TR;
+    double *cs = ls_smem + stages * stage_doubles;      // coefficients
+    double *wsum = cs + ((total + 1) & ~1);             // per-warp sums at the end
+    double *abuf = wsum + LS_WSUM_DOUBLES;              // partial chain sums [2][groups][TR]
+    int *coff = reinterpret_cast<int *>(abuf + (cgroups > 1 ? 2 * cgroups * TR : 0));   // column -> offset in a slab
+    int *req_dst = coff + total + 1;                    // requests of one row slab: slab offset,
+    int *req_map = req_dst + 64;                        //   tensor map,
+    int *req_col = req_map + 64;                        //   first column
 
-    for (int i = tid; i < total; i += LS_THREADS) cs[i] = coef[i];
+    // requests of one slab: per block ceil(n / bc) column boxes, then the basis box
+    int nreq = 1;
+    unsigned slab_bytes = 2u * LS_BOX_ROWS * sizeof(double);
+    for (int b = 0; b < L.nseg; ++b)
+    {
+        const int boxes = (L.n[b] + L.bc[b] - 1) / L.bc[b];
+        nreq += boxes;
+        slab_bytes += (unsigned)(boxes * L.bc[b] * LS_BOX_ROWS * sizeof(double));
+    }
     if (tid == 0)
     {
-        for (int s = 0; s < LS_STAGES; ++s) mbar_init(&full[s], 1);
+        int q = 0, j = 0;
+        for (int b = 0; b < L.nseg; ++b)
+        {
+            for (int c0 = 0; c0 < L.n[b]; c0 += L.bc[b], ++q)
+            {
+                req_dst[q] = (L.off[b] + c0) * LS_BOX_ROWS;
+                req_map[q] = b;
+                req_col[q] = c0;
+            }
+            for (int c = 0; c < L.n[b]; ++c, ++j)
+                coff[j] = (L.off[b] + c) * LS_BOX_ROWS;
+        }
+        req_dst[q] = L.padded * LS_BOX_ROWS;
+        req_map[q] = MAX_SEGS;
+        req_col[q] = qcol - 1;
+        for (int s = 0; s < stages; ++s)
+        {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], ncons);
+        }
         mbar_fence_init();
     }
+    for (int i = tid; i < total; i += blockDim.x) cs[i] = coef[i];
     __syncthreads();
 
+    const long long ntiles = (rows + TR - 1) / TR;
+    const int row_slabs = TR / LS_BOX_ROWS;
+    const size_t slab_doubles = (size_t)(L.padded + 2) * LS_BOX_ROWS;
+
+    if (warp == ncons)
+    {
+        // ---- producer warp: keeps `stages` tiles requested ahead of the consumers
+        int s = 0;
+        unsigned round = 0;
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+        {
+            if (round > 0)
+                mbar_wait(&empty[s], (round - 1) & 1u);          // every consumer warp has left stage s
+            double *dst = ls_smem + s * stage_doubles;
+            if (lane == 0)
+                mbar_expect_tx(&full[s], slab_bytes * (unsigned)row_slabs);
+            __syncwarp();
+            for (int q = lane; q < nreq * row_slabs; q += 32)
+            {
+                const int rb = q / nreq, e = q - rb * nreq;
+                tensor2d_g2s(dst + rb * slab_doubles + req_dst[e], &maps.m[req_map[e]],
+                             (int)(tile * TR + (long long)rb * LS_BOX_ROWS), req_col[e], &full[s]);
+            }
+            if (++s == stages) { s = 0; ++round; }
+        }
+        return;
+    }
+    if (warp > ncons)
+        return;
+
+    // ---- consumer warp
+    const int rg = warp % nrg, cg = warp / nrg;
+    const int c0 = cg * CACC, c1 = min(total, c0 + CACC);             // columns of this warp
     const double nrm = sqrt(fabs(*wsq_dev));
     const double alpha = *alpha_dev, sc = 1.0 / nrm, beta = nrm;
-    const long long ntiles = (rows + TR - 1) / TR;
-
-    // warp 0 moves a tile: lane 0 announces the byte count, then the lanes issue one
-    // bulk copy per staged column (column c of the concatenated blocks, w_i, q_{i-1})
-    auto issue = [&](long long tile, int s) {
-        const long long r0 = tile * TR;
-        const int nr = (int)min((long long)TR, rows - r0);
-        const unsigned bytes = (unsigned)(((nr + 1) & ~1) * sizeof(double));   // 16-byte granules
-        double *dst = ls_smem + s * stage_doubles;
-        if (lane == 0)
-            mbar_expect_tx(&full[s], bytes * (unsigned)ncol);
-        __syncwarp();
-        for (int j = lane; j < ncol; j += 32)
-        {
-            const double *src;
-            if (j < total)
-            {
-                int b = 0, c = j;
-                while (c >= S.n[b]) { c -= S.n[b]; ++b; }
-                src = S.p[b] + (size_t)c * S.ld[b];
-            }
-            else
-                src = j == total ? wi : qprev;
-            bulk_g2s(dst + (size_t)j * TR, src + r0, bytes, &full[s]);
-        }
-    };
-
-    // this lane's share of the inner products, kept in registers over ALL tiles of the
-    // CTA: warp w owns columns w, w + 16, ...
-    double acc[CPW];
+    double acc[CACC + 1];
 #pragma unroll
-    for (int c = 0; c < CPW; ++c) acc[c] = 0.0;
+    for (int j = 0; j <= CACC; ++j) acc[j] = 0.0;
+    const int rt = rg * 32 + lane;                                     // row inside the tile
+    const size_t my = (size_t)(rt / LS_BOX_ROWS) * slab_doubles + (rt % LS_BOX_ROWS);
 
-    long long tile = blockIdx.x;
-    if (warp == 0 && tile < ntiles)
-        issue(tile, 0);
-    for (int it = 0; tile < ntiles; tile += gridDim.x, ++it)
+    int s = 0, par = 0;
+    unsigned round = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
     {
-        const int s = it & (LS_STAGES - 1);
-        if (warp == 0 && tile + (long long)gridDim.x < ntiles)
-            issue(tile + gridDim.x, s ^ 1);
-        const long long r0 = tile * TR;
-        const int nr = (int)min((long long)TR, rows - r0);
-        const double *X = ls_smem + s * stage_doubles;
-        mbar_wait(&full[s], (unsigned)(it / LS_STAGES) & 1u);
-
-        // phase 1: a thread per row -- the fma chain over all columns in block order,
-        // then the update with separately rounded products
-        if (tid < nr)
+        const long long r = tile * TR + rt;
+        const double *X = ls_smem + s * stage_doubles + my;            // column offset o of this row: X[o]
+        mbar_wait(&full[s], round & 1u);
+        // the fma chain in block order (the arithmetic of multi_gemv_kernel), over this
+        // warp's columns
+        // (CU columns at a time: their loads issue ahead of the dependent fmas; as many as
+        // the instance's registers hold without spilling)
+        double a = 0.0;
+        if (CU > 0)
         {
-            const int r = tid;
-            double a = 0.0;
+#pragma unroll 1
+            for (int jb = c0; jb < c1; jb += (CU > 0 ? CU : 1))
+            {
+#pragma unroll
+                for (int j = 0; j < CU; ++j)
+                    if (jb + j < c1)
+                        a = fma(X[coff[jb + j]], cs[jb + j], a);
+            }
+        }
+        else
+        {
 #pragma unroll 8
-            for (int j = 0; j < total; ++j)
-                a = fma(X[(size_t)j * TR + r], cs[j], a);
-            const double q = __dmul_rn(X[(size_t)total * TR + r], sc);
-            double x = __dadd_rn(a, -__dmul_rn(alpha, q));
-            if (qprev)
-                x = __dadd_rn(x, -__dmul_rn(beta, X[(size_t)(total + 1) * TR + r]));
-            wi[r0 + r] = q;
-            wnext[r0 + r] = x;
-            wnew[r] = x;
+            for (int j = c0; j < c1; ++j)
+                a = fma(X[coff[j]], cs[j], a);
         }
-        __syncthreads();
-        // phase 2: warp w, columns w + 16 c (column `total` = the new vector itself)
-        for (int r = lane; r < nr; r += 32)
+        if (cgroups > 1)
         {
-            const double w = wnew[r];
-#pragma unroll
-            for (int c = 0; c < CPW; ++c)
+            // partial sums of the row group's warps, added in group order.  Two buffers:
+            // a warp is at most one barrier ahead of the others of its group.
+            double *ab = abuf + (size_t)par * cgroups * TR;
+            ab[cg * TR + rt] = a;
+            asm volatile("bar.sync %0, %1;" ::"r"(2 + rg), "r"(cgroups * 32) : "memory");
+            a = ab[rt];
+            for (int g = 1; g < cgroups; ++g)
+                a += ab[g * TR + rt];
+            par ^= 1;
+        }
+        // the update with separately rounded products (the arithmetic of md_tile<., true>)
+        const double q = __dmul_rn(X[(size_t)(L.padded + 1) * LS_BOX_ROWS], sc);
+        double x = __dadd_rn(a, -__dmul_rn(alpha, q));
+        if (have_prev)
+            x = __dadd_rn(x, -__dmul_rn(beta, X[(size_t)L.padded * LS_BOX_ROWS]));
+        if (r < rows)
+        {
+            if (cg == 0)
             {
-                const int j = warp + c * LS_WARPS;
-                if (j < total)
-                    acc[c] = fma(X[(size_t)j * TR + r], w, acc[c]);
-                else if (j == total)
-                    acc[c] = fma(w, w, acc[c]);
+                wi[r] = q;
+                wnext[r] = x;
             }
         }
-        __syncthreads();        // stage s and wnew are free again
-    }
-    // lanes -> warp sums, once per kernel
+        else
+            x = 0.0;                                                   // rows past the end stay out of the sums
+        // the projection of the new vector on this warp's columns, from the same staged tile
 #pragma unroll
-    for (int c = 0; c < CPW; ++c)
+        for (int j = 0; j < CACC; ++j)
+            if (c0 + j < c1)
+                acc[j] = fma(X[coff[c0 + j]], x, acc[j]);
+        acc[CACC] = fma(x, x, acc[CACC]);
+        __syncwarp();
+        if (lane == 0)
+            mbar_arrive(&empty[s]);                                    // this warp is done with stage s
+        if (++s == stages) { s = 0; ++round; }
+    }
+    // lanes -> warp sums -> CTA sums, once per kernel, fixed order
+#pragma unroll
+    for (int j = 0; j <= CACC; ++j)
     {
-        double p = acc[c];
+        double p = acc[j];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1)
             p += __shfl_xor_sync(0xffffffffu, p, o);
-        const int j = warp + c * LS_WARPS;
-        if (lane == 0 && j <= total)
-            partial[(size_t)blockIdx.x * (total + 1) + j] = p;
+        if (lane == 0)
+            wsum[warp * (CACC + 1) + j] = p;
+    }
+    // consumers only (the producer has returned): named barrier 1
+    asm volatile("bar.sync 1, %0;" ::"r"(ncons * 32) : "memory");
+    for (int j = tid; j <= total; j += ncons * 32)
+    {
+        // column j lives in column group j / CACC; the squared norm with group 0
+        const int g = j < total ? j / CACC : 0, jj = j < total ? j - g * CACC : CACC;
+        double p = 0.0;
+        for (int w = 0; w < nrg; ++w)
+            p += wsum[(g * nrg + w) * (CACC + 1) + jj];
+        partial[(size_t)blockIdx.x * (total + 1) + j] = p;
     }
 }
 
-// launches the instance whose CPW covers `total` + 1 columns
-int launch_lanczos_step(int grid, size_t smem, Segs const &S, int total, const double *coef, double *wi,
-                        const double *qprev, double *wnext, const double *alpha_dev, const double *wsq_dev,
-                        long long rows, int TR, double *partial)
+// cuTensorMapEncodeTiled through the runtime (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled()
 {
-    const int cpw = (total + 1 + LS_WARPS - 1) / LS_WARPS;
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried)
+    {
+        tried = true;
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
+// column-major block of `cols` columns of `rows` doubles, leading dimension ld: boxes of
+// [box_cols][128 rows]
+bool make_map(CUtensorMap *m, const double *base, long long rows, int cols, long long ld, int box_cols)
+{
+    EncodeTiledFn fn = encode_tiled();
+    if (!fn || cols < 1 || rows < 1) return false;
+    cuuint64_t gdim[2] = {(cuuint64_t)rows, (cuuint64_t)cols};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * sizeof(double)};
+    cuuint32_t box[2] = {(cuuint32_t)LS_BOX_ROWS, (cuuint32_t)box_cols};
+    cuuint32_t estride[2] = {1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double *>(base), gdim, gstride, box, estride,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// launches the instance whose per-warp accumulators cover the columns of one group
+int launch_lanczos_step(int grid, size_t smem, StepMaps const &maps, StepLayout const &L, const double *coef,
+                        double *wi, int have_prev, double *wnext, int qcol, const double *alpha_dev,
+                        const double *wsq_dev, long long rows, int TR, int stages, double *partial)
+{
     static int configured_device = -1;
     if (configured_device != ctx().device)
     {
         const int bytes = (int)(LS_SMEM_BUDGET);
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<LS_MAX_CPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<12, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<24, 16, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<36, 8, 36>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        RAILS_CUDA_TRY(cudaFuncSetAttribute(lanczos_step_kernel<50, 8, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
         configured_device = ctx().device;
     }
-#define RAILS_LS_LAUNCH(N)                                                                          \
-    RAILS_LAUNCH(lanczos_step_kernel<N>, grid, LS_THREADS, smem, S, total, coef, wi, qprev, wnext,  \
-                 alpha_dev, wsq_dev, rows, TR, partial)
-    if (cpw <= 2) RAILS_LS_LAUNCH(2);
-    else if (cpw <= 4) RAILS_LS_LAUNCH(4);
-    else if (cpw <= 7) RAILS_LS_LAUNCH(7);
-    else RAILS_LS_LAUNCH(LS_MAX_CPW);
-#undef RAILS_LS_LAUNCH
+    const int groups = ls_groups(L.total);
+    const int threads = 32 * (TR / 32 * groups + 1);
+#define RAILS_LS_ARGS maps, L, coef, wi, have_prev, wnext, qcol, alpha_dev, wsq_dev, rows, TR, stages, groups, partial
+    if (groups > 1)
+        RAILS_LAUNCH((lanczos_step_kernel<24, 16, 12>), grid, threads, smem, RAILS_LS_ARGS);
+    else if (L.total <= 12)
+        RAILS_LAUNCH((lanczos_step_kernel<12, 16, 12>), grid, threads, smem, RAILS_LS_ARGS);
+    else if (L.total <= 24)
+        RAILS_LAUNCH((lanczos_step_kernel<24, 16, 12>), grid, threads, smem, RAILS_LS_ARGS);
+    else if (L.total <= 36)
+        RAILS_LAUNCH((lanczos_step_kernel<36, 8, 36>), grid, threads, smem, RAILS_LS_ARGS);
+    else
+    {
+        RAILS_LAUNCH((lanczos_step_kernel<50, 8, 0>), grid, threads, smem, RAILS_LS_ARGS);
+    }
+#undef RAILS_LS_ARGS
     RAILS_CHECK_LAUNCH();
     return RAILS_OK;
 }
@@ -1077,17 +1277,26 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
             const char *e = getenv("RAILS_LANCZOS_ALPHA");
             alpha_from_dot = (e && strcmp(e, "dot") == 0) ? 1 : 0;
         }
-        // One kernel per step (lanczos_step_kernel) when the staged tile fits shared
-        // memory: 2k + n <= 207 columns.  RAILS_LANCZOS_ONE_KERNEL=0 keeps the
-        // two-kernel step.
+        // One kernel per step (lanczos_step_kernel) for 2k + n <= 96 columns, when the
+        // driver offers tensor maps.
+        // RAILS_LANCZOS_ONE_KERNEL=0 keeps the two-kernel step.
         static int one_kernel = -1;
         if (one_kernel < 0)
         {
             const char *e = getenv("RAILS_LANCZOS_ONE_KERNEL");
             one_kernel = (e && e[0] == '0') ? 0 : 1;
         }
-        const int tile_rows = ls_tile_rows(total);
-        if (one_kernel && !alpha_from_dot && tile_rows > 0)
+        StepLayout lay = ls_layout(S.n, S.nseg);
+        int tile_rows = 0, stages = 0;
+        if (total > 0)
+            ls_shape(lay, &tile_rows, &stages);
+        StepMaps maps;
+        bool have_maps = one_kernel && !alpha_from_dot && tile_rows > 0 && L > 1;
+        for (int b = 0; have_maps && b < S.nseg; ++b)
+            have_maps = make_map(&maps.m[b], S.p[b], rows, S.n[b], S.ld[b], lay.bc[b]);
+        if (have_maps)
+            have_maps = make_map(&maps.m[MAX_SEGS], Q->data, rows, Q->cols, Q->ld, 2);
+        if (have_maps)
         {
             const long long tiles = (rows + tile_rows - 1) / tile_rows;
             const int nb_step = (int)std::max<long long>(1, std::min<long long>(tiles, c.sm_count));
@@ -1111,10 +1320,9 @@ extern "C" int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc
             for (int i = 0; i + 1 < L; ++i)
             {
                 double *col = col0 + (size_t)i * Q->ld;
-                rc = launch_lanczos_step(nb_step, ls_smem_bytes(total, tile_rows), S, total, (const double *)coef, col,
-                                         i > 0 ? (const double *)(col - Q->ld) : (const double *)nullptr,
-                                         col + Q->ld, (const double *)(a + i), (const double *)(b2 + i), rows,
-                                         tile_rows, c.d_partial);
+                rc = launch_lanczos_step(nb_step, ls_smem_bytes(lay, tile_rows, stages), maps, lay, (const double *)coef, col,
+                                         i > 0 ? 1 : 0, col + Q->ld, qc0 + i, (const double *)(a + i),
+                                         (const double *)(b2 + i), rows, tile_rows, stages, c.d_partial);
                 if (rc) return rc;
                 rc = rails::finish_reduction(c.d_partial, nb_step, total + 1, g, reduce, dT, k, coef, b2 + i + 1,
                                              nullptr, a + i + 1);

@@ -26,6 +26,10 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
 {
     asm volatile(
@@ -47,6 +51,19 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
                      smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+
+// 2-D tiled tensor-map copy: one request moves a whole box (dim 0 = rows, contiguous
+// in memory; dim 1 = columns), rows / columns outside the tensor arrive as zeros and
+// cost no HBM traffic.  `map` is the address of a CUtensorMap in kernel-parameter
+// (__grid_constant__) space; the destination must be 128-byte aligned.
+__device__ __forceinline__ void tensor2d_g2s(void *dst, const void *map, int row0, int col0,
+                                             unsigned long long *bar)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(row0), "r"(col0), "r"(smem_u32(bar))
+        : "memory");
 }
 
 }

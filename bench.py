@@ -78,6 +78,8 @@ def parse_args():
     ap.add_argument("--kernels-only", action="store_true",
                     help="only the per-kernel timings (the command profiled with ncu --set full)")
     ap.add_argument("--kernel-k", type=int, default=64)
+    ap.add_argument("--step-k", type=int, default=0,
+                    help="space size the step kernel is timed at (0: median of the timed window)")
     ap.add_argument("--kernel-reps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=25.0,
                     help="time budget of the bounded CPU sample")
@@ -168,7 +170,7 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
+def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10, step_k=0, step_n=1):
     """Per-kernel device time at the workload's row count (CUDA events on the
     library stream, after warm-up; operands are GBs, far beyond L2).
     Algorithmic bytes follow SURVEY.md §8(d) / DESIGN.md."""
@@ -242,6 +244,49 @@ def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10):
     # + 8m: the squared norm of `prev` is recomputed by this entry point (in the
     # chain it is already on the device)
     rec("lanczos_project", ms, 8.0 * m * (2 * h + 1 + 5), 4)
+    # The dominant kernel of an iteration since round 2: one Lanczos step as ONE kernel
+    # (lanczos_step_kernel: the row tile of [V AV B] staged once in shared memory by TMA;
+    # gemv with coef, three-term update and the next projection out of the staged tile).
+    # Timed alone by events around each of its launches inside rails_mv_lanczos_run
+    # (rails_lanczos_step_timing), at `step_k` columns per block (the median space size
+    # of the timed window).  Algorithmic bytes, each operand read once and each result
+    # written once: 8 m (2k + n) for the blocks, q_{i-1} and w_i read, q_i and w_{i+1}
+    # written = 8 m (2k + n + 4).
+    if step_k:
+        sk, n1, Ls = step_k, step_n, 10
+        Vb, AVb, Bb = api.MultiVector(rows, sk), api.MultiVector(rows, sk), api.MultiVector(rows, n1)
+        Qb = api.MultiVector(rows, Ls + 1)
+        for mv, c, sd in ((Vb, sk, 3), (AVb, sk, 4), (Bb, n1, 5)):
+            api.check(lib.rails_mv_random(mv.h, 0, c, row_offset, ctypes.c_uint(sd)), "random")
+            api.check(lib.rails_mv_scal(mv.h, 0, c, 1.0 / np.sqrt(global_rows)), "scal")
+        Tm = np.asfortranarray(-1e-2 * np.eye(sk))
+        hb = (P * 3)(Vb.h, AVb.h, Bb.h)
+        cb = (ctypes.c_int * 3)(0, 0, 0)
+        nb = (ctypes.c_int * 3)(sk, sk, n1)
+        alb, beb = np.zeros(Ls), np.zeros(Ls)
+        stp = ctypes.c_int(0)
+
+        def chain():
+            api.check(lib.rails_mv_random(Qb.h, 0, 1, row_offset, ctypes.c_uint(9)), "random")
+            api.check(lib.rails_mv_lanczos_run(3, hb, cb, nb, api.dptr(Tm), sk, Qb.h, 0, Ls, api.dptr(alb),
+                                               api.dptr(beb), ctypes.byref(stp)), "lanczos_run")
+
+        for _ in range(3):
+            chain()
+        api.check(lib.rails_lanczos_step_timing(1), "step_timing")
+        for _ in range(max(reps // 2, 3)):
+            chain()
+        tot, nl = ctypes.c_double(0), ctypes.c_int(0)
+        shp = (ctypes.c_int * 5)()
+        api.check(lib.rails_lanczos_step_timing_read(ctypes.byref(tot), ctypes.byref(nl), shp), "step_timing_read")
+        api.check(lib.rails_lanczos_step_timing(0), "step_timing")
+        if nl.value > 0:
+            rec("lanczos_step", tot.value / nl.value, 8.0 * m * (2 * sk + n1 + 4), 1)
+            out["lanczos_step"].update({"block_columns": int(shp[0]), "tile_rows": int(shp[1]), "stages": int(shp[2]),
+                                        "column_groups": int(shp[3]), "ctas": int(shp[4]), "launches_timed": nl.value,
+                                        "space_size": sk, "survey_two_pass_bound_bytes": 16.0 * m * (2 * sk + n1 + 2)})
+        for mv in (Vb, AVb, Bb, Qb):
+            mv.free()
     # The two calls of the path that are bound by FP64 arithmetic rather than by HBM
     # once k, r >~ 50: the restart compression V <- V X (k x r,
     # src/LyapunovSolver.hpp:265-297) and the warm-start projection V'(AV) (k x k,
@@ -461,7 +506,8 @@ def run_b200(args):
     B = problems.reference_B(m, n_b, r0, r1)
     params["Skip random draws"] = 1
     if args.kernels_only:
-        kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps)
+        kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps,
+                               step_k=args.step_k or 15, step_n=n_b)
         if rank == 0:
             print(json.dumps({"kernels": kernels, "rows": rows}), flush=True)
         return
@@ -561,7 +607,11 @@ def run_b200(args):
 
     kernels = None
     if not args.no_kernels:
-        kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps)
+        # the step kernel at the median space size of the timed window
+        sp = [int(x) for x in res["space"][W:W + K]] or [15]
+        step_k = args.step_k or int(np.median(sp))
+        kernels = time_kernels(api, rows, rp, ci, v, m, r0, k=args.kernel_k, reps=args.kernel_reps,
+                               step_k=step_k, step_n=n_b)
     if rank != 0:
         return
 
@@ -575,21 +625,33 @@ def run_b200(args):
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650"
     roofline = None
     if kernels:
-        # the dominant kernel of an outer iteration: first kernel of the fused
-        # residual-Lanczos step, g = [V AV B]' q (about half of all bytes moved)
-        dk = kernels["lanczos_project"]
-        # ncu DRAM bytes of this launch at the N = 1 row count; not a measurement
-        # for the smaller per-rank blocks of N > 1
+        # the dominant kernel of an outer iteration: the one-kernel Lanczos step
+        # (L - 1 launches per iteration; ~80 % of the iteration's device time)
         traffic = None
-        if world == 1 and rows == 16777216 and dk["k"] == 64:
-            try:
-                traffic = _json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("lanczos_dot")
-            except Exception:
-                pass
-        roofline = {"bound": "hbm",
-                    "kernel": "lanczos_dot_kernel (fused Lanczos update + [V AV B]'w, %d columns, "
-                              "m=%d rows; timed through rails_mv_lanczos_project)"
-                              % (2 * (dk["k"] // 2) + 1, rows),
+        tj = {}
+        try:
+            tj = _json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        except Exception:
+            pass
+        if "lanczos_step" in kernels:
+            dk = kernels["lanczos_step"]
+            # ncu DRAM bytes of one launch at the N = 1 row count and this space size;
+            # not a measurement for other shapes or the per-rank blocks of N > 1
+            t = tj.get("lanczos_step", {})
+            if world == 1 and rows == t.get("rows") and dk["space_size"] == t.get("space_size"):
+                traffic = t.get("dram_bytes_per_launch")
+            name = ("lanczos_step_kernel (one Lanczos step in one kernel: TMA-staged row tile of [V AV B], "
+                    "gemv + update + next projection; %d block columns, space size %d, m=%d rows, "
+                    "tile %d rows x %d stages, %d column groups; events around each launch inside "
+                    "rails_mv_lanczos_run)" % (dk["block_columns"], dk["space_size"], rows, dk["tile_rows"],
+                                               dk["stages"], dk["column_groups"]))
+        else:
+            dk = kernels["lanczos_project"]
+            if world == 1 and rows == 16777216 and dk["k"] == 64:
+                traffic = tj.get("lanczos_dot")
+            name = ("lanczos_dot_kernel (fused Lanczos update + [V AV B]'w, %d columns, m=%d rows; timed through "
+                    "rails_mv_lanczos_project)" % (2 * (dk["k"] // 2) + 1, rows))
+        roofline = {"bound": "hbm", "kernel": name,
                     "achieved": dk["gbs"], "peak": peak, "unit": "GB/s", "frac": dk["gbs"] / peak,
                     "traffic": traffic, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": dk["bytes"], "ms_per_launch": dk["ms"]}

@@ -218,6 +218,14 @@ int rails_mv_lanczos_project(int nblk, const rails_mv_t *X, const int *xc0, cons
                              rails_mv_t Q, int col, int prev_col, int prev2_col,
                              double alpha, double *out);
 
+/* Measurement aid (bench.py `roofline`; no reference counterpart): with enable != 0
+ * every launch of the one-kernel Lanczos step inside rails_mv_lanczos_run is bracketed
+ * by CUDA events on the library's stream.  _read synchronises, returns the summed
+ * kernel time in ms, the number of launches and the shape of the last launch
+ * {block columns, tile rows, pipeline stages, column groups, CTAs}, and resets. */
+int rails_lanczos_step_timing(int enable);
+int rails_lanczos_step_timing_read(double *ms_total, int *launches, int *shape5);
+
 /* ---- Gram-Schmidt: column-wise CGS2 of columns [first, last] against all
  *      earlier columns (StlWrapper::orthogonalize :305-321), executed as one
  *      device-side chain with no host round trip. ------------------------ */

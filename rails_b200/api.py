@@ -112,6 +112,8 @@ CUDA_SYMBOLS = [
                                  c_double_p, c_double_p, c_int_p]),
     ("rails_mv_lanczos_begin", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, P, I]),
     ("rails_mv_lanczos_project", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, P, I, I, I, D, c_double_p]),
+    ("rails_lanczos_step_timing", I, [I]),
+    ("rails_lanczos_step_timing_read", I, [c_double_p, c_int_p, c_int_p]),
     ("rails_mv_orthogonalize", I, [P, I, I, I]),
     ("rails_mv_random", I, [P, I, I, LL, ctypes.c_uint]),
     ("rails_csr_create", I, [LL, LL, LL, LL, c_int_p, c_int_p, c_double_p, ctypes.POINTER(P)]),

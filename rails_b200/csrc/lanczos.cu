@@ -670,8 +670,47 @@ bool make_map(CUtensorMap *m, const double *base, long long rows, int cols, long
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Optional timing of the step kernel alone (bench.py's roofline): CUDA events on the
+// launching stream around every launch, read back by rails_lanczos_step_timing_read.
+struct StepTiming
+{
+    bool on = false;
+    std::vector<cudaEvent_t> ev;       // pairs
+    size_t used = 0;
+    int cols = 0, tile_rows = 0, stages = 0, groups = 0, ctas = 0;
+};
+StepTiming g_step_timing;
+
 // launches the instance whose per-warp accumulators cover the columns of one group
+int launch_lanczos_step_untimed(int grid, size_t smem, StepMaps const &maps, StepLayout const &L, const double *coef,
+                                double *wi, int have_prev, double *wnext, int qcol, const double *alpha_dev,
+                                const double *wsq_dev, long long rows, int TR, int stages, double *partial);
+
 int launch_lanczos_step(int grid, size_t smem, StepMaps const &maps, StepLayout const &L, const double *coef,
+                        double *wi, int have_prev, double *wnext, int qcol, const double *alpha_dev,
+                        const double *wsq_dev, long long rows, int TR, int stages, double *partial)
+{
+    StepTiming &t = g_step_timing;
+    if (!t.on)
+        return launch_lanczos_step_untimed(grid, smem, maps, L, coef, wi, have_prev, wnext, qcol, alpha_dev, wsq_dev,
+                                           rows, TR, stages, partial);
+    if (t.used + 2 > t.ev.size())
+        for (int i = 0; i < 2; ++i)
+        {
+            cudaEvent_t e;
+            RAILS_CUDA_TRY(cudaEventCreate(&e));
+            t.ev.push_back(e);
+        }
+    RAILS_CUDA_TRY(cudaEventRecord(t.ev[t.used], ctx().stream));
+    const int rc = launch_lanczos_step_untimed(grid, smem, maps, L, coef, wi, have_prev, wnext, qcol, alpha_dev,
+                                               wsq_dev, rows, TR, stages, partial);
+    RAILS_CUDA_TRY(cudaEventRecord(t.ev[t.used + 1], ctx().stream));
+    t.used += 2;
+    t.cols = L.total; t.tile_rows = TR; t.stages = stages; t.groups = ls_groups(L.total); t.ctas = grid;
+    return rc;
+}
+
+int launch_lanczos_step_untimed(int grid, size_t smem, StepMaps const &maps, StepLayout const &L, const double *coef,
                         double *wi, int have_prev, double *wnext, int qcol, const double *alpha_dev,
                         const double *wsq_dev, long long rows, int TR, int stages, double *partial)
 {
@@ -1433,5 +1472,34 @@ extern "C" int rails_mv_lanczos_begin(int nblk, const rails_mv_t *X, const int *
     c.lz_pending = true;
     c.lz_q = col;
     c.lz_total = total;
+    return RAILS_OK;
+}
+
+// ---- timing of the step kernel alone (see StepTiming) --------------------------------
+extern "C" int rails_lanczos_step_timing(int enable)
+{
+    g_step_timing.on = enable != 0;
+    g_step_timing.used = 0;
+    return RAILS_OK;
+}
+
+extern "C" int rails_lanczos_step_timing_read(double *ms_total, int *launches, int *shape5)
+{
+    StepTiming &t = g_step_timing;
+    RAILS_CUDA_TRY(cudaStreamSynchronize(rails::ctx().stream));
+    double total = 0.0;
+    for (size_t i = 0; i + 1 < t.used; i += 2)
+    {
+        float ms = 0.f;
+        RAILS_CUDA_TRY(cudaEventElapsedTime(&ms, t.ev[i], t.ev[i + 1]));
+        total += ms;
+    }
+    if (ms_total) *ms_total = total;
+    if (launches) *launches = (int)(t.used / 2);
+    if (shape5)
+    {
+        shape5[0] = t.cols; shape5[1] = t.tile_rows; shape5[2] = t.stages; shape5[3] = t.groups; shape5[4] = t.ctas;
+    }
+    t.used = 0;
     return RAILS_OK;
 }

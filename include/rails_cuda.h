@@ -252,12 +252,20 @@ int rails_csr_free(rails_csr_t A);
  * src/Epetra_OperatorWrapper.cpp:87.  local_col[nnz] = column indices
  * renumbered [owned | ghost]; the *nghost ghost rows in ascending global order
  * (ghost_global), as row ids in their owner's numbering (ghost_owner_row), and
- * need_from[nranks] = how many come from each rank.  No CUDA call is made;
- * rails_csr_create uses it and exchanges the lists over NCCL. */
+ * need_from[nranks] = how many come from each rank.  No CUDA call is made: this
+ * is the specification the CPU tests pin (tests/test_partition_gloo.py). */
 int rails_csr_halo_plan(long long rows, long long global_rows, long long row_offset,
                         int nranks, const int *rowptr, const int *colidx,
                         int *local_col, int *nghost, int *ghost_global,
                         int *ghost_owner_row, int *need_from);
+/* The same plan built on the device, as rails_csr_create builds it (ghost columns
+ * marked in a byte map of the global index range, compacted in ascending order,
+ * indices renumbered in place), then exchanged over NCCL there.  Same arguments and
+ * results as rails_csr_halo_plan; host arrays in and out. */
+int rails_csr_halo_plan_device(long long rows, long long global_rows, long long row_offset,
+                               int nranks, const int *rowptr, const int *colidx,
+                               int *local_col, int *nghost, int *ghost_global,
+                               int *ghost_owner_row, int *need_from);
 /* New values on the same sparsity pattern (same order as the arrays given to
  * rails_csr_create): a continuation step or a re-assembled Jacobian keeps the row
  * blocks, the renumbered columns and the halo plan.  The reference replaces the

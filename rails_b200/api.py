@@ -120,6 +120,8 @@ CUDA_SYMBOLS = [
     ("rails_csr_free", I, [P]),
     ("rails_csr_halo_plan", I, [LL, LL, LL, I, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p,
                                 c_int_p]),
+    ("rails_csr_halo_plan_device", I, [LL, LL, LL, I, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p,
+                                c_int_p]),
     ("rails_csr_update_values", I, [P, c_double_p]),
     ("rails_csr_get_value", I, [P, LL, LL, c_double_p]),
     ("rails_csr_set_value", I, [P, LL, LL, D]),

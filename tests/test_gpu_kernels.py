@@ -408,3 +408,73 @@ def test_linearity_at_full_size(gpu):
     gpu.check(lib.rails_mv_get(Y.h, r, 0, ctypes.byref(got)), "get")
     assert abs(got.value - want) < 1e-14
     lib.rails_csr_free(A)
+
+
+@pytest.mark.parametrize("case", ["lap3d_mid", "lap3d_first", "convdiff_last", "random", "no_ghosts", "empty_rank",
+                                  "all_ghost"])
+def test_device_halo_plan_equals_the_host_plan(gpu, case):
+    """rails_csr_create builds the halo plan of a row-partitioned operator on the
+    device; the host restatement rails_csr_halo_plan (what Epetra's column map +
+    Import hold, src/Epetra_OperatorWrapper.cpp:87; pinned by
+    tests/test_partition_gloo.py) must give the same renumbering, ghost list,
+    owner rows and per-rank counts -- bit for bit."""
+    import ctypes
+    lib = gpu.cuda()
+    rs = np.random.RandomState(5)
+    world = 4
+    if case.startswith("lap3d") or case.startswith("convdiff"):
+        g = 24
+        m = g ** 3
+        rank = {"lap3d_mid": 1, "lap3d_first": 0, "convdiff_last": 3}[case]
+        r0, r1 = problems.partition_rows(m, world, rank)
+        rp, ci, _ = problems.build("convdiff" if case.startswith("conv") else "laplacian", g, 3, r0, r1)
+    elif case == "random":
+        m, world = 50021, 7
+        r0, r1 = problems.partition_rows(m, world, 3)
+        per = rs.randint(0, 9, r1 - r0)
+        rp = np.concatenate([[0], np.cumsum(per)]).astype(np.int32)
+        ci = rs.randint(0, m, int(rp[-1])).astype(np.int32)        # unsorted, duplicates, any owner
+    elif case == "no_ghosts":
+        m = 4096
+        r0, r1 = problems.partition_rows(m, world, 2)
+        rp = np.arange(r1 - r0 + 1, dtype=np.int32)
+        ci = np.arange(r0, r1, dtype=np.int32)
+    elif case == "empty_rank":
+        m, world = 3, 4                                           # rank 3 owns no rows
+        r0, r1 = problems.partition_rows(m, world, 3)
+        assert r1 == r0
+        rp, ci = np.zeros(1, dtype=np.int32), np.zeros(0, dtype=np.int32)
+    else:                                                          # every column lives elsewhere
+        m = 10000
+        r0, r1 = problems.partition_rows(m, world, 1)
+        rp = (2 * np.arange(r1 - r0 + 1)).astype(np.int32)
+        ci = np.concatenate([rs.randint(0, r0, r1 - r0), rs.randint(r1, m, r1 - r0)]).astype(np.int32)
+    rows, nnz = r1 - r0, int(rp[-1])
+    ci = np.ascontiguousarray(ci)
+
+    def plan(fn):
+        lcol = np.full(max(nnz, 1), -1, dtype=np.int32)
+        gg = np.full(max(nnz, 1), -1, dtype=np.int32)
+        gl = np.full(max(nnz, 1), -1, dtype=np.int32)
+        need = np.full(world, -1, dtype=np.int32)
+        ng = ctypes.c_int(-1)
+        assert fn(rows, m, r0, world, gpu.iptr(rp), gpu.iptr(ci), gpu.iptr(lcol), ctypes.byref(ng), gpu.iptr(gg),
+                  gpu.iptr(gl), gpu.iptr(need)) == 0
+        return lcol[:nnz], ng.value, gg[:ng.value], gl[:ng.value], need
+
+    host, dev = plan(lib.rails_csr_halo_plan), plan(lib.rails_csr_halo_plan_device)
+    assert host[1] == dev[1]
+    for a, b in zip(host, dev):
+        assert np.array_equal(a, b)
+    if case == "no_ghosts" or case == "empty_rank":
+        assert dev[1] == 0
+    # an index outside the global range is an argument error on both
+    if nnz:
+        bad = ci.copy()
+        bad[nnz // 2] = m
+        for fn in (lib.rails_csr_halo_plan, lib.rails_csr_halo_plan_device):
+            lcol = np.zeros(nnz, dtype=np.int32)
+            need = np.zeros(world, dtype=np.int32)
+            ng = ctypes.c_int(0)
+            assert fn(rows, m, r0, world, gpu.iptr(rp), gpu.iptr(bad), gpu.iptr(lcol), ctypes.byref(ng), None, None,
+                      gpu.iptr(need)) == 2

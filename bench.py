@@ -75,6 +75,9 @@ def parse_args():
                     help="identical timed windows run back to back; the MEDIAN is reported, all are listed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true")
+    ap.add_argument("--continuation", action="store_true",
+                    help="add the two-step continuation leg (default for --workload C5)")
+    ap.add_argument("--no-continuation", action="store_true")
     ap.add_argument("--kernels-only", action="store_true",
                     help="only the per-kernel timings (the command profiled with ncu --set full)")
     ap.add_argument("--kernel-k", type=int, default=64)
@@ -326,6 +329,62 @@ def time_kernels(api, rows, rp, ci, v, global_rows, row_offset, k=64, reps=10, s
         o["k"] = k
     V.free(); q.free(); small.free()
     return out
+
+
+def continuation_leg(api, lib, dist, world, rp, ci, v, n_b, params, B, m, r0, M):
+    """first: solve with A.  warm: A <- A - 0.01 I in place, solve from the basis of
+    `first` (resident).  cold: the same second problem from a random start.  Wall
+    clock per solve between barriers, max over ranks; X_warm against X_cold through
+    the k x k Gram matrices (all-reduced)."""
+    def barrier():
+        lib.rails_cuda_sync()
+        if dist is not None:
+            dist.barrier()
+
+    def timed(fn):
+        barrier()
+        t = time.time()
+        out = fn()
+        barrier()
+        return out, allreduce_max(dist, time.time() - t)
+
+    def gram(X, Y):
+        G = np.ascontiguousarray(X.T @ Y)
+        if dist is not None:
+            import torch
+            t = torch.from_numpy(G)
+            dist.all_reduce(t)
+            G = t.numpy()
+        return G
+
+    ses, t_setup = timed(lambda: api.Session(rp, ci, v, n_b, B=B, global_rows=m, row_offset=r0, M=M, skip_draws=1))
+    P = dict(params)
+    P["Random seed"] = 12345          # every solve of this leg draws the same start vectors
+    first, t_first = timed(lambda: ses.solve(P))
+    v2 = problems.shift_diagonal(rp, ci, v, -0.01, r0)
+    _, t_update = timed(lambda: ses.update_operator(v2))
+    Pw = dict(P)
+    Pw["Restart from solution"] = 1
+    warm, t_warm = timed(lambda: ses.solve(Pw))
+    Vw, Tw = ses.download()
+    cold, t_cold2 = timed(lambda: ses.solve(P))
+    Vc, Tc = ses.download()
+    ses.free()
+    Gww, Gcc, Gwc = gram(Vw, Vw), gram(Vc, Vc), gram(Vw, Vc)
+    nw = np.trace(Tw @ Gww @ Tw.T @ Gww)
+    nc = np.trace(Tc @ Gcc @ Tc.T @ Gcc)
+    x_diff = float(np.sqrt(max(nw - 2 * np.trace(Tw @ Gwc @ Tc.T @ Gwc.T) + nc, 0.0) / nc))
+
+    def rec(o, t):
+        return {"ret": int(o["ret"]), "iterations": int(o["iterations"]), "space_size": int(o["k"]),
+                "wall_s": t, "solve_s": o["solve_seconds"], "final_relative_residual": float(o["rel"][-1]),
+                "first_relative_residual": float(o["rel"][0])}
+
+    return {"what": "A, then A - 0.01 I: warm = \"Restart from solution\" from the resident basis of the first "
+                    "solve (operator values replaced in place), cold = the same problem from a random start",
+            "session_setup_s": t_setup, "operator_update_s": t_update,
+            "first": rec(first, t_first), "warm": rec(warm, t_warm), "cold": rec(cold, t_cold2),
+            "warm_over_cold_wall": t_warm / t_cold2, "x_rel_diff_warm_vs_cold": x_diff}
 
 
 def dist_setup(n_gpus):
@@ -605,6 +664,16 @@ def run_b200(args):
         n2 = np.trace(T2 @ G22 @ T2.T @ G22)
         x_diff = float(np.sqrt(max(n1 - 2 * np.trace(T1 @ G12 @ T2.T @ G12.T) + n2, 0.0) / n1))
 
+    # ---- leg 4 (workload C5, or --continuation): the two-step continuation of
+    #      test/LyapunovSolver_test.cpp:312-352 with everything resident on the
+    #      device: one session holds A, B and the solution; the second solve runs
+    #      on A - 0.01 I (values replaced in place, same pattern) warm-started from
+    #      the basis of the first ("Restart from solution"), and is compared with
+    #      the same solve started cold. ------------------------------------------
+    continuation = None
+    if args.continuation or (args.workload == "C5" and not args.no_continuation):
+        continuation = continuation_leg(api, lib, dist, world, rp, ci, v, n_b, params, B, m, r0, M)
+
     kernels = None
     if not args.no_kernels:
         # the step kernel at the median space size of the timed window
@@ -712,6 +781,8 @@ def run_b200(args):
         "solve_seconds": res["solve_seconds"], "setup_seconds": res["setup_seconds"],
         "relative_residual": [float(e2e["rel"][0]), float(e2e["rel"][-1])],
     }
+    if continuation is not None:
+        line["continuation"] = continuation
     print(json.dumps(line), flush=True)
 
 

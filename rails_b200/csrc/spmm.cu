@@ -372,11 +372,10 @@ count_ghost_kernel(const unsigned char *__restrict__ flags, long long nchunks, i
     }
 }
 
-// list[offsets[ch] ..] = the flagged indices of chunk ch in ascending order;
-// gmap[index] = first_ghost + position in the list
+// list[offsets[ch] ..] = the flagged indices of chunk ch in ascending order
 __global__ void __launch_bounds__(256)
 write_ghost_kernel(const unsigned char *__restrict__ flags, long long nchunks, const int *__restrict__ offsets,
-                   int first_ghost, int *__restrict__ list, int *__restrict__ gmap)
+                   int *__restrict__ list)
 {
     const int lane = threadIdx.x & 31;
     for (long long ch = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); ch < nchunks; ch += (long long)gridDim.x * 8)
@@ -400,23 +399,33 @@ write_ghost_kernel(const unsigned char *__restrict__ flags, long long nchunks, c
 #pragma unroll
             for (int b = 0; b < 4; ++b)
                 if (f & (1u << (8 * b)))
-                {
-                    list[pos] = (int)(i0 + b);
-                    gmap[i0 + b] = first_ghost + pos;
-                    ++pos;
-                }
+                    list[pos++] = (int)(i0 + b);
             base += __shfl_sync(0xffffffffu, incl, 31);
         }
     }
 }
 
+// owned columns shift down; a ghost column becomes rows + its position in the sorted
+// ghost list (binary search: ghost entries are the few that cross the partition)
 __global__ void __launch_bounds__(256)
-renumber_kernel(int *__restrict__ colidx, long long nnz, long long lo, long long hi, const int *__restrict__ gmap)
+renumber_kernel(int *__restrict__ colidx, long long nnz, long long lo, long long hi, const int *__restrict__ list,
+                int nlist)
 {
     for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < nnz; i += (long long)gridDim.x * 256)
     {
         const long long g = colidx[i];
-        colidx[i] = (g >= lo && g < hi) ? (int)(g - lo) : gmap[g];
+        if (g >= lo && g < hi)
+            colidx[i] = (int)(g - lo);
+        else
+        {
+            int a = 0, b = nlist;
+            while (a < b)
+            {
+                const int mid = (a + b) >> 1;
+                if (list[mid] < (int)g) a = mid + 1; else b = mid;
+            }
+            colidx[i] = (int)(hi - lo) + a;
+        }
     }
 }
 
@@ -430,19 +439,16 @@ int device_halo_plan(int *colidx_dev, long long nnz, long long rows, long long g
     ghosts.clear();
     if (nnz == 0) return RAILS_OK;
     const long long nchunks = (gm + GH_CHUNK - 1) / GH_CHUNK;
+    // scratch from the block cache: the next operator of the same shape reuses it
     unsigned char *flags = nullptr;
-    int *gmap = nullptr, *counts = nullptr, *list = nullptr;
+    int *counts = nullptr, *list = nullptr;
     int rc = rails::ensure_small(1);
     if (rc) return rc;
     int *bad = reinterpret_cast<int *>(c.d_small);
-    auto cleanup = [&]() { cudaFree(flags); cudaFree(gmap); cudaFree(counts); cudaFree(list); };
-    RAILS_CUDA_TRY(cudaMalloc(&flags, (size_t)nchunks * GH_CHUNK));
-    if (cudaMalloc(&gmap, (size_t)gm * sizeof(int)) != cudaSuccess ||
-        cudaMalloc(&counts, (size_t)(nchunks + 1) * sizeof(int)) != cudaSuccess)
-    {
-        cleanup();
-        return rails::fail(RAILS_ERR_CUDA, "csr_create: out of device memory for the halo plan");
-    }
+    auto cleanup = [&]() { rails::dev_free(flags); rails::dev_free(counts); rails::dev_free(list); };
+    rc = rails::dev_alloc_t(&flags, (size_t)nchunks * GH_CHUNK);
+    if (!rc) rc = rails::dev_alloc_t(&counts, (size_t)(nchunks + 1) * sizeof(int));
+    if (rc) { cleanup(); return rc; }
     RAILS_CUDA_TRY(cudaMemsetAsync(flags, 0, (size_t)nchunks * GH_CHUNK, c.stream));
     RAILS_CUDA_TRY(cudaMemsetAsync(bad, 0, sizeof(int), c.stream));
     const int nb = (int)std::min<long long>((nnz + 1023) / 1024, (long long)c.sm_count * 8);
@@ -473,15 +479,11 @@ int device_halo_plan(int *colidx_dev, long long nnz, long long rows, long long g
         cleanup();
         return rails::fail(RAILS_ERR_ARG, "csr_create: owned + ghost columns exceed the int32 index range");
     }
-    if (cudaMalloc(&list, std::max<size_t>((size_t)total, 1) * sizeof(int)) != cudaSuccess)
-    {
-        cleanup();
-        return rails::fail(RAILS_ERR_CUDA, "csr_create: out of device memory for the halo plan");
-    }
+    rc = rails::dev_alloc_t(&list, std::max<size_t>((size_t)total, 1) * sizeof(int));
+    if (rc) { cleanup(); return rc; }
     RAILS_CUDA_TRY(cudaMemcpyAsync(counts, h.data(), (size_t)(nchunks + 1) * sizeof(int), cudaMemcpyHostToDevice, c.stream));
-    RAILS_LAUNCH(write_ghost_kernel, nbc, 256, 0, (const unsigned char *)flags, nchunks, (const int *)counts,
-                 (int)rows, list, gmap);
-    RAILS_LAUNCH(renumber_kernel, nb, 256, 0, colidx_dev, nnz, lo, hi, (const int *)gmap);
+    RAILS_LAUNCH(write_ghost_kernel, nbc, 256, 0, (const unsigned char *)flags, nchunks, (const int *)counts, list);
+    RAILS_LAUNCH(renumber_kernel, nb, 256, 0, colidx_dev, nnz, lo, hi, (const int *)list, (int)total);
     RAILS_CHECK_LAUNCH();
     ghosts.resize((size_t)total);
     if (total)
@@ -713,7 +715,8 @@ extern "C" int rails_csr_create(long long rows, long long global_rows, long long
     A->recv_count = need;
     // need matrix: all[r * P + p] = rows rank r needs from rank p
     int *d_all = nullptr, *d_ids = nullptr;
-    RAILS_CUDA_TRY(cudaMalloc(&d_all, (size_t)P * P * sizeof(int)));
+    rc = rails::dev_alloc_t(&d_all, (size_t)P * P * sizeof(int));
+    if (rc) { free_csr(A); return rc; }
     RAILS_CUDA_TRY(cudaMemcpyAsync(d_all + (size_t)c.rank * P, need.data(), P * sizeof(int),
                                    cudaMemcpyHostToDevice, c.stream));
     RAILS_NCCL_TRY(ncclAllGather(d_all + (size_t)c.rank * P, d_all, P, ncclInt, c.comm, c.stream));
@@ -725,7 +728,8 @@ extern "C" int rails_csr_create(long long rows, long long global_rows, long long
         A->send_count[p] = all[(size_t)p * P + c.rank];
         A->nsend += A->send_count[p];
     }
-    RAILS_CUDA_TRY(cudaMalloc(&d_ids, std::max<size_t>(ghost_local.size(), 1) * sizeof(int)));
+    rc = rails::dev_alloc_t(&d_ids, std::max<size_t>(ghost_local.size(), 1) * sizeof(int));
+    if (rc) { free_csr(A); return rc; }
     rc = rails::dev_alloc_t(&A->send_rows, std::max<size_t>(A->nsend, 1) * sizeof(int));
     if (rc) { free_csr(A); return rc; }
     if (!ghost_local.empty())
@@ -746,8 +750,8 @@ extern "C" int rails_csr_create(long long rows, long long global_rows, long long
     }
     RAILS_NCCL_TRY(ncclGroupEnd());
     RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
-    cudaFree(d_all);
-    cudaFree(d_ids);
+    rails::dev_free(d_all);
+    rails::dev_free(d_ids);
     *out = A;
     return RAILS_OK;
 }

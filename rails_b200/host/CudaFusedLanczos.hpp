@@ -34,6 +34,12 @@ template<>
 struct BackendHealth<CudaMultiVectorWrapper>
 {
     static long long errors() { return rails_cuda_error_count(); }
+    static void fence()
+    {
+        static const bool profiling = std::getenv("RAILS_PROFILE") && std::atoi(std::getenv("RAILS_PROFILE")) != 0;
+        if (profiling)
+            rails_cuda_sync();
+    }
 };
 
 // The projection dots with one host round trip (rails_mv_dot_batch).

@@ -126,6 +126,11 @@ template<class MultiVector>
 struct BackendHealth
 {
     static long long errors() { return 0; }
+    // Called where a timed section closes.  A backend whose calls are asynchronous
+    // waits here for its queued work WHEN PROFILING IS ON (RAILS_PROFILE=1 for the CUDA
+    // wrappers), so that the section table shows where device time goes rather than
+    // where the host happened to block; a no-op otherwise.
+    static void fence() {}
 };
 
 struct IterationRecord
@@ -297,6 +302,7 @@ protected:
             : acc(a), name(n), t0(std::chrono::steady_clock::now()) {}
         ~Section()
         {
+            BackendHealth<MultiVector>::fence();
             acc[name] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         }
     };

@@ -144,6 +144,7 @@ void Solver<Matrix, MultiVector, DenseMatrix>::compress(
     DenseMatrix X;
     compute_restart_vectors(X, T, std::min(reduced_size_, V.N()), restart_tolerance_);
     const int kept = X.N();
+    Section s(sections_, "Restart compression");
 
     if (tsqr)
     {
@@ -528,9 +529,12 @@ int Solver<Matrix, MultiVector, DenseMatrix>::solve(MultiVector &V, DenseMatrix 
         }
         else
         {
-            std::vector<int> picked = pick_ritz(grow_by);
-            for (int i = 0; i < grow_by; i++)
-                V.push_back(ritz_vectors.view(picked[i]));
+            {
+                Section e(sections_, "Expand");
+                std::vector<int> picked = pick_ritz(grow_by);
+                for (int i = 0; i < grow_by; i++)
+                    V.push_back(ritz_vectors.view(picked[i]));
+            }
             Section s(sections_, "orthogonalize");
             V.orthogonalize();
         }

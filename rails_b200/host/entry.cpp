@@ -10,7 +10,9 @@
 #include "RailsSolver.hpp"
 #include "CudaFusedLanczos.hpp"
 
+#include <atomic>
 #include <chrono>
+#include <thread>
 #include <dlfcn.h>
 #include <cstdlib>
 #include <cstring>
@@ -88,8 +90,19 @@ struct Session
     bool has_solution = false;
     HostDenseMatrix T;
     double setup_seconds = 0.0;
+    std::atomic<int> *space_now = nullptr;      // updated every iteration when set (one-shot solve)
 };
 
+}
+
+namespace
+{
+// set-up = everything between entry and the download that is not the solve
+double s_setup_for_trace(std::chrono::steady_clock::time_point t0, std::chrono::steady_clock::time_point t1,
+                         const double *solve_seconds)
+{
+    return std::chrono::duration<double>(t1 - t0).count() - (solve_seconds ? *solve_seconds : 0.0);
+}
 }
 
 extern "C" {
@@ -230,6 +243,8 @@ int rails_host_session_solve(void *session, int nparams, const char *const *keys
     bool have_start = false, have_stop = false;
     long long launches_start = 0, launches_stop = 0;
     solver.set_observer([&](b200::IterationRecord const &rec) {
+        if (s->space_now)
+            s->space_now->store(rec.space_size, std::memory_order_relaxed);
         if (rec.iteration == time_from)
         {
             have_start = rails_cuda_event_record(0) == 0;
@@ -365,15 +380,47 @@ int rails_host_solve_x(int rows, int global_rows, int row_offset,
         return 102;
     }
     auto t_setup = std::chrono::steady_clock::now();
+    const bool warm = params.get("Restart from solution", false);
+    // The output block V_io is usually fresh memory: every page faults on its first
+    // write, ~10 GB/s when that happens inside the download.  A helper thread touches
+    // the columns the solution can occupy (the space size so far, plus two) while the
+    // GPU works; the values are left as they are.
+    std::atomic<int> space_now(0);
+    std::atomic<bool> stop_touching(false);
+    std::thread toucher;
+    struct JoinToucher
+    {
+        std::atomic<bool> &stop; std::thread &t;
+        ~JoinToucher() { stop.store(true); if (t.joinable()) t.join(); }
+    } join_toucher{stop_touching, toucher};
+    if (V_io && v_cap_cols > 0 && rows > 0 && !warm && !std::getenv("RAILS_NO_PREFAULT"))
+        toucher = std::thread([&, rows, v_cap_cols, V_io] {
+            const size_t col_bytes = (size_t)rows * sizeof(double);
+            int done = 0;
+            while (!stop_touching.load(std::memory_order_relaxed))
+            {
+                const int target = std::min(v_cap_cols, std::max(8, space_now.load(std::memory_order_relaxed) + 2));
+                if (done >= target)
+                {
+                    std::this_thread::sleep_for(std::chrono::microseconds(200));
+                    continue;
+                }
+                volatile char *col = reinterpret_cast<volatile char *>(V_io) + (size_t)done * col_bytes;
+                for (size_t off = 0; off < col_bytes && !stop_touching.load(std::memory_order_relaxed); off += 4096)
+                    col[off] = col[off];
+                col[col_bytes - 1] = col[col_bytes - 1];
+                ++done;
+            }
+        });
     Session *s = static_cast<Session *>(rails_host_session_create(
         rows, global_rows, row_offset, rowptr, colidx, vals, m_rowptr, m_colidx, m_vals, n_b, B_in, seed,
         params.get("Skip random draws", 0)));
     if (!s)
         return 200;
     std::unique_ptr<Session> owner(s);
+    s->space_now = &space_now;
     if (n_null > 0 && N_in && rails_host_session_set_nullspace(s, n_null, N_in))
         return 200;
-    const bool warm = params.get("Restart from solution", false);
     if (warm && k_io && V_io && *k_io > 0 && rails_host_session_set_start(s, *k_io, V_io))
         return 200;
     rails_cuda_sync();
@@ -388,8 +435,24 @@ int rails_host_solve_x(int rows, int global_rows, int row_offset,
         return ret;
     if (k_io)
         *k_io = k;
+    s->space_now = nullptr;
+    stop_touching.store(true);
+    if (toucher.joinable())
+        toucher.join();
+    auto t_down = std::chrono::steady_clock::now();
     if (V_io && T_out && k <= v_cap_cols && rails_host_session_download(s, v_cap_cols, V_io, T_out) < 0)
         return 200;
+    // RAILS_E2E_TRACE=1: where the wall clock of a one-shot solve goes (stderr)
+    if (std::getenv("RAILS_E2E_TRACE"))
+    {
+        auto now = std::chrono::steady_clock::now();
+        owner.reset();
+        auto freed = std::chrono::steady_clock::now();
+        std::cerr << "rails_host_solve trace: set-up " << s_setup_for_trace(t_setup, t_down, solve_seconds)
+                  << " s, solve " << (solve_seconds ? *solve_seconds : 0.0) << " s, download "
+                  << std::chrono::duration<double>(now - t_down).count() << " s, free "
+                  << std::chrono::duration<double>(freed - now).count() << " s" << std::endl;
+    }
     return ret;
 }
 

@@ -39,6 +39,7 @@
 #include "SolutionTools.hpp"
 
 #include <chrono>
+#include <ctime>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -46,6 +47,7 @@
 #include <iostream>
 #include <string>
 #include <thread>
+#include <sys/stat.h>
 #include <unistd.h>
 
 using namespace RAILS;
@@ -111,9 +113,13 @@ int exchange_id(std::string const &path, int rank, char id[RAILS_NCCL_ID_BYTES])
         std::fclose(f);
         return std::rename(tmp.c_str(), path.c_str());
     }
+    // a file left behind by a run that died before rank 0 could remove it is older
+    // than this launch: ignore anything written more than two minutes before now
+    const time_t oldest = std::time(nullptr) - 120;
     for (int tries = 0; tries < 6000; ++tries)
     {
-        FILE *f = std::fopen(path.c_str(), "rb");
+        struct stat st;
+        FILE *f = stat(path.c_str(), &st) == 0 && st.st_mtime >= oldest ? std::fopen(path.c_str(), "rb") : nullptr;
         if (f)
         {
             size_t got = std::fread(id, 1, RAILS_NCCL_ID_BYTES, f);
@@ -262,8 +268,13 @@ int main(int argc, char *argv[])
         {
             std::cerr << "rank " << rank << ": communicator setup failed: " << rails_cuda_last_error()
                       << std::endl;
+            if (rank == 0)
+                std::remove(file.c_str());
             return 3;
         }
+        // the communicator exists on every rank, so every rank has read the id
+        if (rank == 0)
+            std::remove(file.c_str());
     }
 
     std::map<std::string, double> profile;

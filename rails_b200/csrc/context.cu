@@ -253,39 +253,74 @@ int copy_h2d(void *dst, const void *src, size_t bytes)
     return RAILS_OK;
 }
 
-int copy_d2h(void *dst, const void *src, size_t bytes)
+// `ncols` columns of `col_bytes` each (strides dst_ld / src_ld bytes) through the two
+// pinned buffers as ONE pipeline: piece i+1 is in flight while piece i is copied out of
+// its buffer, across column boundaries too.
+int copy_d2h_2d(void *dst, size_t dst_ld, const void *src, size_t src_ld, size_t col_bytes, int ncols)
 {
     Context &c = ctx();
-    if (bytes < (8u << 20))
+    if (col_bytes == 0 || ncols <= 0)
+        return RAILS_OK;
+    if (dst_ld == col_bytes && src_ld == col_bytes)
     {
-        RAILS_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.stream));
+        // contiguous on both sides: one long column
+        col_bytes *= (size_t)ncols;
+        dst_ld = src_ld = col_bytes;
+        ncols = 1;
+    }
+    if (col_bytes * (size_t)ncols < (8u << 20))
+    {
+        RAILS_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_ld, src, src_ld, col_bytes, ncols, cudaMemcpyDeviceToHost, c.stream));
         RAILS_CUDA_TRY(cudaStreamSynchronize(c.stream));
         return RAILS_OK;
     }
     int rc = ensure_stage();
     if (rc) return rc;
-    // chunk i+1 is in flight while chunk i is copied out of its pinned buffer
-    size_t off_prev = 0, len_prev = 0;
+    // pieces: a slice of one tall column, or several whole short columns packed densely
+    struct Piece { char *dst; size_t len; int cols; };
+    Piece prev = {nullptr, 0, 0};
+    auto drain = [&](int buf) -> int {
+        RAILS_CUDA_TRY(cudaEventSynchronize(c.stage_ev[buf]));
+        if (prev.cols <= 1)
+            parallel_memcpy(prev.dst, c.h_stage[buf], prev.len);
+        else
+            for (int q = 0; q < prev.cols; ++q)
+                memcpy(prev.dst + (size_t)q * dst_ld, (char *)c.h_stage[buf] + (size_t)q * col_bytes, col_bytes);
+        return RAILS_OK;
+    };
     int b = 0;
-    bool have_prev = false;
-    for (size_t off = 0; off < bytes; off += STAGE_CHUNK, b ^= 1)
+    const int pack = col_bytes <= STAGE_CHUNK / 2 ? (int)(STAGE_CHUNK / col_bytes) : 1;
+    for (int j = 0; j < ncols; j += pack)
     {
-        const size_t len = std::min(STAGE_CHUNK, bytes - off);
-        RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_stage[b], (const char *)src + off, len, cudaMemcpyDeviceToHost, c.stream));
-        RAILS_CUDA_TRY(cudaEventRecord(c.stage_ev[b], c.stream));
-        if (have_prev)
+        const int nc = std::min(pack, ncols - j);
+        for (size_t off = 0; off < col_bytes; off += STAGE_CHUNK, b ^= 1)
         {
-            RAILS_CUDA_TRY(cudaEventSynchronize(c.stage_ev[b ^ 1]));
-            parallel_memcpy((char *)dst + off_prev, c.h_stage[b ^ 1], len_prev);
+            const size_t len = std::min(STAGE_CHUNK, col_bytes - off);
+            if (nc > 1)
+                RAILS_CUDA_TRY(cudaMemcpy2DAsync(c.h_stage[b], col_bytes, (const char *)src + (size_t)j * src_ld, src_ld,
+                                                 col_bytes, nc, cudaMemcpyDeviceToHost, c.stream));
+            else
+                RAILS_CUDA_TRY(cudaMemcpyAsync(c.h_stage[b], (const char *)src + (size_t)j * src_ld + off, len,
+                                               cudaMemcpyDeviceToHost, c.stream));
+            RAILS_CUDA_TRY(cudaEventRecord(c.stage_ev[b], c.stream));
+            if (prev.dst)
+            {
+                rc = drain(b ^ 1);
+                if (rc) return rc;
+            }
+            prev.dst = (char *)dst + (size_t)j * dst_ld + off;
+            prev.len = len;
+            prev.cols = nc;
         }
-        off_prev = off; len_prev = len; have_prev = true;
     }
-    if (have_prev)
-    {
-        RAILS_CUDA_TRY(cudaEventSynchronize(c.stage_ev[b ^ 1]));
-        parallel_memcpy((char *)dst + off_prev, c.h_stage[b ^ 1], len_prev);
-    }
+    if (prev.dst)
+        return drain(b ^ 1);
     return RAILS_OK;
+}
+
+int copy_d2h(void *dst, const void *src, size_t bytes)
+{
+    return copy_d2h_2d(dst, bytes, src, bytes, bytes, 1);
 }
 
 int ensure_small(size_t doubles)
@@ -595,22 +630,8 @@ extern "C" int rails_mv_download(rails_mv_t mv, int col0, int ncols, double *hos
         return RAILS_OK;
     if (!host || ldh < mv->rows)
         return rails::fail(RAILS_ERR_ARG, "download: bad host block");
-    if ((size_t)mv->rows * sizeof(double) >= (8u << 20))
-    {
-        for (int j = 0; j < ncols; ++j)
-        {
-            rc = rails::copy_d2h(host + (size_t)j * ldh, mv->data + (size_t)(col0 + j) * mv->ld,
-                                 (size_t)mv->rows * sizeof(double));
-            if (rc) return rc;
-        }
-        return RAILS_OK;
-    }
-    RAILS_CUDA_TRY(cudaMemcpy2DAsync(host, ldh * sizeof(double),
-                                     mv->data + (size_t)col0 * mv->ld, mv->ld * sizeof(double),
-                                     (size_t)mv->rows * sizeof(double), ncols,
-                                     cudaMemcpyDeviceToHost, ctx().stream));
-    RAILS_CUDA_TRY(cudaStreamSynchronize(ctx().stream));
-    return RAILS_OK;
+    return rails::copy_d2h_2d(host, (size_t)ldh * sizeof(double), mv->data + (size_t)col0 * mv->ld,
+                              (size_t)mv->ld * sizeof(double), (size_t)mv->rows * sizeof(double), ncols);
 }
 
 extern "C" int rails_mv_get(rails_mv_t mv, long long row, int col, double *value)

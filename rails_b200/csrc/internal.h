@@ -148,6 +148,7 @@ int upload_small(const double *host, int k, int c, int ldc, const double **d_out
 // (the host block may be reused / is complete on return).
 int copy_h2d(void *dst, const void *src, size_t bytes);
 int copy_d2h(void *dst, const void *src, size_t bytes);
+int copy_d2h_2d(void *dst, size_t dst_ld, const void *src, size_t src_ld, size_t col_bytes, int ncols);
 
 // Finishes a reduction and, with a communicator, sums it over the ranks, in ONE
 // kernel: out[i] = sum over ranks of (sum_b partial[b * n + i]), b < nblocks.

@@ -89,6 +89,22 @@ def test_large_upload_download_round_trip(gpu):
     mv = gpu.MultiVector.from_numpy(a)
     assert np.array_equal(mv.numpy(), a)
     assert np.array_equal(mv.numpy(1, 1), a[:, 1:2])
+    mv.free()
+    # many short columns, > 8 MB in all: several whole columns per pipeline piece;
+    # the host block has a leading dimension larger than the row count
+    m, k = 300007, 37
+    a = np.asfortranarray(np.random.RandomState(1).uniform(-1, 1, (m, k)))
+    mv = gpu.MultiVector.from_numpy(a)
+    out = np.full((m + 5, k - 3), -3.0, order="F")
+    gpu.check(gpu.cuda().rails_mv_download(mv.h, 2, k - 3, gpu.dptr(out), m + 5), "download")
+    assert np.array_equal(out[:m], a[:, 2:k - 1])
+    assert np.all(out[m:] == -3.0)
+    # columns of ~20 MB: one column per piece, odd tail
+    m, k = (20 << 20) // 8 + 77, 5
+    a = np.asfortranarray(np.random.RandomState(2).uniform(-1, 1, (m, k)))
+    mv2 = gpu.MultiVector.from_numpy(a)
+    assert np.array_equal(mv2.numpy(), a)
+    mv.free(); mv2.free()
 
 
 def test_spmm_row_longer_than_the_staging_buffer(gpu):

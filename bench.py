@@ -75,6 +75,10 @@ def parse_args():
                     help="identical timed windows run back to back; the MEDIAN is reported, all are listed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true")
+    ap.add_argument("--parity-full", action="store_true",
+                    help="solve the workload to tolerance on the GPU and on the CPU arm; print the comparison")
+    ap.add_argument("--parity-cpu-grid", type=int, default=0,
+                    help="with --parity-full: grid size of the CPU comparison (default: full size)")
     ap.add_argument("--continuation", action="store_true",
                     help="add the two-step continuation leg (default for --workload C5)")
     ap.add_argument("--no-continuation", action="store_true")
@@ -385,6 +389,64 @@ def continuation_leg(api, lib, dist, world, rp, ci, v, n_b, params, B, m, r0, M)
             "session_setup_s": t_setup, "operator_update_s": t_update,
             "first": rec(first, t_first), "warm": rec(warm, t_warm), "cold": rec(cold, t_cold2),
             "warm_over_cold_wall": t_warm / t_cold2, "x_rel_diff_warm_vs_cold": x_diff}
+
+
+def parity_full(args):
+    """`--parity-full`: the workload solved TO TOLERANCE at full size on the GPU (through
+    rails_host_solve, host buffers) and by the CPU arm (the oracle port, all host
+    threads; the unmodified reference loop is ~20x slower than the port and is compared
+    at reduced sizes in tests/), same inputs: iteration counts, space sizes, the largest
+    relative difference of the residual histories and of X.  `--parity-cpu-grid G` runs
+    the CPU side (and a second GPU solve) at grid G instead, for workloads whose CPU
+    solve does not fit a bench run (C4: ~1 min per CPU iteration at full size).
+    One JSON line; not a bench line."""
+    import harness
+    from rails_b200 import api
+    api.init(0)
+    api.host()
+    kind, g, dim, n_b, params = workload(args)
+    out = {"parity_full": workload_name(args, kind, g, dim, n_b, params), "params": params}
+
+    def both(grid, cpu):
+        m = grid ** dim
+        rp, ci, v = problems.build(kind, grid, dim)
+        M = problems.lumped_mass(m) if params.get("Use mass matrix") else None
+        B = problems.reference_B(m, n_b)
+        P = dict(params)
+        P["Skip random draws"] = 1
+        cap = int(P.get("Restart size", 0)) if P.get("Restart size", 0) > 0 else 400
+        cap = max(cap + int(P.get("Expand size", 1)), 64)
+        t = time.time()
+        d = api.solve(rp, ci, v, n_b, P, B=B, v_cap_cols=cap, M=M)
+        rec = {"grid": grid, "rows": m,
+               "gpu": {"ret": int(d["ret"]), "iterations": int(d["iterations"]), "space_size": int(d["k"]),
+                       "max_space_size": int(d["space"].max()), "wall_s": time.time() - t,
+                       "final_relative_residual": float(d["rel"][-1])}}
+        if not cpu:
+            return rec
+        harness.oracle().oracle_set_num_threads(os.cpu_count() or 1)
+        t = time.time()
+        o = harness.oracle_solve(rp, ci, v, n_b, P, B=B, M=M, v_cap_cols=cap)
+        rec["cpu"] = {"kind": "port", "cores": harness.oracle().oracle_num_threads(), "ret": int(o["ret"]),
+                      "iterations": int(o["iterations"]), "space_size": int(o["k"]),
+                      "max_space_size": int(o["space"].max()), "wall_s": time.time() - t,
+                      "final_relative_residual": float(o["rel"][-1])}
+        n = min(d["iterations"], o["iterations"])
+        rel = np.abs(d["rel"][:n] - o["rel"][:n]) / o["rel"][:n]
+        rec["history_rel_diff_first10"] = float(rel[:10].max())
+        rec["history_rel_diff_all_common"] = float(rel.max())
+        rec["first_iteration_above_1e-8"] = int(np.argmax(rel > 1e-8)) + 1 if np.any(rel > 1e-8) else None
+        rec["space_sizes_equal_on_common_prefix"] = bool(np.array_equal(d["space"][:n], o["space"][:n]))
+        if "V" in d and "V" in o:
+            rec["x_rel_diff"] = float(harness.lowrank_rel_diff(d["V"], d["T"], o["V"], o["T"]))
+        return rec
+
+    if args.parity_cpu_grid:
+        out["full_size"] = both(g, cpu=False)
+        out["reduced"] = both(args.parity_cpu_grid, cpu=True)
+    else:
+        out["full_size"] = both(g, cpu=True)
+    print(json.dumps(out), flush=True)
 
 
 def dist_setup(n_gpus):
@@ -772,6 +834,7 @@ def run_b200(args):
         "window_ms_per_step_min": min(all_ms), "window_ms_per_step_max": max(all_ms),
         "window_spread": (max(all_ms) - min(all_ms)) / min(all_ms),
         "gpu_launches": int(res["timed_launches"]),
+        "host_syncs_per_step": res["timed_syncs"] / float(K),
         "clocks": clocks,
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
@@ -803,7 +866,9 @@ def main():
         real_print(*a, **kw)
         out.flush()
     globals()["print"] = emit
-    if args.impl == "reference":
+    if args.parity_full:
+        parity_full(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)

@@ -69,6 +69,9 @@ long long rails_cuda_error_count(void);
 /* number of this library's kernels launched since init (bench.py's
  * gpu_launches) */
 long long rails_cuda_kernel_launches(void);
+/* stream synchronisations made by the library so far: how often the host waited for
+ * the device (bench.py reports the count per outer iteration) */
+long long rails_cuda_host_syncs(void);
 /* Sustained FP64 throughput of this GPU in TFLOP/s, measured with a register-only
  * kernel on every SM: kind 0 = DFMA (vector pipe), 1 = DMMA (tensor cores).  The
  * denominator of the FLOP-bound rooflines bench.py reports (restart compression,

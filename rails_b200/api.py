@@ -52,6 +52,7 @@ def host():
         lib = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
         lib.rails_host_last_sections.restype = ctypes.c_char_p
         lib.rails_host_last_timed_launches.restype = ctypes.c_longlong
+        lib.rails_host_last_timed_syncs.restype = ctypes.c_longlong
         lib.rails_host_lu_factor.restype = ctypes.c_void_p
         lib.rails_host_schur_create.restype = ctypes.c_void_p
         lib.rails_host_session_create.restype = ctypes.c_void_p
@@ -70,6 +71,7 @@ CUDA_SYMBOLS = [
     ("rails_cuda_last_error", ctypes.c_char_p, []),
     ("rails_cuda_error_count", LL, []),
     ("rails_cuda_kernel_launches", LL, []),
+    ("rails_cuda_host_syncs", LL, []),
     ("rails_cuda_bytes_in_use", LL, []),
     ("rails_cuda_fp64_peak", I, [I, c_double_p]),
     ("rails_cuda_event_record", I, [I]),
@@ -244,7 +246,8 @@ def solve(rowptr, colidx, vals, n_b, params, B=None, seed=1, global_rows=None, r
                space=hk[:n].copy(), seconds=hs[:n].copy(), timed_ms=tm.value,
                solve_seconds=ss.value, setup_seconds=su.value, dense_solve_seconds=sd.value,
                sections=lib.rails_host_last_sections().decode(),
-               timed_launches=lib.rails_host_last_timed_launches())
+               timed_launches=lib.rails_host_last_timed_launches(),
+               timed_syncs=lib.rails_host_last_timed_syncs())
     if V is not None and k.value <= v_cap_cols:
         out["V"] = V[:, :k.value]
         out["T"] = T[:k.value, :k.value]
@@ -298,7 +301,8 @@ class Session:
         return dict(ret=ret, iterations=hl.value, k=k.value, abs=ha[:n].copy(), rel=hr[:n].copy(),
                     space=hk[:n].copy(), seconds=hs[:n].copy(), timed_ms=tm.value, solve_seconds=ss.value,
                     dense_solve_seconds=sd.value, sections=lib.rails_host_last_sections().decode(),
-                    timed_launches=lib.rails_host_last_timed_launches())
+                    timed_launches=lib.rails_host_last_timed_launches(),
+                    timed_syncs=lib.rails_host_last_timed_syncs())
 
     def download(self):
         """(V, T) of the last solution: this rank's rows of V and the k x k T."""

@@ -437,6 +437,7 @@ extern "C" int rails_cuda_sync(void)
 extern "C" const char *rails_cuda_last_error(void) { return ctx().last_error.c_str(); }
 extern "C" long long rails_cuda_error_count(void) { return ctx().errors.load(); }
 extern "C" long long rails_cuda_kernel_launches(void) { return ctx().launches.load(); }
+extern "C" long long rails_cuda_host_syncs(void) { return ctx().host_syncs.load(); }
 extern "C" long long rails_cuda_bytes_in_use(void) { return ctx().bytes_in_use.load(); }
 
 extern "C" int rails_cuda_event_record(int slot)

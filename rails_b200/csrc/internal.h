@@ -114,6 +114,7 @@ struct Context
     const double *lz_q = nullptr;
     int lz_total = 0;
     std::atomic<long long> launches{0};
+    std::atomic<long long> host_syncs{0};      // stream synchronisations the library made (host waits for the GPU)
     std::atomic<long long> errors{0};        // calls that failed since the library was loaded
     std::atomic<long long> bytes_in_use{0};
     std::vector<cudaEvent_t> events;
@@ -149,6 +150,9 @@ int upload_small(const double *host, int k, int c, int ldc, const double **d_out
 int copy_h2d(void *dst, const void *src, size_t bytes);
 int copy_d2h(void *dst, const void *src, size_t bytes);
 int copy_d2h_2d(void *dst, size_t dst_ld, const void *src, size_t src_ld, size_t col_bytes, int ncols);
+// transpose.cu: CSR arrays of A' built on the device (outputs from dev_alloc)
+int csr_transpose_device(long long rows, long long ncols, long long nnz, const int *rowptr, const int *colidx,
+                         const double *vals, int **rowptr_t, int **colidx_t, double **vals_t);
 
 // Finishes a reduction and, with a communicator, sums it over the ranks, in ONE
 // kernel: out[i] = sum over ranks of (sum_b partial[b * n + i]), b < nblocks.
@@ -225,5 +229,17 @@ int gemm_device(const double *V, long long ldv, int k, const double *dC, int ldc
     } while (0)
 
 #define RAILS_CHECK_LAUNCH() RAILS_CUDA_TRY(cudaGetLastError())
+
+// every cudaStreamSynchronize of the library is counted (rails_cuda_host_syncs):
+// the number of times per iteration the host waits for the device is a reported figure
+namespace rails
+{
+inline cudaError_t stream_sync_counted(cudaStream_t s)
+{
+    ctx().host_syncs.fetch_add(1, std::memory_order_relaxed);
+    return (cudaStreamSynchronize)(s);
+}
+}
+#define cudaStreamSynchronize(s) rails::stream_sync_counted(s)
 
 #endif

@@ -254,10 +254,11 @@ void free_csr(rails_csr_s *A)
 }
 
 // uploads CSR arrays whose column indices are already local ([owned|ghost])
-int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const double *vals, bool validate = true)
+// cuts the rows into blocks for the staged kernel (host row pointers in) and uploads
+// the block table
+int plan_blocks(rails_csr_s *A, const int *rowptr)
 {
-    const long long rows = A->rows, nnz = A->nnz;
-    // row blocks
+    const long long rows = A->rows;
     // staging capacity: what a full block of SPMM_THREADS rows needs, bounded
     int cap = 256;
     for (long long r = 0; r < rows; r += SPMM_THREADS)
@@ -280,16 +281,28 @@ int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const doubl
     }
     A->nblk = (int)blk.size() - 1;
     A->max_blk_nnz = maxnnz;
+    const size_t b_blk = blk.size() * sizeof(int);
+    int rc = rails::dev_alloc_t(&A->blk_row, b_blk);
+    if (rc) return rc;
+    A->bytes += b_blk;
+    ctx().bytes_in_use.fetch_add((long long)b_blk);
+    return rails::copy_h2d(A->blk_row, blk.data(), b_blk);
+}
+
+int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const double *vals, bool validate = true)
+{
+    const long long rows = A->rows, nnz = A->nnz;
+    int rca = plan_blocks(A, rowptr);
+    if (rca) return rca;
     // 64 bytes of slack: bulk copies are rounded up to 16 bytes
     size_t b_rp = (size_t)(rows + 1) * sizeof(int), b_ci = (size_t)nnz * sizeof(int) + 64,
-           b_v = (size_t)nnz * sizeof(double) + 64, b_blk = blk.size() * sizeof(int);
-    int rca = rails::dev_alloc_t(&A->rowptr, b_rp);
+           b_v = (size_t)nnz * sizeof(double) + 64;
+    rca = rails::dev_alloc_t(&A->rowptr, b_rp);
     if (!rca) rca = rails::dev_alloc_t(&A->colidx, b_ci);
     if (!rca) rca = rails::dev_alloc_t(&A->vals, b_v);
-    if (!rca) rca = rails::dev_alloc_t(&A->blk_row, b_blk);
     if (rca) return rca;
-    A->bytes += b_rp + b_ci + b_v + b_blk;
-    ctx().bytes_in_use.fetch_add((long long)(b_rp + b_ci + b_v + b_blk));
+    A->bytes += b_rp + b_ci + b_v;
+    ctx().bytes_in_use.fetch_add((long long)(b_rp + b_ci + b_v));
     int rc = rails::copy_h2d(A->rowptr, rowptr, b_rp);
     if (rc) return rc;
     if (nnz)
@@ -299,8 +312,6 @@ int upload_csr(rails_csr_s *A, const int *rowptr, const int *colidx, const doubl
         rc = rails::copy_h2d(A->vals, vals, (size_t)nnz * sizeof(double));
         if (rc) return rc;
     }
-    rc = rails::copy_h2d(A->blk_row, blk.data(), b_blk);
-    if (rc) return rc;
     // column indices are validated where they now live: one streaming pass on
     // the device instead of a scalar host loop over nnz entries
     if (nnz && validate)
@@ -882,37 +893,14 @@ extern "C" long long rails_csr_nnz(rails_csr_t A) { return A ? A->nnz : -1; }
 namespace
 {
 
+// A' of this rank's block as a CSR operator of its own, built on the device
+// (transpose.cu).  For a row-partitioned A the block is rows x [owned | ghost] columns,
+// so A' has ncols_local + nghost rows: the owned part of A'x comes out first, the
+// ghost part is what the owners of those rows still have to add (reverse halo).
 int build_transpose(rails_csr_s *A)
 {
     if (A->transposed) return RAILS_OK;
-    if (A->partitioned)
-        return rails::fail(RAILS_ERR_ARG, "transposed apply is not available on a row-partitioned operator");
-    const long long m = A->rows, n = A->global_cols, nnz = A->nnz;
-    // rare path (B given as an Operator, Operator::norm): the CSR arrays are
-    // read back from the device rather than kept on the host for every operator
-    std::vector<int> h_rowptr(m + 1), h_colidx(nnz);
-    std::vector<double> h_vals(nnz);
-    int rc0 = rails::copy_d2h(h_rowptr.data(), A->rowptr, (size_t)(m + 1) * sizeof(int));
-    if (rc0) return rc0;
-    if (nnz)
-    {
-        rc0 = rails::copy_d2h(h_colidx.data(), A->colidx, (size_t)nnz * sizeof(int));
-        if (rc0) return rc0;
-        rc0 = rails::copy_d2h(h_vals.data(), A->vals, (size_t)nnz * sizeof(double));
-        if (rc0) return rc0;
-    }
-    std::vector<int> rp(n + 1, 0), ci(nnz);
-    std::vector<double> v(nnz);
-    for (long long p = 0; p < nnz; ++p) rp[h_colidx[p] + 1]++;
-    for (long long j = 0; j < n; ++j) rp[j + 1] += rp[j];
-    std::vector<int> next(rp.begin(), rp.end() - 1);
-    for (long long i = 0; i < m; ++i)
-        for (int p = h_rowptr[i]; p < h_rowptr[i + 1]; ++p)
-        {
-            int q = next[h_colidx[p]]++;
-            ci[q] = (int)i;
-            v[q] = h_vals[p];
-        }
+    const long long m = A->rows, n = A->ncols_local + A->nghost, nnz = A->nnz;
     rails_csr_s *T = new rails_csr_s();
     T->rows = n; T->global_rows = n; T->global_cols = m; T->row_offset = 0; T->nnz = nnz;
     T->ncols_local = m;
@@ -920,9 +908,80 @@ int build_transpose(rails_csr_s *A)
     T->send_rows = nullptr; T->send_buf = T->ghost_buf = nullptr;
     T->nghost = T->nsend = 0; T->halo_cols_cap = 0; T->transposed = nullptr; T->bytes = 0;
     T->partitioned = false;
-    int rc = upload_csr(T, rp.data(), ci.data(), v.data());
+    T->recv_count.assign(ctx().nranks, 0);
+    T->send_count.assign(ctx().nranks, 0);
+    int rc = rails::csr_transpose_device(m, n, nnz, A->rowptr, A->colidx, A->vals, &T->rowptr, &T->colidx, &T->vals);
+    if (rc) { free_csr(T); return rc; }
+    T->bytes = (size_t)(n + 1) * sizeof(int) + (size_t)nnz * (sizeof(int) + sizeof(double)) + 128;
+    ctx().bytes_in_use.fetch_add((long long)T->bytes);
+    // the block table is cut on the host from the row pointers (4 (n + 1) bytes back)
+    std::vector<int> h_rowptr(n + 1);
+    rc = rails::copy_d2h(h_rowptr.data(), T->rowptr, (size_t)(n + 1) * sizeof(int));
+    if (!rc) rc = plan_blocks(T, h_rowptr.data());
     if (rc) { free_csr(T); return rc; }
     A->transposed = T;
+    return RAILS_OK;
+}
+
+__global__ void __launch_bounds__(256)
+add_rows_kernel(const int *__restrict__ rows, int n, const double *__restrict__ buf, long long ldb,
+                double *__restrict__ Y, long long ldy)
+{
+    const int c = blockIdx.y;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256)
+        Y[rows[i] + (size_t)c * ldy] += buf[i + (size_t)c * ldb];
+}
+
+// Y = A' X on a row-partitioned A: Z = (local block)' X has ncols_local + nghost rows;
+// its first ncols_local rows are this rank's own contribution to Y, the ghost rows go to
+// their owners, who add what they receive peer by peer in rank order (a fixed order: the
+// result does not depend on arrival times).  The plan is the forward halo plan with the
+// roles of the lists exchanged (Epetra: Export with Add over the column map).
+int transposed_apply_partitioned(rails_csr_s *A, const double *X, long long ldx, int ncols, double *Y, long long ldy)
+{
+    rails::Context &c = ctx();
+    rails_csr_s *T = A->transposed;
+    const long long nz = T->rows;                       // ncols_local + nghost
+    double *Z = nullptr;
+    int rc = rails::dev_alloc_t(&Z, (size_t)std::max<long long>(nz, 1) * ncols * sizeof(double));
+    if (rc) return rc;
+    rc = launch_spmm(T, X, ldx, ncols, Z, nz);
+    if (!rc) rc = ensure_halo_cols(A, ncols);
+    if (rc) { rails::dev_free(Z); return rc; }
+    if (A->ncols_local)
+        RAILS_CUDA_TRY(cudaMemcpy2DAsync(Y, (size_t)ldy * sizeof(double), Z, (size_t)nz * sizeof(double),
+                                         (size_t)A->ncols_local * sizeof(double), ncols, cudaMemcpyDeviceToDevice,
+                                         c.stream));
+    RAILS_NCCL_TRY(ncclGroupStart());
+    long long soff = 0, goff = 0;
+    for (int p = 0; p < c.nranks; ++p)
+    {
+        for (int col = 0; col < ncols; ++col)
+        {
+            if (A->recv_count[p])           // ghost rows of Z go back to their owner
+                RAILS_NCCL_TRY(ncclSend(Z + A->ncols_local + goff + (size_t)col * nz, A->recv_count[p], ncclDouble, p,
+                                        c.comm, c.stream));
+            if (A->send_count[p])           // contributions to the rows this rank sends in the forward halo
+                RAILS_NCCL_TRY(ncclRecv(A->send_buf + soff + (size_t)col * A->nsend, A->send_count[p], ncclDouble, p,
+                                        c.comm, c.stream));
+        }
+        soff += A->send_count[p];
+        goff += A->recv_count[p];
+    }
+    RAILS_NCCL_TRY(ncclGroupEnd());
+    soff = 0;
+    for (int p = 0; p < c.nranks; ++p)
+    {
+        if (A->send_count[p])
+        {
+            dim3 grid(std::min((A->send_count[p] + 255) / 256, c.sm_count * 4), ncols);
+            RAILS_LAUNCH(add_rows_kernel, grid, 256, 0, (const int *)(A->send_rows + soff), A->send_count[p],
+                         (const double *)(A->send_buf + soff), (long long)A->nsend, Y, ldy);
+        }
+        soff += A->send_count[p];
+    }
+    RAILS_CHECK_LAUNCH();
+    rails::dev_free(Z);          // stream-ordered reuse: later work on this stream comes after the sends
     return RAILS_OK;
 }
 
@@ -944,6 +1003,15 @@ extern "C" int rails_csr_spmm(rails_csr_t A, int trans, rails_mv_t X, int xc0, i
         int rc = build_transpose(A);
         if (rc) return rc;
         Op = A->transposed;
+        if (A->partitioned)
+        {
+            if (X->rows != A->rows || Y->rows != A->ncols_local)
+                return rails::fail(RAILS_ERR_ARG, "spmm: transposed operator %lld x %lld applied to %lld rows -> %lld rows",
+                                   A->ncols_local, A->rows, X->rows, Y->rows);
+            if (ncols == 0) return RAILS_OK;
+            return transposed_apply_partitioned(A, X->data + (size_t)xc0 * X->ld, X->ld, ncols,
+                                                Y->data + (size_t)yc0 * Y->ld, Y->ld);
+        }
     }
     if (X->rows != Op->ncols_local || Y->rows != Op->rows)
         return rails::fail(RAILS_ERR_ARG, "spmm: operator %lld x %lld applied to %lld rows -> %lld rows",
@@ -966,12 +1034,16 @@ extern "C" int rails_csr_norm2(rails_csr_t A, double *out)
         return rails::fail(RAILS_ERR_ARG, "csr_norm2: null argument");
     int rc = build_transpose(A);
     if (rc) return rc;
+    // on a row-partitioned operator x and y are distributed like its rows (the dots
+    // below then reduce over the ranks) and the start vector is the same global vector
+    // whatever the partition
+    const int flags = A->partitioned ? 0 : RAILS_MV_REPLICATED;
     rails_mv_t x = nullptr, y = nullptr;
-    rc = rails_mv_alloc(A->ncols_local, 1, RAILS_MV_REPLICATED, &x);
+    rc = rails_mv_alloc(A->ncols_local, 1, flags, &x);
     if (rc) return rc;
-    rc = rails_mv_alloc(A->rows, 1, RAILS_MV_REPLICATED, &y);
+    rc = rails_mv_alloc(A->rows, 1, flags, &y);
     if (rc) { rails_mv_free(x); return rc; }
-    rails_mv_random(x, 0, 1, 0, 12345u);
+    rails_mv_random(x, 0, 1, A->partitioned ? A->row_offset : 0, 12345u);
     double lambda = 0.0, prev = -1.0;
     for (int it = 0; it < 1000; ++it)
     {

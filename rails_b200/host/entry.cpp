@@ -69,6 +69,7 @@ void limit_blas_threads()
     if (n > 0) f(n);
 }
 long long g_timed_launches = 0;
+long long g_timed_syncs = 0;
 
 }
 
@@ -241,7 +242,7 @@ int rails_host_session_solve(void *session, int nparams, const char *const *keys
         s->V = CudaMultiVectorWrapper(s->global_rows, 1);
 
     bool have_start = false, have_stop = false;
-    long long launches_start = 0, launches_stop = 0;
+    long long launches_start = 0, launches_stop = 0, syncs_start = 0, syncs_stop = 0;
     solver.set_observer([&](b200::IterationRecord const &rec) {
         if (s->space_now)
             s->space_now->store(rec.space_size, std::memory_order_relaxed);
@@ -249,11 +250,13 @@ int rails_host_session_solve(void *session, int nparams, const char *const *keys
         {
             have_start = rails_cuda_event_record(0) == 0;
             launches_start = rails_cuda_kernel_launches();
+            syncs_start = rails_cuda_host_syncs();
         }
         if (rec.iteration == time_to)
         {
             have_stop = rails_cuda_event_record(1) == 0;
             launches_stop = rails_cuda_kernel_launches();
+            syncs_stop = rails_cuda_host_syncs();
         }
     });
     rails_cuda_sync();
@@ -261,6 +264,7 @@ int rails_host_session_solve(void *session, int nparams, const char *const *keys
     {
         have_start = rails_cuda_event_record(0) == 0;
         launches_start = rails_cuda_kernel_launches();
+        syncs_start = rails_cuda_host_syncs();
     }
     auto t0 = std::chrono::steady_clock::now();
 
@@ -277,6 +281,7 @@ int rails_host_session_solve(void *session, int nparams, const char *const *keys
             rails_cuda_event_elapsed_ms(0, 1, timed_ms);
     }
     g_timed_launches = have_start && have_stop ? launches_stop - launches_start : 0;
+    g_timed_syncs = have_start && have_stop ? syncs_stop - syncs_start : 0;
 
     auto const &hist = solver.history();
     if (hist_len)
@@ -501,5 +506,7 @@ void rails_host_limit_blas_threads(void) { limit_blas_threads(); }
 
 // kernels launched between the two timing marks of the last solve
 long long rails_host_last_timed_launches(void) { return g_timed_launches; }
+// stream synchronisations of the library inside the same window
+long long rails_host_last_timed_syncs(void) { return g_timed_syncs; }
 
 }

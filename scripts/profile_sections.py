@@ -50,5 +50,5 @@ if rank == 0:
   print(json.dumps({"rows": r1 - r0, "ranks": world, "profile": os.environ.get("RAILS_PROFILE", "0"),
                   "alpha": os.environ.get("RAILS_LANCZOS_ALPHA", "projected"),
                   "ms_per_step_median": best["timed_ms"] / K, "ms_per_step_all": [r["timed_ms"] / K for r in runs],
-                  "launches_per_step": best["timed_launches"] / K,
+                  "launches_per_step": best["timed_launches"] / K, "host_syncs_per_step": best["timed_syncs"] / K,
                   "sections_ms_per_iteration": {k: round(1e3 * float(x) / (W + K), 4) for k, x in sec.items()}}))

@@ -78,6 +78,25 @@ def main():
                                          harness.dptr(Xg), LL(m), harness.dptr(Yo), LL(m))
             assert np.array_equal(Y, Yo), "distributed SpMM differs from the global CSR loop"
 
+        # 1b. transposed apply on the partition (a2: local block' * x, ghost part sent
+        #     back to the owners and added in rank order) against the global A'X, and
+        #     twice in a row bit for bit; 2-norm of the partitioned operator
+        Zd = api.MultiVector(rows, e)
+        api.check(lib.rails_csr_spmm(A, 1, Xd.h, 0, e, Zd.h, 0), "spmm^T")
+        Z = gather_rows(Zd.numpy())
+        api.check(lib.rails_csr_spmm(A, 1, Xd.h, 0, e, Zd.h, 0), "spmm^T")
+        assert np.array_equal(gather_rows(Zd.numpy()), Z), "transposed apply is not reproducible"
+        nrm2 = ctypes.c_double(0)
+        api.check(lib.rails_csr_norm2(A, ctypes.byref(nrm2)), "norm2")
+        if rank == 0:
+            import scipy.sparse as sp
+            Ag = sp.csr_matrix((vg, cig, rpg), shape=(m, m))
+            Zo = Ag.T @ Xg
+            assert np.max(np.abs(Z - Zo)) <= 1e-13 * np.max(np.abs(Zo)), "distributed A'X"
+            import scipy.sparse.linalg as spl
+            s_max = spl.svds(Ag, k=1, return_singular_vectors=False)[0]
+            assert abs(nrm2.value - s_max) < 1e-5 * s_max, ("norm2", nrm2.value, s_max)
+
         # 2. inner products
         out = np.zeros((e, e), order="F")
         api.check(lib.rails_mv_dot(Xd.h, 0, e, Yd.h, 0, e, api.dptr(out), e), "dot")

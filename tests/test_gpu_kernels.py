@@ -169,6 +169,68 @@ def test_spmm_transpose_and_irregular_rows(gpu):
     gpu.cuda().rails_csr_free(A)
 
 
+@pytest.mark.parametrize("shape", ["grid", "tall_dense_columns", "wide", "one_column", "empty"])
+def test_transposed_operator_built_on_the_device_is_exact_and_ordered(gpu, shape):
+    """a2: A' is built on the device (column histogram, scan, STABLE radix sort of the
+    positions by column, gather).  Every row of A' must list its entries by ascending
+    original row, so that A'x is the same sum, term by term in the same order, as a CSR
+    loop over scipy's A.T.tocsr() (which sorts the same way): bit for bit, and the same
+    on a rebuilt operator.  tall_dense_columns is B given as an Operator
+    (src/LyapunovSolver.hpp:150,389: B'W): rows of A' with 120 000 entries."""
+    import scipy.sparse as sp
+    rs = np.random.RandomState(8)
+    if shape == "grid":
+        rp, ci, v = problems.build("convdiff", 40, 3)
+        m = n = 40 ** 3
+    elif shape == "tall_dense_columns":
+        m, n = 120000, 5
+        D = rs.uniform(-1, 1, (m, n))
+        D[rs.uniform(size=(m, n)) < 0.3] = 0.0
+        D[:, 2] = rs.uniform(0.5, 1, m)              # one completely dense column
+        S = sp.csr_matrix(D)
+        rp, ci, v = S.indptr.astype(np.int32), S.indices.astype(np.int32), S.data.copy()
+    elif shape == "wide":
+        m, n = 300, 70001                             # 17 bits of column index: three radix passes
+        S = sp.random(m, n, density=0.002, format="csr", random_state=rs, data_rvs=lambda k: rs.uniform(-1, 1, k))
+        rp, ci, v = S.indptr.astype(np.int32), S.indices.astype(np.int32), S.data.copy()
+    elif shape == "one_column":
+        m, n = 5000, 1
+        rp = np.arange(m + 1, dtype=np.int32)
+        ci, v = np.zeros(m, dtype=np.int32), rs.uniform(-1, 1, m)
+    else:
+        m, n = 100, 50
+        rp, ci, v = np.zeros(m + 1, dtype=np.int32), np.zeros(0, dtype=np.int32), np.zeros(0)
+    St = sp.csr_matrix((v, ci, rp), shape=(m, n)).T.tocsr()
+    St.sort_indices()
+    e = 2
+    X = np.asfortranarray(rs.uniform(-1, 1, (m, e)))
+    want = np.zeros((n, e), order="F")
+    LL = ctypes.c_longlong
+    if St.nnz:
+        harness.oracle().oracle_spmm(n, harness.iptr(St.indptr.astype(np.int32)),
+                                     harness.iptr(St.indices.astype(np.int32)),
+                                     harness.dptr(np.ascontiguousarray(St.data)), e, harness.dptr(X), LL(m),
+                                     harness.dptr(want), LL(n))
+    outs = []
+    for _ in range(2):                               # two operators: the build itself is reproducible
+        A = ctypes.c_void_p()
+        gpu.check(gpu.cuda().rails_csr_create(m, m, n, 0, gpu.iptr(rp), gpu.iptr(ci), gpu.dptr(v),
+                                              ctypes.byref(A)), "csr_create")
+        Xd, Yd = gpu.MultiVector.from_numpy(X), gpu.MultiVector(n, e)
+        gpu.check(gpu.cuda().rails_mv_fill(Yd.h, 0, e, ctypes.c_double(3.0)), "fill")
+        gpu.check(gpu.cuda().rails_csr_spmm(A, 1, Xd.h, 0, e, Yd.h, 0), "spmm^T")
+        outs.append(Yd.numpy())
+        gpu.cuda().rails_csr_free(A)
+        Xd.free(); Yd.free()
+    assert np.array_equal(outs[0], outs[1])
+    if shape == "tall_dense_columns":
+        # rows of A' longer than the staging buffer take the whole-CTA reduction of the
+        # SpMM kernel, a different summation order from the CSR loop: rounding only
+        assert np.max(np.abs(outs[0] - want)) <= 1e-13 * np.max(np.abs(want)) * 300
+    else:
+        assert np.array_equal(outs[0], want)
+
+
 @pytest.mark.parametrize("m", [1, 2, 15, 511, 512, 513, 4099, 100003])
 @pytest.mark.parametrize("a,b", [(1, 1), (5, 1), (1, 5), (3, 2), (37, 1), (1, 200), (200, 1),
                                  (16, 16), (9, 4), (130, 3)])

@@ -3,8 +3,9 @@ path: the Epetra-style linear map, the halo plan rails_csr_halo_plan builds for
 a rank's rows (column renumbering [owned | ghost], ghost lists grouped by
 owner), and the id exchange rails_csr_create performs over NCCL -- replayed here
 with gloo send/recv pairs.  The distributed SpMM assembled from the plan must equal
-the global SpMM bit for bit (same CSR order within every row).  No GPU and no
-compute entry point of the library is used."""
+the global SpMM bit for bit (same CSR order within every row); the transposed
+apply (reverse halo: ghost contributions sent back to the owners and added) must
+equal the global A'X.  No GPU and no compute entry point of the library is used."""
 import ctypes
 import os
 import socket
@@ -109,6 +110,29 @@ def _worker(rank, world, port, kind, g, dim, q):
         rpg, cig, vg = problems.build(kind, g, dim)
         Yg = _csr_apply(rpg[r0:r1 + 1] - rpg[r0], cig[rpg[r0]:], vg[rpg[r0]:], Xg)
         assert np.array_equal(Y, Yg)
+
+        # the transposed apply on the partition (a2), as spmm.cu does it: the local
+        # block's transpose applied to the owned rows gives rows + nghost values; the
+        # ghost part goes back to the owners over the SAME plan with the lists
+        # exchanged (what was received is sent, what was sent is received) and is
+        # added there peer by peer in rank order.  Against the global A'X.
+        Z = np.zeros((rows + ng, e_cols))
+        for i in range(rows):
+            for pp in range(rp[i], rp[i + 1]):
+                Z[lcol[pp]] += v[pp] * Xl[i]
+        Yt = Z[:rows].copy()
+        back_out = list(torch.from_numpy(np.ascontiguousarray(Z[rows:])).split([int(c) for c in need]))
+        back_in = [torch.zeros((c, e_cols), dtype=torch.float64) for c in send_count]
+        _exchange(dist, rank, back_in, back_out)
+        off = 0
+        for p in range(world):
+            for j in range(send_count[p]):
+                Yt[send_rows[off + j]] += back_in[p][j].numpy()
+            off += send_count[p]
+        import scipy.sparse as sp
+        Ag = sp.csr_matrix((vg, cig, rpg), shape=(m, m))
+        want = (Ag.T @ Xg)[r0:r1]
+        assert np.max(np.abs(Yt - want)) <= 1e-13 * max(np.max(np.abs(want)), 1.0)
         dist.barrier()
         dist.destroy_process_group()
         q.put((rank, "ok"))

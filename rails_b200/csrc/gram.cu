@@ -175,11 +175,13 @@ gram_finish_kernel(const double *__restrict__ partial, int nblocks, int a, int b
 // r0 + 4g .. r0 + 4g + 3 of column k0 + t as two 128-bit words (the A fragments of
 // four MMA row blocks) and stores four consecutive rows of a result column.  The
 // k x (8 NB) block of C sits in shared memory, zero-padded to a multiple of 4 rows.
+constexpr int GEMM_RING = 8;          // k-steps (4 columns x 32 rows = 1 KB each) a warp keeps in flight
+
 template<int NB>
-__global__ void __launch_bounds__(GRAM_THREADS)
+__global__ void __launch_bounds__(GRAM_THREADS, NB <= 4 ? 4 : 2)
 gemm_dmma_kernel(const double *__restrict__ V, long long ldv, int k, const double *__restrict__ C,
                  int ldc, int c, double alpha, double beta, double *__restrict__ Out, long long ldo,
-                 long long rows)
+                 long long rows, int use_ring)
 {
     extern __shared__ double Cs[];
     constexpr int CSLD = NB * 8 + 1;
@@ -194,6 +196,7 @@ gemm_dmma_kernel(const double *__restrict__ V, long long ldv, int k, const doubl
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
+    double2 *ring = reinterpret_cast<double2 *>(Cs + (size_t)kpad * CSLD);     // kpad * CSLD * 8 is a multiple of 32
     const long long nblocks = (rows + 31) / 32;
     for (long long rb = (long long)blockIdx.x * 4 + warp; rb < nblocks; rb += (long long)gridDim.x * 4)
     {
@@ -214,13 +217,7 @@ gemm_dmma_kernel(const double *__restrict__ V, long long ldv, int k, const doubl
             else
                 load4<false>(vc, r, rows, dst);
         };
-        double a0[4], a1[4], a2[4];
-        fetch(0, a0);
-        fetch(min(4, kpad - 4), a1);
-#pragma unroll 3
-        for (int k0 = 0; k0 < kpad; k0 += 4)
-        {
-            fetch(min(k0 + 8, kpad - 4), a2);
+        auto mma_step = [&](int k0, const double (&a)[4]) {
             const double *cs = Cs + (k0 + t) * CSLD + g;
 #pragma unroll
             for (int j = 0; j < NB; ++j)
@@ -228,13 +225,61 @@ gemm_dmma_kernel(const double *__restrict__ V, long long ldv, int k, const doubl
                 const double bv = cs[8 * j];
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
-                    dmma(acc[i][j][0], acc[i][j][1], a0[i], bv);
+                    dmma(acc[i][j][0], acc[i][j][1], a[i], bv);
             }
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
+        };
+        if (full && use_ring)
+        {
+            // Round 2 (RAILS_GEMM_DMMA_RING=0 selects the register pipeline below; same
+            // box, 64 x 32 at 16.8 M rows: 3.22 ms with the ring, 3.76 ms without,
+            // profiles/r02_gemm_dmma.md): the rows of V travel through a per-lane ring in shared memory
+            // filled by 16-byte asynchronous copies (cp.async.ca), GEMM_RING k-steps deep:
+            // the loads of a warp no longer hold registers while in flight (round 1:
+            // two steps ahead in registers, 59 % of the DMMA pipe, long-scoreboard
+            // stalls), each lane reads back exactly the two words it copied, so the
+            // layout is conflict-free and no barrier is needed.
+            const int steps = kpad / 4;
+            double2 *rw = ring + (size_t)warp * GEMM_RING * 64;
+            auto issue = [&](int st) {
+                if (st < steps)
+                {
+                    const double *src = V + (size_t)min(4 * st + t, k - 1) * ldv + r;
+                    const int slot = st % GEMM_RING;
+                    const unsigned d0 = (unsigned)__cvta_generic_to_shared(rw + (slot * 2) * 32 + lane);
+                    const unsigned d1 = (unsigned)__cvta_generic_to_shared(rw + (slot * 2 + 1) * 32 + lane);
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d0), "l"(src) : "memory");
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d1), "l"(src + 2) : "memory");
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            };
+            for (int st = 0; st < GEMM_RING - 1; ++st)
+                issue(st);
+            for (int st = 0; st < steps; ++st)
             {
-                a0[i] = a1[i];
-                a1[i] = a2[i];
+                issue(st + GEMM_RING - 1);
+                asm volatile("cp.async.wait_group %0;" ::"n"(GEMM_RING - 1) : "memory");
+                const int slot = st % GEMM_RING;
+                const double2 lo = rw[(slot * 2) * 32 + lane], hi = rw[(slot * 2 + 1) * 32 + lane];
+                const double a[4] = {lo.x, lo.y, hi.x, hi.y};
+                mma_step(4 * st, a);
+            }
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        else
+        {
+            double a0[4], a1[4], a2[4];
+            fetch(0, a0);
+            fetch(min(4, kpad - 4), a1);
+            for (int k0 = 0; k0 < kpad; k0 += 4)
+            {
+                fetch(min(k0 + 8, kpad - 4), a2);
+                mma_step(k0, a0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                {
+                    a0[i] = a1[i];
+                    a1[i] = a2[i];
+                }
             }
         }
         // fragment (i, j): row r + i, columns n0 + 8 j + 2 t, + 1
@@ -280,7 +325,8 @@ int launch_gemm_dmma(const double *V, long long ldv, int k, const double *dC, in
 {
     rails::Context &cx = ctx();
     const int kpad = (k + 3) & ~3;
-    const size_t smem = (size_t)kpad * (NB * 8 + 1) * sizeof(double);
+    const size_t smem = (size_t)kpad * (NB * 8 + 1) * sizeof(double) +
+                        (size_t)(GRAM_THREADS / 32) * GEMM_RING * 64 * sizeof(double2);
     static size_t configured = 0;
     static int configured_device = -1;          // the attribute is per device
     if (configured_device != cx.device)
@@ -298,7 +344,8 @@ int launch_gemm_dmma(const double *V, long long ldv, int k, const double *dC, in
     dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((nblocks + 3) / 4, (long long)cx.sm_count * 6)),
               (unsigned)((c + NB * 8 - 1) / (NB * 8)));
     auto kern = gemm_dmma_kernel<NB>;
-    RAILS_LAUNCH(kern, grid, GRAM_THREADS, smem, V, ldv, k, dC, ldc, c, alpha, beta, Out, ldo, rows);
+    static const int use_ring = std::getenv("RAILS_GEMM_DMMA_RING") ? std::atoi(std::getenv("RAILS_GEMM_DMMA_RING")) : 1;
+    RAILS_LAUNCH(kern, grid, GRAM_THREADS, smem, V, ldv, k, dC, ldc, c, alpha, beta, Out, ldo, rows, use_ring);
     RAILS_CHECK_LAUNCH();
     return RAILS_OK;
 }
@@ -408,7 +455,8 @@ namespace rails
 bool gemm_dmma_fits(int k, int c)
 {
     const int nb = c > 32 ? 8 : 4;
-    return fp64_tensor_enabled() && c > 8 && k >= 4 && (size_t)((k + 3) & ~3) * (nb * 8 + 1) * sizeof(double) <= 200 * 1024;
+    return fp64_tensor_enabled() && c > 8 && k >= 4 &&
+           (size_t)((k + 3) & ~3) * (nb * 8 + 1) * sizeof(double) + (size_t)(GRAM_THREADS / 32) * GEMM_RING * 1024 <= 200 * 1024;
 }
 
 int gemm_dmma_device(const double *V, long long ldv, int k, const double *dC, int ldc, int c,

@@ -23,6 +23,7 @@ using rails::ctx;
 namespace rails
 {
 int scal_inv_norm_device(double *x, long long ld, long long rows, const double *d);
+int cgs2_fused(rails_mv_s *V, int first_col, int against, int vcol, const double *c1_dev, bool dist);
 }
 
 namespace
@@ -445,6 +446,18 @@ extern "C" int rails_mv_orthogonalize(rails_mv_t V, int col0, int first, int las
                 if (rc) return rc;
             }
             const int against = i - old;        // columns [old, i)
+            if (against > 0 && e == 1)
+            {
+                // one column: first projection, then both updates, the second projection
+                // and the norm out of two step-kernel passes (lanczos.cu: cgs2_fused)
+                const double *Vo1 = base + (size_t)old * V->ld;
+                rc = rails::dot_device(Vo1, V->ld, against, v, V->ld, 1, V->rows, c.d_small, against, dist);
+                if (rc) return rc;
+                rc = rails::cgs2_fused(V, col0 + old, against, col0 + i, c.d_small, dist);
+                if (rc == RAILS_OK) continue;
+                if (rc != 1) return rc;
+                // (shape outside the step kernel: the plain chain below; its first dot is repeated)
+            }
             if (against > 0)
             {
                 const double *Vo = base + (size_t)old * V->ld;

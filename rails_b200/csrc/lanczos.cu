@@ -592,7 +592,8 @@ lanczos_step_kernel(const __grid_constant__ StepMaps maps, StepLayout L, const d
         {
             if (cg == 0)
             {
-                wi[r] = q;
+                if (wi != wnext)            // CGS2 use: the column is updated in place
+                    wi[r] = q;
                 wnext[r] = x;
             }
         }
@@ -744,6 +745,14 @@ int launch_lanczos_step_untimed(int grid, size_t smem, StepMaps const &maps, Ste
     return RAILS_OK;
 }
 
+__device__ double g_cgs2_consts[2] = {-1.0, 1.0};      // alpha = -1, |w|^2 = 1 for the CGS2 use of the step kernel
+
+__global__ void __launch_bounds__(128)
+negate_kernel(const double *__restrict__ in, double *__restrict__ out, int n)
+{
+    for (int i = threadIdx.x; i < n; i += 128) out[i] = -in[i];
+}
+
 // q = w / |w| for the last column of the recurrence
 __global__ void __launch_bounds__(256)
 normalize_kernel(double *__restrict__ w, const double *__restrict__ sq_dev, long long rows)
@@ -819,6 +828,81 @@ int finish_to_host(int n, bool distributed, double *out)
     { int xrc = rails::check_exchange_error("reduction"); if (xrc) return xrc; }
     memcpy(out, c.h_small, (size_t)n * sizeof(double));
     return RAILS_OK;
+}
+
+}
+
+namespace rails
+{
+
+int scal_inv_norm_device(double *x, long long ld, long long rows, const double *d);
+
+// CGS2 of one column with the step kernel (round 2): the column v = V[:, vcol] against the
+// `against` columns before it, c1 = Vo'v already on the device.  The reference's two
+// passes (StlWrapper::orthogonalize, src/StlWrapper.cpp:305-321: dot, update, dot,
+// update, norm) read Vo four times; here
+//     step kernel:  v <- v - Vo c1,  c2 = Vo'v and |v|^2 from the same staged tile
+//     step kernel:  v <- v - Vo c2,  |v|^2                 (its Vo'v is not used)
+//     v <- v / |v|
+// read it twice more after the first dot: three passes instead of four, the same sums
+// (v - Vo c is formed as fma chain + v, exactly the update of gemm_kernel).
+// Returns 1 when the shape does not fit the step kernel (the caller runs the plain chain).
+int cgs2_fused(rails_mv_s *V, int first_col, int against, int vcol, const double *c1_dev, bool dist)
+{
+    Context &c = ctx();
+    // RAILS_CGS2_FUSED=0, or RAILS_FUSED_LANCZOS=0 (the operation-by-operation mode, which
+    // keeps the reference's call sequence everywhere), select the plain chain; read per
+    // call, the tests switch modes inside one process
+    const char *e1 = getenv("RAILS_CGS2_FUSED"), *e2 = getenv("RAILS_FUSED_LANCZOS");
+    if ((e1 && e1[0] == '0') || (e2 && strcmp(e2, "0") == 0) || against < 1 || vcol < 1)
+        return 1;
+    int n1[1] = {against};
+    StepLayout lay = ls_layout(n1, 1);
+    int tile_rows = 0, stages = 0;
+    ls_shape(lay, &tile_rows, &stages);
+    if (tile_rows == 0 || !encode_tiled())
+        return 1;
+    const long long rows = V->rows;
+    static double *scratch = nullptr, *consts = nullptr;
+    static int scratch_device = -1;
+    if (scratch_device != c.device)
+    {
+        int rc = dev_alloc_t(&scratch, (size_t)2 * (LS_MAX_COLS + 2) * sizeof(double));
+        if (rc) return rc;
+        RAILS_CUDA_TRY(cudaGetSymbolAddress((void **)&consts, g_cgs2_consts));
+        scratch_device = c.device;
+    }
+    double *coef = scratch, *g = scratch + LS_MAX_COLS + 2;
+    StepMaps maps;
+    bool have = rows > 0;
+    if (have)
+        have = make_map(&maps.m[0], V->data + (size_t)first_col * V->ld, rows, against, V->ld, lay.bc[0]) &&
+               make_map(&maps.m[MAX_SEGS], V->data, rows, V->cols, V->ld, 2);
+    if (rows > 0 && !have)
+        return 1;
+    const long long tiles = (rows + tile_rows - 1) / tile_rows;
+    const int nb = (int)std::max<long long>(1, std::min<long long>(tiles, c.sm_count));
+    int rc = ensure_partial((size_t)nb * (against + 1));
+    if (rc) return rc;
+    double *v = V->data + (size_t)vcol * V->ld;
+    const double *cin = c1_dev;
+    for (int pass = 0; pass < 2; ++pass)
+    {
+        RAILS_LAUNCH(negate_kernel, 1, 128, 0, cin, coef, against);
+        if (rows > 0)
+        {
+            rc = launch_lanczos_step(nb, ls_smem_bytes(lay, tile_rows, stages), maps, lay, (const double *)coef, v, 0, v,
+                                     vcol, (const double *)consts, (const double *)(consts + 1), rows, tile_rows, stages,
+                                     c.d_partial);
+            if (rc) return rc;
+        }
+        else
+            RAILS_CUDA_TRY(cudaMemsetAsync(c.d_partial, 0, (size_t)nb * (against + 1) * sizeof(double), c.stream));
+        rc = finish_reduction(c.d_partial, nb, against + 1, g, dist, nullptr, 0, nullptr, nullptr, nullptr, nullptr);
+        if (rc) return rc;
+        cin = g;
+    }
+    return scal_inv_norm_device(v, V->ld, rows, g + against);
 }
 
 }

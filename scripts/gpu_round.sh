@@ -13,3 +13,4 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-fi
 ncu --set full --clock-control none --import-source on -k regex:lanczos_step_kernel -s 20 -c 1 -o gpurun_out/step_full python scripts/chain_bench.py --grid 256 --k 15 --reps 2 > gpurun_out/ncu_full.log 2>&1; echo ncu_full_rc=$?
 ncu -i gpurun_out/step_full.ncu-rep --page raw --csv > gpurun_out/step_full_raw.csv 2>/dev/null
 fi
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2

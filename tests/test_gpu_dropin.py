@@ -42,9 +42,12 @@ CASES = [
 @pytest.mark.parametrize("kind,g,dim,n_b,P", CASES)
 def test_reference_loop_runs_on_cuda_wrappers(gpu, kind, g, dim, n_b, P):
     rp, ci, v = problems.build(kind, g, dim)
-    r = refloop_solve(gpu, rp, ci, v, n_b, P)
+    # both loops over the backend in its operation-by-operation configuration (the
+    # reference loop has no fused Lanczos to switch off; the setting also selects the
+    # plain CGS2 chain inside orthogonalize for both)
     os.environ["RAILS_FUSED_LANCZOS"] = "0"
     try:
+        r = refloop_solve(gpu, rp, ci, v, n_b, P)
         p = gpu.solve(rp, ci, v, n_b, P, v_cap_cols=400)
     finally:
         del os.environ["RAILS_FUSED_LANCZOS"]

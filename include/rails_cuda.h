@@ -206,6 +206,11 @@ int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc0, const in
                          const double *T, int ldt, rails_mv_t Q, int qc0, int L,
                          double *alpha, double *beta, int *steps);
 
+/* Widest [X_0 X_1 ..] (sum of xn) rails_mv_lanczos_run, _begin, _project and the
+ * multi_* entry points accept (2040: the reduced vector plus the squared norm fits one
+ * peer-memory exchange); a caller with a wider space uses the plain sequence. */
+int rails_mv_lanczos_max_columns(void);
+
 /* Optional head start: the first projection of the chain does not depend on T, so
  * it can be enqueued before the host solves the projected problem
  * (src/LyapunovSolver.hpp:209); the next rails_mv_lanczos_run with the same Q,

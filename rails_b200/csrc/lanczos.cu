@@ -35,7 +35,7 @@ constexpr int MD_WARPS = MD_THREADS / 32;
 constexpr int MD_RP = 4;                         // double2 per thread and column
 constexpr long long MD_TILE = 512LL * MD_RP;     // rows per CTA iteration
 constexpr int MD_U = 4;                          // columns in flight
-constexpr int MD_MAXCOLS = 1024;                 // 64 KB of per-warp accumulators
+constexpr int MD_MAXCOLS = 2040;                 // 128 KB of per-warp accumulators; + 1 fits one mailbox exchange (2048)
 
 int lz_attr();      // defined with the chain's scratch management below
 
@@ -1587,3 +1587,7 @@ extern "C" int rails_lanczos_step_timing_read(double *ms_total, int *launches, i
     t.used = 0;
     return RAILS_OK;
 }
+
+// Widest [V AV B] (2k + n columns) the fused Lanczos entry points take; the host loop
+// falls back to the operation-by-operation sequence beyond it.
+extern "C" int rails_mv_lanczos_max_columns(void) { return MD_MAXCOLS; }

@@ -101,6 +101,7 @@ struct FusedLanczos<CudaMultiVectorWrapper, HostDenseMatrix>
         const char *e = std::getenv("RAILS_FUSED_LANCZOS");
         return !(e && std::strcmp(e, "0") == 0);
     }
+    static bool fits(int k, int n) { return 2 * k + n <= rails_mv_lanczos_max_columns(); }
     static bool per_step()
     {
         const char *e = std::getenv("RAILS_FUSED_LANCZOS");

@@ -98,6 +98,8 @@ struct FusedLanczos
 {
     static const bool enabled = false;
     static bool active() { return false; }
+    // whether a space of k columns with an n-column B fits the fused kernels
+    static bool fits(int, int) { return true; }
     static int run(MultiVector const &, MultiVector const &, DenseMatrix const &,
                    MultiVector const &, DenseMatrix &, MultiVector &, int) { return -1; }
     // optional head start before T is known (Q holds the random start vector)

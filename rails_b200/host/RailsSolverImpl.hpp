@@ -645,7 +645,8 @@ bool Solver<Matrix, MultiVector, DenseMatrix>::lanczos_start(
     MultiVector const &AV, MultiVector const &V, MultiVector &Q, int max_iter)
 {
     if (!(FusedLanczos<MultiVector, DenseMatrix>::enabled && B_.is_multivector() &&
-          FusedLanczos<MultiVector, DenseMatrix>::active()))
+          FusedLanczos<MultiVector, DenseMatrix>::active() &&
+          FusedLanczos<MultiVector, DenseMatrix>::fits(V.N(), B_.multivector().N())))
         return false;
     Section s(sections_, "resid_lanczos");
     Q = MultiVector(V, max_iter + 1);
@@ -684,7 +685,8 @@ int Solver<Matrix, MultiVector, DenseMatrix>::resid_lanczos(
 
     int steps = 0;
     if (FusedLanczos<MultiVector, DenseMatrix>::enabled && B_.is_multivector() &&
-        FusedLanczos<MultiVector, DenseMatrix>::active())
+        FusedLanczos<MultiVector, DenseMatrix>::active() &&
+        FusedLanczos<MultiVector, DenseMatrix>::fits(V.N(), B_.multivector().N()))
     {
         // same recurrence, three fused kernels per step (backend-supplied)
         steps = FusedLanczos<MultiVector, DenseMatrix>::run(AV, V, T, B_.multivector(), H, Q,

@@ -43,11 +43,11 @@ for i in range(reps):
     if dist is not None:
         dist.barrier()
     t0 = time.time()
-    out = api.solve(rp, ci, v, n_b, P, B=B, global_rows=m, row_offset=r0, v_cap_cols=64, M=M)
+    out = api.solve(rp, ci, v, n_b, P, B=B, global_rows=m, row_offset=r0, v_cap_cols=int(os.environ.get("RAILS_TRACE_VCAP", "64")), M=M)
     t1 = time.time()
     if dist is not None:
         dist.barrier()
     t2 = time.time()
     if rank == 0:
-        print("run %d: api.solve %.4f s (+ barrier %.4f s), iterations %d, setup %.4f, solve %.4f" % (
-            i, t1 - t0, t2 - t1, out["iterations"], out["setup_seconds"], out["solve_seconds"]), flush=True)
+        print("run %d: api.solve %.4f s (+ barrier %.4f s), ret %d, iterations %d, space %d (max %d), setup %.4f, solve %.4f" % (
+            i, t1 - t0, t2 - t1, out["ret"], out["iterations"], out["k"], int(out["space"].max()), out["setup_seconds"], out["solve_seconds"]), flush=True)

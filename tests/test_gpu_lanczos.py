@@ -81,7 +81,11 @@ def test_lanczos_update(gpu, m):
         assert abs(nrm.value - np.linalg.norm(want)) <= 1e-14 * np.linalg.norm(want) * 10
 
 
-@pytest.mark.parametrize("m,k,n,L", [(5000, 7, 2, 6), (100003, 33, 1, 10), (2048, 0, 3, 2), (64, 3, 1, 12)])
+# (3001, 40, 16, 5): 96 block columns, four column groups of the one-kernel step;
+# (3001, 60, 16, 5): 136 columns, the two-kernel chain; (2500, 600, 16, 4): 1216 columns,
+# wider than round 1's 1024-column limit (config C4's own list reaches 1044)
+@pytest.mark.parametrize("m,k,n,L", [(5000, 7, 2, 6), (100003, 33, 1, 10), (2048, 0, 3, 2), (64, 3, 1, 12),
+                                     (3001, 40, 16, 5), (3001, 60, 16, 5), (2500, 600, 16, 4)])
 def test_lanczos_run_matches_the_recurrence(gpu, m, k, n, L):
     """rails_mv_lanczos_run (device-resident chain) against a numpy restatement
     of src/LyapunovSolver.hpp:375-434 on the same blocks."""
@@ -187,6 +191,17 @@ def test_block_errors(gpu):
     assert lib.rails_mv_multi_dot(1, hs, c0, nn, A.h, 1, 0.5, gpu.dptr(g)) == 2     # rescaled q inside block
     al = ctypes.c_double(0)
     assert lib.rails_mv_multi_gemv(1, hs, c0, nn, gpu.dptr(g), A.h, 2, None, 0, ctypes.byref(al)) == 2
+    # wider than the fused entry points take: refused with an argument error, and the
+    # limit is what rails_mv_lanczos_max_columns reports (the host loop asks it)
+    lim = lib.rails_mv_lanczos_max_columns()
+    assert lim == 2040
+    W = gpu.MultiVector(16, lim + 1)
+    hs = (P * 1)(W.h)
+    c1 = (ctypes.c_int * 1)(0)
+    n1 = (ctypes.c_int * 1)(lim + 1)
+    q = gpu.MultiVector(16, 2)
+    gw = np.zeros(lim + 1)
+    assert lib.rails_mv_multi_dot(1, hs, c1, n1, q.h, 0, 1.0, gpu.dptr(gw)) == 2
 
 
 # cases the reference reproduces against itself (tests/golden/ref_self_stability.json):

@@ -1,6 +1,11 @@
 // Context, communicator and multivector storage of librails_cuda.so.
 #include "internal.h"
 
+#include <sched.h>
+#include <cctype>
+#include <cstdio>
+#include <string>
+
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -344,6 +349,53 @@ int ensure_small(size_t doubles)
 
 using rails::ctx;
 
+namespace
+{
+// RAILS_NUMA_BIND=1: restrict the calling thread (and the threads it creates later: the
+// staging copies) to the CPUs next to the GPU, as listed by the kernel in
+// /sys/bus/pci/devices/<bus id>/local_cpulist, so that pinned staging buffers and the
+// caller's arrays are first-touched on the GPU's NUMA node.  Off by default: measured
+// on the 8-GPU box of this pool (profiles/r02_scaling.md).  Failures are ignored.
+void bind_to_gpu_numa_node(int device)
+{
+    const char *e = getenv("RAILS_NUMA_BIND");
+    if (!(e && e[0] == '1'))
+        return;
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, sizeof(bus), device) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return;
+    }
+    for (char *p = bus; *p; ++p) *p = (char)tolower(*p);
+    const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/local_cpulist";
+    FILE *f = fopen(path.c_str(), "r");
+    if (!f) return;
+    char line[4096] = {0};
+    const bool got = fgets(line, sizeof(line), f) != nullptr;
+    fclose(f);
+    if (!got) return;
+    cpu_set_t allowed, want;
+    if (sched_getaffinity(0, sizeof(allowed), &allowed) != 0) return;
+    CPU_ZERO(&want);
+    int n = 0;
+    for (char *tok = strtok(line, ",\n"); tok; tok = strtok(nullptr, ",\n"))
+    {
+        int a = 0, b = 0;
+        const int parts = sscanf(tok, "%d-%d", &a, &b);
+        if (parts == 1) b = a;
+        if (parts < 1) continue;
+        for (int cpu = a; cpu <= b && cpu < CPU_SETSIZE; ++cpu)
+            if (CPU_ISSET(cpu, &allowed)) { CPU_SET(cpu, &want); ++n; }
+    }
+    if (n >= 2)
+        sched_setaffinity(0, sizeof(want), &want);
+    if (getenv("RAILS_NUMA_VERBOSE"))
+        fprintf(stderr, "rails_cuda_init: device %d (%s) local cpus %d of %d allowed\n", device, bus, n,
+                CPU_COUNT(&allowed));
+}
+}
+
 extern "C" int rails_cuda_init(int device)
 {
     rails::Context &c = ctx();
@@ -359,6 +411,7 @@ extern "C" int rails_cuda_init(int device)
         return rails::fail(RAILS_ERR_ARG, "device %d out of range (0..%d)", device, ndev - 1);
     RAILS_CUDA_TRY(cudaSetDevice(device));
     c.device = device;
+    bind_to_gpu_numa_node(device);
     cudaDeviceProp prop;
     RAILS_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     c.sm_count = prop.multiProcessorCount;

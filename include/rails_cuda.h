@@ -211,6 +211,12 @@ int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc0, const in
  * peer-memory exchange); a caller with a wider space uses the plain sequence. */
 int rails_mv_lanczos_max_columns(void);
 
+/* Host-only (no CUDA call, usable before rails_cuda_init): the launch shape the
+ * one-kernel Lanczos step takes for blocks of xn[0..nblk) columns.  shape6 = {tile
+ * rows (0: the two-kernel chain runs instead), pipeline stages, column groups, dynamic
+ * shared memory in bytes, TMA requests per 128-row slab, consumer warps}. */
+int rails_lanczos_step_shape(int nblk, const int *xn, int *shape6);
+
 /* Optional head start: the first projection of the chain does not depend on T, so
  * it can be enqueued before the host solves the projected problem
  * (src/LyapunovSolver.hpp:209); the next rails_mv_lanczos_run with the same Q,

@@ -115,6 +115,7 @@ CUDA_SYMBOLS = [
     ("rails_mv_lanczos_begin", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, P, I]),
     ("rails_mv_lanczos_project", I, [I, ctypes.POINTER(P), c_int_p, c_int_p, P, I, I, I, D, c_double_p]),
     ("rails_mv_lanczos_max_columns", I, []),
+    ("rails_lanczos_step_shape", I, [I, c_int_p, c_int_p]),
     ("rails_lanczos_step_timing", I, [I]),
     ("rails_lanczos_step_timing_read", I, [c_double_p, c_int_p, c_int_p]),
     ("rails_mv_orthogonalize", I, [P, I, I, I]),

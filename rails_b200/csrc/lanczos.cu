@@ -1591,3 +1591,31 @@ extern "C" int rails_lanczos_step_timing_read(double *ms_total, int *launches, i
 // Widest [V AV B] (2k + n columns) the fused Lanczos entry points take; the host loop
 // falls back to the operation-by-operation sequence beyond it.
 extern "C" int rails_mv_lanczos_max_columns(void) { return MD_MAXCOLS; }
+
+// Host-only view of how the one-kernel Lanczos step would be launched for blocks of
+// xn[0..nblk) columns (no CUDA call; tests/test_abi.py checks the invariants on CPU):
+// shape6 = {tile rows (0: the two-kernel chain runs instead), pipeline stages, column
+// groups, dynamic shared memory in bytes, TMA requests per 128-row slab, consumer warps}.
+extern "C" int rails_lanczos_step_shape(int nblk, const int *xn, int *shape6)
+{
+    if (nblk < 1 || nblk > MAX_SEGS || !xn || !shape6)
+        return RAILS_ERR_ARG;
+    int n[MAX_SEGS], nseg = 0;
+    for (int b = 0; b < nblk; ++b)
+        if (xn[b] > 0) n[nseg++] = xn[b];
+    StepLayout L = ls_layout(n, nseg);
+    int tr = 0, st = 0;
+    if (L.total > 0)
+        ls_shape(L, &tr, &st);
+    int nreq = 1;
+    for (int b = 0; b < L.nseg; ++b)
+        nreq += (L.n[b] + L.bc[b] - 1) / L.bc[b];
+    const int groups = L.total > 0 && L.total <= LS_MAX_COLS ? ls_groups(L.total) : 0;
+    shape6[0] = tr;
+    shape6[1] = st;
+    shape6[2] = groups;
+    shape6[3] = tr ? (int)ls_smem_bytes(L, tr, st) : 0;
+    shape6[4] = nreq;
+    shape6[5] = tr ? tr / 32 * groups : 0;
+    return RAILS_OK;
+}

@@ -94,3 +94,53 @@ def test_partition_rows_matches_epetra_linear_map():
             prev = e.value
             assert e.value - b.value in (m // P, m // P + 1)
         assert prev == m
+
+
+def test_lanczos_step_launch_shapes_fit_the_machine():
+    """Host-only plan of the one-kernel Lanczos step (rails_lanczos_step_shape, no CUDA
+    call): for every space size and block shape the solver can present, the chosen tile,
+    pipeline depth and warp roles respect the limits the kernel is written for -- 216 KB
+    of dynamic shared memory, at most 16 consumer warps (8 for the wide instances), 2-6
+    stages, tiles of whole 128-row TMA boxes, at most 64 TMA requests per slab -- and the
+    path is declined (tile rows 0) beyond 96 block columns, where the two-kernel chain
+    runs."""
+    lib = api.cuda()
+    shape = (ctypes.c_int * 6)()
+    seen = set()
+    declined = []
+    for n_b in (1, 2, 3, 4, 16):
+        for k in range(0, 60):
+            for blocks in ((k, k, n_b), (k, k, n_b, 0)):          # [V AV B]; an empty fourth block
+                if sum(blocks) == 0:
+                    continue
+                xn = (ctypes.c_int * len(blocks))(*blocks)
+                assert lib.rails_lanczos_step_shape(len(blocks), xn, shape) == 0
+                tr, st, groups, smem, nreq, warps = list(shape)
+                total = 2 * k + n_b
+                if total > 96:
+                    assert tr == 0 and smem == 0
+                    continue
+                if tr == 0:
+                    # no candidate fits the shared-memory budget: only right at the column
+                    # limit with padded blocks (e.g. 46 + 46 + 4); the two-kernel chain runs
+                    assert total >= 90, (k, n_b)
+                    declined.append((k, n_b))
+                    continue
+                assert tr in (128, 256, 384, 512), (k, n_b, tr)
+                assert 2 <= st <= 6
+                assert smem <= 216 * 1024
+                assert nreq <= 64
+                assert groups == (1 if total <= 50 else -(-total // 24))
+                assert warps == tr // 32 * groups
+                assert warps <= (8 if 24 < total <= 50 else 16)
+                # the staged tiles alone must fit: stages x (padded columns + 2 basis columns) x rows
+                assert st * (total + 2) * tr * 8 <= smem
+                seen.add((tr, st, groups))
+    # the shapes the measurements of profiles/r02_lanczos_step.md were taken at
+    for k, want in ((5, (512, 3, 1)), (15, (256, 3, 1)), (24, (256, 2, 1)), (30, (128, 3, 3)), (47, (128, 2, 4))):
+        xn = (ctypes.c_int * 3)(k, k, 1)
+        assert lib.rails_lanczos_step_shape(3, xn, shape) == 0
+        assert tuple(shape[:3]) == want, (k, tuple(shape[:3]))
+    assert len(seen) >= 5
+    assert len(set(declined)) <= 4, declined
+    assert lib.rails_lanczos_step_shape(0, None, shape) == 2          # RAILS_ERR_ARG

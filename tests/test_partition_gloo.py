@@ -156,3 +156,58 @@ def test_halo_plan_and_exchange(world, kind, g, dim):
         p.join(60)
     for rank, msg in results:
         assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+@pytest.mark.parametrize("case", ["grid", "random", "all_ghost"])
+def test_device_plan_algorithm_in_numpy_equals_the_host_plan(case):
+    """The steps rails_csr_create runs on the device (spmm.cu: mark ghost columns in a byte
+    map, count per 2048-entry chunk, scan the counts, write the flagged indices in order,
+    renumber with a binary search in that list), restated in numpy, against the host plan
+    rails_csr_halo_plan: same renumbering and ghost list.  (The CUDA kernels themselves are
+    compared bit for bit on the GPU, tests/test_gpu_kernels.py.)"""
+    sys.path.insert(0, ROOT)
+    from rails_b200 import api, problems
+    lib = api.cuda()
+    rs = np.random.RandomState(3)
+    world = 3
+    if case == "grid":
+        g = 11
+        m = g ** 3
+        r0, r1 = problems.partition_rows(m, world, 1)
+        rp, ci, _ = problems.build("convdiff", g, 3, r0, r1)
+    elif case == "random":
+        m = 9001
+        r0, r1 = problems.partition_rows(m, world, 2)
+        per = rs.randint(0, 7, r1 - r0)
+        rp = np.concatenate([[0], np.cumsum(per)]).astype(np.int32)
+        ci = rs.randint(0, m, int(rp[-1])).astype(np.int32)
+    else:
+        m = 5000
+        r0, r1 = problems.partition_rows(m, world, 1)
+        rp = np.arange(r1 - r0 + 1, dtype=np.int32)
+        ci = rs.randint(0, r0, r1 - r0).astype(np.int32)
+    rows, nnz = r1 - r0, int(rp[-1])
+    # host plan
+    lcol = np.zeros(max(nnz, 1), dtype=np.int32)
+    gg = np.zeros(max(nnz, 1), dtype=np.int32)
+    gl = np.zeros(max(nnz, 1), dtype=np.int32)
+    need = np.zeros(world, dtype=np.int32)
+    ng = ctypes.c_int(0)
+    assert lib.rails_csr_halo_plan(rows, m, r0, world, api.iptr(rp), api.iptr(ci), api.iptr(lcol), ctypes.byref(ng),
+                                   api.iptr(gg), api.iptr(gl), api.iptr(need)) == 0
+    # the device algorithm, step by step
+    CH = 2048
+    nchunks = -(-m // CH)
+    flags = np.zeros(nchunks * CH, dtype=np.uint8)
+    ghost_entry = (ci < r0) | (ci >= r1)
+    flags[ci[ghost_entry]] = 1                                        # mark_ghost_kernel
+    counts = flags.reshape(nchunks, CH).sum(axis=1).astype(np.int64)  # count_ghost_kernel
+    offsets = np.concatenate([[0], np.cumsum(counts)])                # host scan of the chunk counts
+    glist = np.zeros(int(offsets[-1]), dtype=np.int32)
+    for ch in range(nchunks):                                         # write_ghost_kernel: ordered inside a chunk
+        idx = np.nonzero(flags[ch * CH:(ch + 1) * CH])[0] + ch * CH
+        glist[offsets[ch]:offsets[ch + 1]] = idx
+    new = np.where(ghost_entry, rows + np.searchsorted(glist, ci), ci - r0).astype(np.int32)   # renumber_kernel
+    assert ng.value == glist.size
+    assert np.array_equal(glist, gg[:ng.value])
+    assert np.array_equal(new, lcol[:nnz])

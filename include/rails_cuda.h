@@ -201,7 +201,9 @@ int rails_mv_lanczos_update(rails_mv_t next, int nc, double alpha, rails_mv_t q,
  * Q[:, qc0] holds the un-normalised start vector and Q has room for L + 1
  * columns from qc0.  On return alpha[i] = H(i,i), beta[i] = H(i+1,i) for
  * i < *steps; *steps < L after a breakdown (beta < 1e-14, :419-427).  One host
- * synchronisation for the whole call. */
+ * synchronisation for the whole call; per step one kernel that reads the blocks
+ * once (TMA-staged tiles) and one single-CTA kernel that finishes the reduction,
+ * exchanges it with the other ranks and forms the k x k products and alpha. */
 int rails_mv_lanczos_run(int nblk, const rails_mv_t *X, const int *xc0, const int *xn,
                          const double *T, int ldt, rails_mv_t Q, int qc0, int L,
                          double *alpha, double *beta, int *steps);

@@ -16,6 +16,14 @@
 // Reductions are deterministic: per-warp shuffle trees, per-CTA partials in
 // global memory, a second kernel adds the partials in a fixed order; with a
 // communicator the small result is all-reduced over the ranks (NCCL).
+//
+// Round 2.  The device-resident chain (rails_mv_lanczos_run) runs a step as ONE kernel,
+// lanczos_step_kernel: a row tile of [V AV B] is staged once in shared memory by TMA
+// and serves both the new vector (row-local) and the next projection, so every column
+// is read ONCE per step, m (8 (2k + n) + 32) bytes; alpha comes out of the finish
+// kernel as g . coef, so there is one cross-GPU reduction per step.  The three entry
+// points above remain as the "step" mode and for shapes the step kernel declines
+// (more than 96 block columns).  DESIGN.md section 4, profiles/r02_lanczos_step.md.
 #include "internal.h"
 #include "tma.cuh"
 

@@ -79,3 +79,32 @@ def test_cgs2_pass_is_the_same_kernel_with_other_scalars():
     c2 = V.T @ x
     y = V @ (-c2) + x
     assert np.max(np.abs(V.T @ y)) <= 1e-15 * np.linalg.norm(v) * 10      # twice is enough
+
+
+def test_stable_radix_sort_by_column_gives_the_transposed_csr():
+    """transpose.cu in numpy: histogram of the columns -> scan = row pointers of A';
+    LSD radix sort of (column, position) by column, 8 bits a pass, each pass STABLE;
+    gather.  Because CSR positions ascend with the row and every pass is stable, each row
+    of A' lists its entries by ascending original row -- scipy's A.T.tocsr() with sorted
+    indices, entry for entry."""
+    import scipy.sparse as sp
+    rs = np.random.RandomState(2)
+    m, n = 900, 70001                                   # 17 bits of column index: three passes
+    A = sp.random(m, n, density=0.003, format="csr", random_state=rs, data_rvs=lambda k: rs.uniform(-1, 1, k))
+    A.sort_indices()
+    rp, ci, v = A.indptr, A.indices, A.data
+    nnz = ci.size
+    rowptr_t = np.concatenate([[0], np.cumsum(np.bincount(ci, minlength=n))])
+    keys, pos = ci.copy(), np.arange(nnz)
+    bits = 1
+    while (1 << bits) < n:
+        bits += 1
+    for shift in range(0, bits, 8):
+        order = np.argsort((keys >> shift) & 255, kind="stable")
+        keys, pos = keys[order], pos[order]
+    rows_of_pos = np.searchsorted(rp, pos, side="right") - 1        # the binary search of the gather kernel
+    At = A.T.tocsr()
+    At.sort_indices()
+    assert np.array_equal(rowptr_t, At.indptr)
+    assert np.array_equal(rows_of_pos, At.indices)
+    assert np.array_equal(v[pos], At.data)
